@@ -1,0 +1,289 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the per-frame 2x upscaler hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cnn|bicubic] [--impl reference]
+
+One JSON line on stdout (rank 0).  Metric (BASELINE.json): 2x-SR frames/sec at 1080p->2160p.
+
+* ``value``   device-resident throughput: inputs already in HBM, CUDA events on the launching stream,
+              barrier + synchronize on both sides, max over ranks; frames of ALL ranks / that time.
+* ``e2e``     same metric through the public host-buffer call (``vex_upscale_host`` behind
+              ``B200VideoEnhancer``): pinned host frames -> H2D -> kernels -> D2H, copies inside the timed region.
+* ``roofline``  dominant kernel against MEASURED_PEAKS.json (HBM GB/s for bicubic, bf16 TFLOP/s for the CNN).
+* ``cpu_baseline``  the oracle (the reference's own torch-CPU code path) on this box's host cores, bounded sample.
+* ``--impl reference``  times only that CPU path, on all host threads (rank 0 only).
+
+A step = one pass of the hot path over one batch of synthetic frames (``config.frames_per_step`` per GPU).
+Inputs are larger than L2 (126 MB) for both workloads, so no explicit L2 flush is needed (``config.l2``).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H, W = 1080, 1920
+BICUBIC_BYTES_PER_FRAME = H * W * 3 * 5                 # read HW3 + write 4HW3
+CNN_FLOP_PER_PX = 1_508_352
+DEFAULT_WORKLOAD = "bicubic"                            # flipped to "cnn" once the tcgen05 path is parity-green
+METRIC = "2x-SR frames/sec at 1080p->2160p"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index: int, period=0.05):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {"hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40,
+                 "sw_power_cap": 0x4, "hw_power_brake_slowdown": 0x80, "sync_boost": 0x10,
+                 "applications_clocks_setting": 0x2}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop.set()
+        self.join(timeout=2)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+# --------------------------------------------------------------------------------------- CPU reference arm
+
+def cpu_reference(workload: str, budget_s: float):
+    """The reference's own CPU implementation of the path (oracle = app.py code on torch CPU), all host threads.
+    Bounded sample: as many 1080p frames as fit in ~budget_s (at least 1)."""
+    import torch
+    from oracle import upscaler_ref as O
+    from video_enhancer_proto_b200 import synth
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    frames = synth.mixed_clip(3, H, W, seed=1234)
+    if workload == "bicubic":
+        fn = O.ref_bicubic_frame
+    else:
+        model = O.make_model(0)
+        fn = lambda f: O.ref_cnn_frame(model, f)
+    n, t0 = 0, time.perf_counter()
+    if workload == "bicubic":
+        fn(frames[0])                                     # warm the thread pool (cheap for bicubic only)
+        t0 = time.perf_counter()
+    while True:
+        fn(frames[n % len(frames)])
+        n += 1
+        dt = time.perf_counter() - t0
+        if dt >= budget_s or n >= 300:
+            break
+    return {"value": n / dt, "unit": "frames/s", "cores": cores, "kind": "port",
+            "sample": f"{n} frame(s) 1080p->2160p, {workload}, torch {torch.__version__} CPU fp32, {torch.get_num_threads()} threads, {dt:.1f}s"}
+
+
+def run_reference(args, workload):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    per_step = 4.0 if workload == "bicubic" else 30.0
+    vals, base = [], None
+    for _ in range(max(1, min(args.steps, 3))):
+        base = cpu_reference(workload, per_step)
+        vals.append(base["value"])
+    v = float(np.mean(vals))
+    base["value"] = v
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus,
+            "steps": len(vals), "warmup": 0, "ms_per_step": 1000.0 / v, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(workload), "note": "reference CPU path (oracle port), bounded sample per step"},
+            "cpu_baseline": base,
+            "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(w):
+    return {"bicubic": "bicubic fallback 2x 1080p->2160p uint8 (BASELINE configs[1])",
+            "cnn": "AdvancedUpscaler 2x CNN bf16 1080p->2160p, batch 8 frames/GPU (BASELINE configs[2]/[3])"}[w]
+
+
+# --------------------------------------------------------------------------------------- GPU arm
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=["cnn", "bicubic"])
+    ap.add_argument("--frames", type=int, default=0, help="frames per step per GPU (0 = workload default)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    workload = args.workload
+    if args.impl == "reference":
+        return run_reference(args, workload)
+
+    import torch
+    import torch.distributed as dist
+    from video_enhancer_proto_b200 import B200VideoEnhancer, synth, _lib, shard
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    warmup = max(args.warmup, 3)
+    fps_step = args.frames or (300 if workload == "bicubic" else 8)
+
+    enh = B200VideoEnhancer(device=f"cuda:{local}", seed=0, batch_size=8)
+    enh._ensure_ctx()
+    # synthetic pool: 12 distinct frames (random / demo pattern / edges, seed 1234+rank), tiled to the batch
+    pool = synth.mixed_clip(12, H, W, seed=1234 + rank)
+    dev_pool = torch.from_numpy(np.stack(pool)).cuda()
+    idx = torch.arange(fps_step, device="cuda") % len(pool)
+    dev_in = dev_pool[idx].contiguous()                     # [F,1080,1920,3] resident in HBM
+    dev_out = torch.empty((fps_step, 2 * H, 2 * W, 3), dtype=torch.uint8, device="cuda")
+    mode = "bicubic" if workload == "bicubic" else "cnn"
+
+    def step():
+        enh.upscale_device(dev_in, mode=mode, out=dev_out)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(warmup):
+        step()
+    barrier()
+    l0 = enh.kernel_launches()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    barrier()
+    ev[0].record()
+    for i in range(args.steps):
+        step()
+        ev[i + 1].record()
+    barrier()
+    clocks = sampler.stop()
+    launches = enh.kernel_launches() - l0
+    total_ms = ev[0].elapsed_time(ev[-1])
+    step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    t = torch.tensor([total_ms], device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    value = world * fps_step * args.steps / (total_ms / 1e3)
+
+    # ---- end to end: pinned host pool -> vex_upscale_host -> pinned host output
+    e2e_frames = min(fps_step, 96) if workload == "bicubic" else fps_step
+    fin = H * W * 3
+    pin_in = enh._pinned_buf("in", e2e_frames * fin)
+    pin_out = enh._pinned_buf("out", e2e_frames * fin * 4)
+    vin = pin_in.numpy()[: e2e_frames * fin].reshape(e2e_frames, H, W, 3)
+    for i in range(e2e_frames):
+        vin[i] = pool[i % len(pool)]
+    mode_id = _lib.VEX_MODE_BICUBIC if workload == "bicubic" else _lib.VEX_MODE_CNN
+    lib = _lib.load()
+
+    def e2e_step():
+        rc = lib.vex_upscale_host(enh._ctx, mode_id, pin_in.data_ptr(), pin_out.data_ptr(), e2e_frames, H, W, 8, 0)
+        _lib.check(enh._ctx, rc, "vex_upscale_host")
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    e2e_steps = max(3, min(args.steps, 10))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()                                           # returns when every output frame is on the host
+    torch.cuda.synchronize()
+    dt = torch.tensor([time.perf_counter() - t0], device="cuda")
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    e2e_value = world * e2e_frames * e2e_steps / float(dt.item())
+
+    peaks = load_peaks()
+    if workload == "bicubic":
+        kern_ms = float(np.mean(step_ms))                    # the step IS one launch of bicubic2x_tile_kernel
+        achieved = BICUBIC_BYTES_PER_FRAME * fps_step / (kern_ms / 1e3) / 1e9
+        roof = {"bound": "hbm", "kernel": "bicubic2x_tile_kernel", "achieved": achieved, "peak": peaks["hbm_gbs"],
+                "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks["source"],
+                "algorithmic_bytes_per_launch": BICUBIC_BYTES_PER_FRAME * fps_step, "launch_ms": kern_ms}
+        dtype = "u8"
+    else:
+        prof = enh.cnn_profile(dev_in, dev_out) if hasattr(enh, "cnn_profile") else None
+        flops = CNN_FLOP_PER_PX * H * W * fps_step
+        kern_ms = float(np.mean(step_ms))
+        achieved = flops / (kern_ms / 1e3) / 1e12
+        roof = {"bound": "tensor", "kernel": "cnn forward (all layers)", "achieved": achieved,
+                "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s", "frac": achieved / peaks["bf16_tflops_sustained"],
+                "traffic": None, "peak_source": peaks["source"] + " (sustained)", "layers": prof}
+        dtype = "bf16"
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+                "warmup": warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": dtype, "data": "synthetic",
+                "config": {"workload": workload_name(workload), "frames_per_step_per_gpu": fps_step, "height": H, "width": W,
+                           "l2": f"inputs per step {fps_step * fin / 1e6:.0f} MB + outputs {fps_step * fin * 4 / 1e6:.0f} MB > 126 MB L2, no flush",
+                           "sharding": "contiguous frame ranges per GPU, no collective"},
+                "clocks": clocks, "gpu_launches": int(launches),
+                "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": e2e_frames * fin,
+                        "d2h_bytes_per_step": e2e_frames * fin * 4, "frames_per_step": e2e_frames, "steps": e2e_steps,
+                        "api": "vex_upscale_host (pinned host in/out, 2 slots x 8-frame chunks)"},
+                "roofline": roof}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_reference(workload, 6.0 if workload == "bicubic" else 25.0)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    enh.close()
+
+
+if __name__ == "__main__":
+    main()

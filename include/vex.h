@@ -1,0 +1,126 @@
+/*
+ * vex.h — C ABI of libvex.so: the B200-native (sm_100a) per-frame 2x upscaler hot path.
+ *
+ * The reference (mindburnlabs/video-enhancer-proto) is pure Python and has NO FFI for this
+ * path; its boundary is the duck-typed GPUVideoEnhancer / handler object.  This ABI is what
+ * the Python mirror of that object (video_enhancer_proto_b200/upscaler.py) binds with ctypes.
+ * Each entry point cites the reference code it replaces (paths relative to the reference repo).
+ *
+ * Conventions
+ *   - every function returns 0 (VEX_OK) or a negative vex_status; nothing throws or exits;
+ *   - vex_ctx is opaque, one per device, NOT thread-safe (the reference holds one global
+ *     `enhancer`, app.py:624, and max_concurrent_tasks=1, agents/enhancer/video_enhancer_sota.py:72);
+ *   - frame buffers are caller-owned, packed uint8 HWC, no row padding, frames contiguous;
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream); device-pointer
+ *     entry points are asynchronous on it;
+ *   - there is NO CPU fallback: without a usable sm_100 device vex_create fails.
+ */
+#ifndef VEX_H_
+#define VEX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VEX_ABI_VERSION 1
+
+typedef enum vex_status {
+  VEX_OK = 0,
+  VEX_ERR_INVALID = -1,      /* bad argument (null pointer, non-positive size, bad flag) */
+  VEX_ERR_CUDA = -2,         /* a CUDA runtime/driver call failed; see vex_last_error */
+  VEX_ERR_NO_WEIGHTS = -3,   /* CNN entry point called before vex_cnn_load_weights */
+  VEX_ERR_UNSUPPORTED = -4,  /* device is not sm_100, or architecture plan not supported */
+  VEX_ERR_NOMEM = -5
+} vex_status;
+
+typedef struct vex_ctx vex_ctx;
+
+/* ---- lifetime --------------------------------------------------------------------------- */
+
+/* Replaces GPUVideoEnhancer.__init__ / load_models (app.py:245-263). */
+int vex_create(int device_ordinal, vex_ctx** out);
+int vex_destroy(vex_ctx* ctx);
+/* Owned by ctx, valid until the next call on ctx.  ctx may be NULL (returns the create error). */
+const char* vex_last_error(const vex_ctx* ctx);
+int vex_abi_version(void);
+
+/* ---- bicubic fallback ------------------------------------------------------------------- */
+
+/* 2x bicubic (Keys cubic, A=-0.75, align_corners=False, border replicate), per channel.
+ * Replaces GPUVideoEnhancer._enhance_frame_cpu_fallback (app.py:359-385) for round_mode 0
+ * (clip then TRUNCATE, app.py:376) and cv2.resize(..., INTER_CUBIC)
+ * (models/enhancement/frame/basic_upscaler_fallback.py:142, realesrgan_fallback.py:104) for
+ * round_mode 1 (round half up).  in: n*[h][w][3] u8 device; out: n*[2h][2w][3] u8 device. */
+int vex_bicubic2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc,
+                     int n, int h, int w, int round_mode, void* stream);
+
+/* ---- CNN upscaler ------------------------------------------------------------------------ */
+
+/* Channel plan of the AdvancedUpscaler family (app.py:269-301):
+ *   conv1 3->c1, conv2 c1->c2 (+skip, needs c1==c2), conv3 c2->c3, conv4 c3->c4, conv5 c4->3,
+ *   upconv1 ConvT 3->up_ch k4 s2 p1, upconv2 ConvT up_ch->3 k3 s1 p1.
+ * The reference is {128,128,256,128,64}.  All widths must be multiples of 64, <= 256; up_ch 64. */
+typedef struct vex_cnn_desc {
+  int c1, c2, c3, c4, up_ch;
+  float bn_eps;              /* 1e-5 (nn.BatchNorm2d default, app.py:284-287) */
+} vex_cnn_desc;
+
+#define VEX_CNN_NUM_TENSORS 30
+/* tensors[i]: fp32 host arrays in the reference module's state_dict order (app.py:273-287):
+ *   conv1..conv5 {weight,bias}, upconv1 {weight,bias}, upconv2 {weight,bias},
+ *   bn1..bn4 {weight,bias,running_mean,running_var}     (num_batches_tracked is skipped).
+ * Folds eval-mode BN into per-channel scale/shift, converts weights to bf16 in the kernels'
+ * layouts, uploads.  Copies; the caller keeps ownership.  Replaces _create_gpu_upscaler
+ * (app.py:265-311) minus the random init (the caller supplies the values). */
+int vex_cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch,
+                         const float* const* tensors, int n_tensors);
+
+/* n frames u8 HWC [h][w][3] -> u8 HWC [2h][2w][3], device pointers.
+ * in_bgr/out_bgr: channel order of the buffers relative to the network's RGB planes
+ * (the batch path takes RGB and returns BGR, app.py:469,550; the single-frame path does not
+ * swap, app.py:334-346).  Replaces _process_frame_batch_gpu (app.py:529-553) and
+ * _enhance_frame_with_gpu (app.py:322-352) including clip(x*255,0,255).astype(uint8). */
+int vex_cnn2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc,
+                 int n, int h, int w, int in_bgr, int out_bgr, void* stream);
+
+/* Parity hook: same network, pre-quantisation fp32 output, NCHW [n][3][2h][2w] (device).
+ * `tap` selects what is written: 0 = final clamp(upconv2) (app.py:299); 1..5 = x1..x5
+ * (NCHW fp32, [n][C][h][w]); 6 = relu(upconv1) ([n][up_ch][2h][2w]). */
+int vex_cnn2x_f32_debug(vex_ctx* ctx, const uint8_t* in_hwc, float* out_nchw,
+                        int n, int h, int w, int in_bgr, int tap, void* stream);
+
+/* Bytes of device workspace the ctx holds (grows on demand) for a batch of this shape. */
+int vex_workspace_bytes(const vex_ctx* ctx, int n, int h, int w, size_t* out);
+
+/* ---- host-buffer streaming entry (the end-to-end path) ------------------------------------ */
+
+#define VEX_MODE_BICUBIC 0
+#define VEX_MODE_CNN 1
+
+/* Pinned host memory for frame pools (cudaHostAlloc); frames decoded into it stream without
+ * an extra staging copy. */
+int vex_host_alloc(vex_ctx* ctx, size_t bytes, void** out);
+int vex_host_free(vex_ctx* ctx, void* p);
+
+/* n frames from HOST memory to HOST memory: chunks of `chunk` frames are copied H2D, upscaled
+ * and copied D2H on double-buffered streams so copy and compute overlap; returns when every
+ * output frame is in out_host.  Pageable pointers work (slower); vex_host_alloc'd ones overlap.
+ * flags: bit0 round_mode (bicubic) / in_bgr (cnn); bit1 out_bgr (cnn).
+ * Replaces the frame loop body of _process_video_gpu_decorated (app.py:458-482) between
+ * cap.read() and out.write(). */
+int vex_upscale_host(vex_ctx* ctx, int mode, const uint8_t* in_host, uint8_t* out_host,
+                     int n, int h, int w, int chunk, int flags);
+
+/* Counters for bench.py's `gpu_launches`: kernels launched by this ctx since creation. */
+int vex_kernel_launches(const vex_ctx* ctx, unsigned long long* out);
+
+/* Debug knobs for bring-up (kernel variant selection); returns previous value or <0. */
+int vex_set_option(vex_ctx* ctx, const char* name, int value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VEX_H_ */

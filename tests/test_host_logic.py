@@ -1,0 +1,116 @@
+"""CPU: host-side logic — weights procedure, frame sharding (incl. a world_size-2 gloo run), interface shape."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from video_enhancer_proto_b200 import shard, weights as W
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_init_state_is_the_reference_procedure():
+    from oracle import upscaler_ref as O
+    for seed in (0, 3):
+        a, b = W.init_state(seed), O.export_state(O.make_model(seed))
+        assert list(a) == list(b) == list(W.STATE_DICT_KEYS)
+        for k in a:
+            assert np.array_equal(a[k], b[k]), k
+
+
+def test_normalize_state_rejects_bad_shapes():
+    st = dict(W.init_state(0))
+    W.normalize_state(st)
+    bad = dict(st)
+    bad["conv3.weight"] = bad["conv3.weight"][:, :64]
+    with pytest.raises(ValueError):
+        W.normalize_state(bad)
+    del bad["conv3.weight"]
+    with pytest.raises(KeyError):
+        W.normalize_state(bad)
+    assert W.infer_plan(st) == ((128, 128, 256, 128), 64)
+
+
+@pytest.mark.parametrize("world,n", [(1, 5), (2, 5), (4, 3000), (8, 3000), (8, 3), (3, 0)])
+def test_frame_ranges_partition(world, n):
+    rs = shard.all_ranges(world, n)
+    assert rs[0][0] == 0 and rs[-1][1] == n
+    assert all(a[1] == b[0] for a, b in zip(rs, rs[1:]))
+    sizes = [hi - lo for lo, hi in rs]
+    assert max(sizes) - min(sizes) <= 1
+    for f in range(0, n, max(1, n // 7)):
+        r = shard.owner_of(f, world, n)
+        assert rs[r][0] <= f < rs[r][1]
+    merged = shard.merge_ordered([list(range(lo, hi)) for lo, hi in rs], world, n)
+    assert merged == list(range(n))
+    if n:
+        with pytest.raises(ValueError):
+            shard.merge_ordered([[] for _ in rs], world, n)
+
+
+def _worker(rank, world, port, n_frames, q):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    lo, hi = shard.frame_range(rank, world, n_frames)
+    # each rank "processes" its contiguous range; the per-frame result is a tag derived from the index
+    local = [(i, (i * 2654435761) & 0xFFFFFFFF) for i in range(lo, hi)]
+    merged = shard.gather_to_rank0(local, n_frames)
+    t = torch.tensor([float(hi - lo)])
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)              # the bench's max-over-ranks reduction
+    if rank == 0:
+        q.put((merged, t.item()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_world2_gloo_sharding_and_host_reorder():
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    n = 11
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, n, q)) for r in range(2)]
+    [p.start() for p in procs]
+    merged, mx = q.get(timeout=120)
+    [p.join(60) for p in procs]
+    assert [m[0] for m in merged] == list(range(n))
+    assert all(m[1] == (m[0] * 2654435761) & 0xFFFFFFFF for m in merged)
+    assert mx == 6.0
+    assert all(p.exitcode == 0 for p in procs)
+
+
+def test_interface_surface_matches_reference_callers():
+    """Names/signatures the reference's callers use."""
+    import inspect
+    from video_enhancer_proto_b200 import B200VideoEnhancer, GPUVideoEnhancer
+    assert GPUVideoEnhancer is B200VideoEnhancer
+    sig = inspect.signature(B200VideoEnhancer.__init__)
+    assert list(sig.parameters)[1:4] == ["device", "model_name", "scale"]       # basic_upscaler_fallback.py:45
+    assert list(inspect.signature(B200VideoEnhancer.process_video).parameters)[1:] == ["input_path", "output_path", "target_fps"]
+    assert inspect.signature(B200VideoEnhancer.process_video).parameters["target_fps"].default == 30   # app.py:388
+    for m in ("enhance_video", "restore_video", "get_model_info", "load_models", "enhance_frame_gpu",
+              "_enhance_frame_with_gpu", "_enhance_frame_cpu_fallback", "_process_frame_batch_gpu"):
+        assert callable(getattr(B200VideoEnhancer, m))
+    e = B200VideoEnhancer(device="cuda")
+    info = e.get_model_info()
+    assert info["scale"] == 2 and info["parameters"] == 750982
+    assert e.models_loaded is False
+    with pytest.raises(ValueError):
+        B200VideoEnhancer(scale=4)
+
+
+def test_synth_generators_are_deterministic():
+    from video_enhancer_proto_b200 import synth
+    a = synth.mixed_clip(6, 48, 64, seed=5)
+    b = synth.mixed_clip(6, 48, 64, seed=5)
+    assert all(np.array_equal(x, y) for x, y in zip(a, b))
+    assert all(f.shape == (48, 64, 3) and f.dtype == np.uint8 for f in a)
+    t = synth.tag_frame(a[0], 0x01020304)
+    assert synth.read_tag(t) == 0x01020304

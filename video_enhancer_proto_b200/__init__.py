@@ -1,0 +1,10 @@
+"""B200-native drop-in for the reference's per-frame 2x upscaler hot path (CNN + bicubic).
+
+Public surface: ``B200VideoEnhancer`` (mirror of ``GPUVideoEnhancer`` / the frame-handler
+protocol), ``shard`` (collective-free frame-range sharding) and ``synth`` (synthetic frames).
+"""
+from .upscaler import B200VideoEnhancer  # noqa: F401
+from . import shard, synth, weights  # noqa: F401
+
+GPUVideoEnhancer = B200VideoEnhancer       # reference class name (app.py:242)
+__all__ = ["B200VideoEnhancer", "GPUVideoEnhancer", "shard", "synth", "weights"]

@@ -1,0 +1,65 @@
+"""ctypes binding of libvex.so (include/vex.h).  Fails loudly: no CPU fallback exists."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libvex.so")
+
+VEX_MODE_BICUBIC = 0
+VEX_MODE_CNN = 1
+VEX_CNN_NUM_TENSORS = 30
+
+
+class VexCnnDesc(C.Structure):
+    _fields_ = [("c1", C.c_int), ("c2", C.c_int), ("c3", C.c_int), ("c4", C.c_int), ("up_ch", C.c_int),
+                ("bn_eps", C.c_float)]
+
+
+# name -> (restype, argtypes); must list every symbol include/vex.h declares (tests check this)
+SIGNATURES = {
+    "vex_abi_version": (C.c_int, []),
+    "vex_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
+    "vex_destroy": (C.c_int, [C.c_void_p]),
+    "vex_last_error": (C.c_char_p, [C.c_void_p]),
+    "vex_bicubic2x_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "vex_cnn_load_weights": (C.c_int, [C.c_void_p, C.POINTER(VexCnnDesc), C.POINTER(C.c_void_p), C.c_int]),
+    "vex_cnn2x_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "vex_cnn2x_f32_debug": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "vex_workspace_bytes": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)]),
+    "vex_host_alloc": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]),
+    "vex_host_free": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "vex_upscale_host": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "vex_kernel_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_ulonglong)]),
+    "vex_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """dlopen libvex.so (built in-tree by ``build.py`` / ``__graft_entry__.build``)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: run `python -m video_enhancer_proto_b200.build` (nvcc, sm_100a). "
+                "There is no CPU or PyTorch fallback for this path.")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+class VexError(RuntimeError):
+    pass
+
+
+def check(ctx, rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load().vex_last_error(ctx)
+        raise VexError(f"{what} failed ({rc}): {msg.decode() if msg else '?'}")

@@ -1,0 +1,67 @@
+// Internal declarations shared by the translation units of libvex.so (not part of the ABI).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cuda.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "../../include/vex.h"
+
+namespace vex {
+
+struct CnnPlan;  // cnn.cu
+
+}  // namespace vex
+
+struct vex_ctx {
+  int device = 0;
+  int sm_count = 148;
+  std::string err;
+  unsigned long long launches = 0;
+
+  // streaming path (vex_upscale_host): 2 slots, each with its own stream + device buffers
+  cudaStream_t slot_stream[2] = {nullptr, nullptr};
+  uint8_t* slot_in[2] = {nullptr, nullptr};
+  uint8_t* slot_out[2] = {nullptr, nullptr};
+  size_t slot_in_bytes = 0, slot_out_bytes = 0;
+
+  // CNN state
+  vex::CnnPlan* cnn = nullptr;
+
+  // debug knobs (vex_set_option)
+  int opt_desc_base_offset = 1;   // 1: smem-descriptor base_offset = (addr>>7)&7 (PTX ISA), 0: always 0
+  int opt_force_generic_bicubic = 0;
+};
+
+namespace vex {
+
+inline int fail(vex_ctx* ctx, int code, const std::string& msg) {
+  if (ctx) ctx->err = msg;
+  return code;
+}
+
+#define VEX_CUDA(ctx, call)                                                                  \
+  do {                                                                                       \
+    cudaError_t e__ = (call);                                                                \
+    if (e__ != cudaSuccess) {                                                                \
+      return ::vex::fail((ctx), VEX_ERR_CUDA,                                                \
+                         std::string(#call) + ": " + cudaGetErrorString(e__) + " (" +        \
+                             __FILE__ + ":" + std::to_string(__LINE__) + ")");               \
+    }                                                                                        \
+  } while (0)
+
+// bicubic.cu
+int launch_bicubic2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w,
+                     int round_mode, cudaStream_t s);
+
+// cnn.cu
+int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const* tensors, int n);
+int cnn_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f32, int tap,
+                int n, int h, int w, int in_bgr, int out_bgr, cudaStream_t s);
+size_t cnn_workspace_bytes(const vex_ctx* ctx, int n, int h, int w);
+void cnn_destroy(vex_ctx* ctx);
+
+}  // namespace vex

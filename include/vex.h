@@ -12,7 +12,8 @@
  *     `enhancer`, app.py:624, and max_concurrent_tasks=1, agents/enhancer/video_enhancer_sota.py:72);
  *   - frame buffers are caller-owned, packed uint8 HWC, no row padding, frames contiguous;
  *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream); device-pointer
- *     entry points are asynchronous on it;
+ *     entry points are asynchronous on it; CNN calls on one ctx share its activation workspace and
+ *     must therefore be stream-ordered with respect to each other;
  *   - there is NO CPU fallback: without a usable sm_100 device vex_create fails.
  */
 #ifndef VEX_H_
@@ -62,7 +63,7 @@ int vex_bicubic2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc,
 /* Channel plan of the AdvancedUpscaler family (app.py:269-301):
  *   conv1 3->c1, conv2 c1->c2 (+skip, needs c1==c2), conv3 c2->c3, conv4 c3->c4, conv5 c4->3,
  *   upconv1 ConvT 3->up_ch k4 s2 p1, upconv2 ConvT up_ch->3 k3 s1 p1.
- * The reference is {128,128,256,128,64}.  All widths must be multiples of 64, <= 256; up_ch 64. */
+ * The reference is {128,128,256,128,64}.  Widths must be multiples of 128 in [128, 512]; up_ch 64. */
 typedef struct vex_cnn_desc {
   int c1, c2, c3, c4, up_ch;
   float bn_eps;              /* 1e-5 (nn.BatchNorm2d default, app.py:284-287) */
@@ -92,6 +93,13 @@ int vex_cnn2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc,
 int vex_cnn2x_f32_debug(vex_ctx* ctx, const uint8_t* in_hwc, float* out_nchw,
                         int n, int h, int w, int in_bgr, int tap, void* stream);
 
+/* Per-layer device time (ms, CUDA events on the caller's stream) of the most recent vex_cnn2x_u8 /
+ * vex_cnn2x_f32_debug(tap 0) call made while option "profile" is 1:
+ * ms7 = {conv1, conv2, conv3, conv4, conv5, upconv1, upconv2}; sub-batches are summed.  Synchronises on
+ * the last event.  (The reference has no per-layer timing; its PerformanceTracker,
+ * utils/performance_monitor.py:178, only wraps whole videos.) */
+int vex_cnn_profile_ms(vex_ctx* ctx, float* ms7);
+
 /* Bytes of device workspace the ctx holds (grows on demand) for a batch of this shape. */
 int vex_workspace_bytes(const vex_ctx* ctx, int n, int h, int w, size_t* out);
 
@@ -117,7 +125,9 @@ int vex_upscale_host(vex_ctx* ctx, int mode, const uint8_t* in_host, uint8_t* ou
 /* Counters for bench.py's `gpu_launches`: kernels launched by this ctx since creation. */
 int vex_kernel_launches(const vex_ctx* ctx, unsigned long long* out);
 
-/* Debug knobs for bring-up (kernel variant selection); returns previous value or <0. */
+/* Knobs: "profile" (0/1), "conv3_bn" (128/256: Cout block of conv3), "ws_budget_mb" (activation
+ * workspace cap; larger batches run as sub-batches), "desc_base_offset", "force_generic_bicubic"
+ * (bring-up).  Returns the previous value, or a negative vex_status. */
 int vex_set_option(vex_ctx* ctx, const char* name, int value);
 
 #ifdef __cplusplus

@@ -1,0 +1,221 @@
+"""GPU parity: the CNN CUDA path (through the C ABI) against the oracle (reference torch-CPU fp32 path).
+
+Bars (BASELINE.json north_star), written here as constants:
+  * fp32 [0,1] output:  max-abs error <= 2/255  and  PSNR >= 50 dB  against the fp32 reference;
+  * uint8 output: |diff| <= 2 LSB (truncating cast, so bf16 noise can flip one LSB; 2/255 budget).
+Per-layer taps (x1..x5, up) are compared too so that a permuted tap / channel cannot hide behind the small
+dynamic range of the Xavier-initialised network ("hard parts").
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import upscaler_ref as O
+from oracle.make_golden import case_inputs
+from video_enhancer_proto_b200 import B200VideoEnhancer, synth
+
+pytestmark = pytest.mark.gpu
+
+MAX_ABS = 2.0 / 255.0
+MIN_PSNR = 50.0
+# The bar above is stated for random-init weights of the architecture (seed0/seed1 here).  The oracle's
+# "stress" weights multiply the tail gains by 4*3*3 = 36 so that the output spans [0,1] and hits both clamps;
+# they amplify the bf16 rounding of x1..x4 by the same factor (CPU emulation of the rounding points:
+# max-abs 2.9e-2, PSNR 50.2 dB, tests/test_layer_algebra.py), so they get their own, looser, bound.
+STRESS_MAX_ABS = 0.05
+STRESS_MIN_PSNR = 45.0
+STRESS_U8 = 13
+TAP_NAMES = {1: "x1", 2: "x2", 3: "x3", 4: "x4", 5: "x5", 6: "up", 0: "out"}
+# relative per-layer tolerance (bf16 operands/activations, fp32 accumulate): max-abs error / max |ref|
+TAP_REL_TOL = {"x1": 6e-3, "x2": 1e-2, "x3": 1.5e-2, "x4": 2e-2, "x5": 3e-2, "up": 2e-2}
+
+
+@pytest.fixture(scope="module")
+def models():
+    return {"seed0": O.make_model(0), "seed1": O.make_model(1), "stress": O.make_stress_model()}
+
+
+@pytest.fixture(scope="module")
+def enhancers(models):
+    out = {}
+    for k, m in models.items():
+        e = B200VideoEnhancer(device="cuda:0", state_dict=O.export_state(m))
+        assert e.load_models()
+        out[k] = e
+    yield out
+    for e in out.values():
+        e.close()
+
+
+def dev(frames):
+    return torch.from_numpy(np.stack(frames)).cuda()
+
+
+def check_f32(got, want, what):
+    stress = "stress" in what
+    err = float(np.abs(got - want).max())
+    p = O.psnr(got, want)
+    assert err <= (STRESS_MAX_ABS if stress else MAX_ABS), f"{what}: max-abs {err:.3e}"
+    assert p >= (STRESS_MIN_PSNR if stress else MIN_PSNR), f"{what}: PSNR {p:.1f} dB"
+    return err, p
+
+
+def u8_tol(key):
+    return STRESS_U8 if "stress" in key else 2
+
+
+@pytest.mark.parametrize("key", ["seed0", "seed1", "stress"])
+@pytest.mark.parametrize("h,w", [(37, 53), (64, 96), (16, 30), (17, 31), (1, 1), (130, 70)])
+def test_layer_taps_and_output(enhancers, models, key, h, w):
+    rng = np.random.default_rng(100 + h)
+    frames = [synth.random_frame(h, w, rng), synth.edges_frame(h, w, rng), synth.checker_frame(h, w)]
+    taps = {}
+    O.ref_cnn_batch_f32(models[key], frames, taps)
+    enh = enhancers[key]
+    d = dev(frames)
+    for tap in (1, 2, 3, 4, 5, 6):
+        name = TAP_NAMES[tap]
+        got = enh.cnn_debug_f32(d, tap=tap).cpu().numpy()
+        want = taps[name].numpy()
+        assert got.shape == want.shape
+        scale = max(float(np.abs(want).max()), 1e-6)
+        err = float(np.abs(got - want).max()) / scale
+        assert err <= TAP_REL_TOL[name], f"{key} {h}x{w} {name}: rel err {err:.3e}"
+    got = enh.cnn_debug_f32(d, tap=0).cpu().numpy()
+    check_f32(got, taps["out"].numpy(), f"{key} {h}x{w} out")
+    u8 = enh.upscale_device(d, mode="cnn").cpu().numpy()
+    for i, f in enumerate(frames):
+        ref = O.ref_cnn_frame(models[key], f)                      # app.py:322-352
+        assert np.abs(u8[i].astype(int) - ref.astype(int)).max() <= u8_tol(key), (key, h, w, i)
+
+
+def test_stress_model_spans_range(models):
+    rng = np.random.default_rng(7)
+    ref = O.ref_cnn_frame(models["stress"], synth.random_frame(64, 96, rng))
+    assert ref.min() == 0 and ref.max() == 255          # both clamps exercised (weak-signal guard)
+
+
+def test_golden_fixtures(enhancers, golden):
+    """Outputs minted by the reference's own code (oracle/make_golden.py), committed under tests/golden/."""
+    cases, small = golden
+    n = 0
+    for key in small.files:
+        if not (key.startswith("cnn_") and key.endswith("__in")):
+            continue
+        enh = enhancers.get(key.split("_")[1])         # cnn_<seed0|seed1|stress>_<h>x<w>_<input>__in
+        if enh is None:
+            continue
+        frame = small[key]
+        want_f32 = small[key.replace("__in", "__out_f32")]
+        want_u8 = small[key.replace("__in", "__out_u8")]
+        d = dev([frame])
+        got = enh.cnn_debug_f32(d, tap=0).cpu().numpy()[0]
+        check_f32(got, want_f32, key)
+        u8 = enh.upscale_device(d, mode="cnn").cpu().numpy()[0]
+        assert np.abs(u8.astype(int) - want_u8.astype(int)).max() <= u8_tol(key), key
+        n += 1
+    assert n >= 5
+
+
+def test_colour_order_flags(enhancers, models):
+    """RGB in / BGR out of the batch path (app.py:469,550) is done inside the kernels."""
+    rng = np.random.default_rng(11)
+    frames = [synth.random_frame(40, 64, rng), synth.demo_frame(2, size=(64, 40), rng=rng, bgr=False)]
+    enh = enhancers["stress"]
+    want = O.ref_cnn_batch(models["stress"], frames, out_bgr=True)
+    got = enh._process_frame_batch_gpu(frames)                      # host-buffer path, RGB in -> BGR out
+    for a, b in zip(got, want):
+        assert a.shape == b.shape and np.abs(a.astype(int) - b.astype(int)).max() <= STRESS_U8
+    # BGR buffers in, BGR out == reversing channels on both sides of the RGB network
+    bgr = [f[:, :, ::-1].copy() for f in frames]
+    o = enh.upscale_device(dev(bgr), mode="cnn", in_bgr=True, out_bgr=True).cpu().numpy()
+    for i in range(len(frames)):
+        assert np.abs(o[i].astype(int) - want[i].astype(int)).max() <= STRESS_U8
+
+
+def test_single_frame_api_and_tensor_input(enhancers, models):
+    rng = np.random.default_rng(12)
+    f = synth.edges_frame(48, 80, rng)
+    enh = enhancers["stress"]
+    ref = O.ref_cnn_frame(models["stress"], f)
+    out = enh.enhance_frame_gpu(f)                                   # app.py:314
+    assert out.shape == (96, 160, 3) and out.dtype == np.uint8
+    assert np.abs(out.astype(int) - ref.astype(int)).max() <= STRESS_U8
+    t = torch.from_numpy(f).permute(2, 0, 1).unsqueeze(0).float() / 255.0      # app.py:337-338 tensor form
+    out2 = enh.enhance_frame_gpu(t)
+    assert np.array_equal(out, out2)
+
+
+def test_conv3_block_variants_agree(enhancers):
+    rng = np.random.default_rng(13)
+    d = dev([synth.random_frame(70, 95, rng)])
+    enh = enhancers["stress"]
+    a = enh.cnn_debug_f32(d, tap=3).cpu().numpy()
+    prev = enh.set_option("conv3_bn", 128)
+    try:
+        b = enh.cnn_debug_f32(d, tap=3).cpu().numpy()
+    finally:
+        enh.set_option("conv3_bn", prev)
+    # same bf16 products and K order per output; allow one bf16 ulp for accumulation-order differences
+    assert np.abs(a - b).max() <= 2.0 ** -7 * np.abs(a).max()
+
+
+def test_sub_batching_matches(enhancers):
+    rng = np.random.default_rng(14)
+    frames = [synth.random_frame(33, 47, rng) for _ in range(5)]
+    enh = enhancers["seed0"]
+    a = enh.upscale_device(dev(frames), mode="cnn").cpu().numpy()
+    prev = enh.set_option("ws_budget_mb", 1)            # forces one frame per sub-batch
+    try:
+        b = enh.upscale_device(dev(frames), mode="cnn").cpu().numpy()
+    finally:
+        enh.set_option("ws_budget_mb", prev)
+    assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("h,w", [(360, 480), (480, 640)])
+def test_config0_demo_clip_shapes(enhancers, models, h, w):
+    """BASELINE configs[0]: the 480p demo-clip shapes (3 of the 30 frames here; bench covers throughput)."""
+    rng = np.random.default_rng(0)
+    frames = [synth.demo_frame(i, size=(w, h), rng=rng, bgr=False) for i in (0, 8, 29)]
+    for key in ("seed0", "stress"):
+        want = O.ref_cnn_batch_f32(models[key], frames).numpy()
+        got = enhancers[key].cnn_debug_f32(dev(frames), tap=0).cpu().numpy()
+        check_f32(got, want, f"{key} {h}x{w}")
+
+
+def test_full_size_1080p(enhancers, models):
+    """BASELINE configs[2] shape: 1080p frames against the fp32 reference (the CPU side takes ~20 s each)."""
+    rng = np.random.default_rng(1234)
+    f = synth.edges_frame(1080, 1920, rng)
+    # the north_star bar, on random-init weights
+    want = O.ref_cnn_batch_f32(models["seed0"], [f]).numpy()
+    got = enhancers["seed0"].cnn_debug_f32(dev([f]), tap=0).cpu().numpy()
+    check_f32(got, want, "seed0 1080p")
+    u8 = enhancers["seed0"].upscale_device(dev([f]), mode="cnn").cpu().numpy()[0]
+    assert np.abs(u8.astype(int) - O.quantize_u8(torch.from_numpy(want[0])).astype(int)).max() <= 2
+    # full-range weights
+    want = O.ref_cnn_batch_f32(models["stress"], [f]).numpy()
+    got = enhancers["stress"].cnn_debug_f32(dev([f]), tap=0).cpu().numpy()
+    check_f32(got, want, "stress 1080p")
+    u8 = enhancers["stress"].upscale_device(dev([f]), mode="cnn").cpu().numpy()[0]
+    assert u8.min() == 0 and u8.max() == 255
+    # size-independent property at full size: translation equivariance away from the borders —
+    # shifting the input by (16 rows, 30 cols) = one tile shifts the output by (32, 60)
+    g = np.roll(f, (16, 30), axis=(0, 1))
+    u8s = enhancers["stress"].upscale_device(dev([g]), mode="cnn").cpu().numpy()[0]
+    a = u8[64:-64, 128:-128]
+    b = u8s[64 + 32:2160 - 64 + 32, 128 + 60:3840 - 128 + 60]
+    assert np.array_equal(a, b)
+
+
+def test_batch8_1080p_frames_independent(enhancers):
+    """configs[2] batch of 8: every frame of a batch equals the same frame run alone (bit-exact)."""
+    rng = np.random.default_rng(5)
+    pool = [synth.random_frame(1080, 1920, rng), synth.edges_frame(1080, 1920, rng)]
+    frames = [pool[i % 2] for i in range(8)]
+    enh = enhancers["seed0"]
+    out8 = enh.upscale_device(dev(frames), mode="cnn").cpu().numpy()
+    solo = enh.upscale_device(dev(pool), mode="cnn").cpu().numpy()
+    for i in range(8):
+        assert np.array_equal(out8[i], solo[i % 2]), i

@@ -1,0 +1,93 @@
+#!/usr/bin/env python
+"""Bring-up diagnostics for the tcgen05 conv path (run on the GPU box; writes gpurun_out/cnn_diag.json).
+
+Each probe runs in its own subprocess with a timeout, so a trap / sticky CUDA error in one variant cannot
+poison the next.  Probes:
+  taps     per-layer parity (x1..x5, up, out) against the oracle's fp32 taps, for a knob setting
+  onehot   conv2 replaced by a one-hot (tap, channel-rotation) kernel: isolates which 3x3 tap / K chunk is
+           mis-addressed when the shared-memory descriptor arithmetic is wrong
+TEST INFRASTRUCTURE: imports oracle/ as the checker only.
+"""
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def child(kind, arg):
+    import numpy as np
+    import torch
+    from oracle import upscaler_ref as O
+    from video_enhancer_proto_b200 import B200VideoEnhancer, synth
+
+    opts = dict(kv.split("=") for kv in arg.split(",") if kv)
+    h, w = int(opts.pop("h", 37)), int(opts.pop("w", 53))
+    seed = int(opts.pop("seed", 0))
+    model = O.make_stress_model() if opts.pop("stress", "0") == "1" else O.make_model(seed)
+    res = {}
+    if kind == "onehot":
+        t, rot = int(opts.pop("tap")), int(opts.pop("rot", 0))
+        with torch.no_grad():
+            wgt = torch.zeros_like(model.conv2.weight)
+            for co in range(wgt.shape[0]):
+                wgt[co, (co + rot) % wgt.shape[1], t // 3, t % 3] = 1.0
+            model.conv2.weight.copy_(wgt)
+    rng = np.random.default_rng(5)
+    frames = [synth.random_frame(h, w, rng), synth.edges_frame(h, w, rng)]
+    enh = B200VideoEnhancer(device="cuda:0", state_dict=O.export_state(model))
+    enh._ensure_ctx()
+    for k, v in opts.items():
+        enh.set_option(k, int(v))
+    dev = torch.from_numpy(np.stack(frames)).cuda()
+    taps = {}
+    O.ref_cnn_batch_f32(model, frames, taps)
+    names = {1: "x1", 2: "x2", 3: "x3", 4: "x4", 5: "x5", 6: "up", 0: "out"}
+    for tap in ((1, 2) if kind == "onehot" else (1, 2, 3, 4, 5, 6, 0)):
+        got = enh.cnn_debug_f32(dev, tap=tap).cpu().numpy()
+        want = taps[names[tap]].numpy()
+        err = np.abs(got - want)
+        res[names[tap]] = {"max_abs": float(err.max()), "ref_max": float(np.abs(want).max()),
+                           "mean_abs": float(err.mean()), "nan": bool(np.isnan(got).any())}
+    if kind == "taps":
+        u8 = enh.upscale_device(dev, mode="cnn").cpu().numpy()
+        ref8 = np.stack([O.ref_cnn_frame(model, f) for f in frames])
+        res["u8_maxdiff"] = int(np.abs(u8.astype(int) - ref8.astype(int)).max())
+        res["u8_range"] = [int(ref8.min()), int(ref8.max())]
+    print("RESULT " + json.dumps(res))
+
+
+def main():
+    if len(sys.argv) >= 3 and sys.argv[1] in ("taps", "onehot"):
+        return child(sys.argv[1], sys.argv[2])
+    probes = []
+    for bo in (1, 0):
+        probes.append(("taps", f"desc_base_offset={bo}"))
+        probes.append(("taps", f"desc_base_offset={bo},conv3_bn=128"))
+    probes.append(("taps", "desc_base_offset=1,stress=1,h=64,w=96"))
+    probes.append(("taps", "desc_base_offset=1,h=130,w=70"))
+    for bo in (1, 0):
+        for t in range(9):
+            probes.append(("onehot", f"desc_base_offset={bo},tap={t}"))
+        probes.append(("onehot", f"desc_base_offset={bo},tap=4,rot=64"))
+        probes.append(("onehot", f"desc_base_offset={bo},tap=4,rot=17"))
+    out = {}
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    for kind, arg in probes:
+        key = f"{kind}:{arg}"
+        try:
+            r = subprocess.run([sys.executable, os.path.abspath(__file__), kind, arg], capture_output=True, text=True,
+                               timeout=240)
+            line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")]
+            out[key] = json.loads(line[-1][7:]) if line else {"error": (r.stderr or r.stdout)[-600:], "rc": r.returncode}
+        except subprocess.TimeoutExpired:
+            out[key] = {"error": "timeout"}
+        print(key, json.dumps(out[key]), flush=True)
+        with open(os.path.join(ROOT, "gpurun_out", "cnn_diag.json"), "w") as f:
+            json.dump(out, f, indent=1)
+
+
+if __name__ == "__main__":
+    main()

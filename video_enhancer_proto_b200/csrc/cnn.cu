@@ -1,12 +1,430 @@
-// placeholder until the tcgen05 path lands (replaced in the next commit)
+// AdvancedUpscaler (reference app.py:269-301) on sm_100a: weight folding/packing, workspace, layer launches.
+//
+//   u8 HWC --conv1_u8--> x1 --conv_tc(+x1)--> x2 --conv_tc--> x3 --conv_tc--> x4 --conv3x3_to3--> x5
+//          --upconv1--> up (2H x 2W x up_ch) --conv3x3_to3<clamp,u8>--> u8 HWC (2H, 2W)
+//
+// Activations x1..x4 and `up` are NHWC bf16 in the ctx workspace; x5 is fp32.  conv2..conv4 (97.8 % of the
+// FLOPs) run on tcgen05 (conv_tc.cuh); the thin layers are fp32 CUDA-core kernels.
+#include <algorithm>
+#include <math.h>
+#include <string.h>
+
+#include <cuda_bf16.h>
+
+#include "cnn_small.cuh"
+#include "conv_tc.cuh"
 #include "vex_internal.cuh"
+
 namespace vex {
-int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc*, const float* const*, int) {
-  return fail(ctx, VEX_ERR_UNSUPPORTED, "cnn path not built yet");
+
+struct TcLayer {
+  int cin = 0, cout = 0, bn = 128;       // bn = Cout block per CTA (TMEM accumulator width)
+  uint8_t* wpack = nullptr;              // device: [cout/bn][cin/64][9] swizzled slices
+  float* bias = nullptr;                 // device: [cout]
+  std::vector<float> w_folded;           // host fp32 [cout][cin][3][3] * bn scale (kept for re-packing)
+};
+
+struct CnnPlan {
+  vex_cnn_desc arch{};
+  // thin layers (device, fp32)
+  float *w1g = nullptr, *b1 = nullptr;       // conv1: [27][c1], [c1]
+  float *w5g = nullptr, *b5 = nullptr;       // conv5: [c4/64][9][64][4], [3]
+  float *wu1 = nullptr, *bu1 = nullptr;      // upconv1: [4][12][up], [up]
+  float *wu2 = nullptr, *bu2 = nullptr;      // upconv2: [up/64][9][64][4], [3]
+  TcLayer tc[3];                             // conv2, conv3, conv4
+  // workspace
+  uint8_t* ws = nullptr;
+  size_t ws_bytes = 0;
+  void* encode = nullptr;                    // cuTensorMapEncodeTiled, resolved through the runtime
+  std::vector<cudaEvent_t> prof;             // option "profile": 8 events per sub-batch of the last forward
+  std::vector<cudaEvent_t> prof_pool;
+};
+
+namespace {
+
+typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                             const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                             CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+uint16_t f32_to_bf16_rne(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return 0x7fc0;      // NaN
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
 }
-int cnn_forward(vex_ctx* ctx, const uint8_t*, uint8_t*, float*, int, int, int, int, int, int, cudaStream_t) {
-  return fail(ctx, VEX_ERR_NO_WEIGHTS, "vex_cnn_load_weights has not been called");
+
+template <typename T>
+int upload(vex_ctx* ctx, T** dst, const void* src, size_t bytes) {
+  if (*dst) cudaFree(*dst);
+  *dst = nullptr;
+  VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(dst), bytes));
+  VEX_CUDA(ctx, cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice));
+  return VEX_OK;
 }
-size_t cnn_workspace_bytes(const vex_ctx*, int, int, int) { return 0; }
-void cnn_destroy(vex_ctx*) {}
+
+// [cout/bn][cin/64][9] slices; slice = bn rows x 64 bf16 (128 B), stored as the SWIZZLE_128B image of a
+// K-major operand: 16-byte chunk j of row r lives at chunk position j ^ (r & 7).
+int pack_tc(vex_ctx* ctx, TcLayer& L) {
+  const int nb = L.cout / L.bn, nc = L.cin / 64;
+  std::vector<uint16_t> img((size_t)L.cout * L.cin * 9);
+  for (int b = 0; b < nb; ++b)
+    for (int c = 0; c < nc; ++c)
+      for (int t = 0; t < 9; ++t) {
+        uint16_t* slice = img.data() + ((size_t)(b * nc + c) * 9 + t) * L.bn * 64;
+        for (int r = 0; r < L.bn; ++r)
+          for (int k = 0; k < 64; ++k) {
+            const int co = b * L.bn + r, ci = c * 64 + k;
+            const float v = L.w_folded[((size_t)co * L.cin + ci) * 9 + t];
+            const int chunk = (k >> 3) ^ (r & 7);
+            slice[(size_t)r * 64 + chunk * 8 + (k & 7)] = f32_to_bf16_rne(v);
+          }
+      }
+  return upload(ctx, &L.wpack, img.data(), img.size() * 2);
+}
+
+int make_amap(vex_ctx* ctx, CUtensorMap* map, const void* base, int n, int H, int W, int C, int box_rows) {
+  CnnPlan* P = ctx->cnn;
+  const cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)n};
+  const cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  const cuuint32_t box[4] = {64, (cuuint32_t)convtc::PITCH, (cuuint32_t)box_rows, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = reinterpret_cast<EncodeFn>(P->encode)(
+      map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(ctx, VEX_ERR_CUDA, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+  return VEX_OK;
+}
+
+template <int BN>
+int launch_tc(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfloat16* out,
+              const __nv_bfloat16* skip, int n, int H, int W, cudaStream_t s) {
+  using C = convtc::Cfg<BN>;
+  CUtensorMap amap;
+  int rc = make_amap(ctx, &amap, in, n, H, W, L.cin, C::ROWS + 2);
+  if (rc) return rc;
+  convtc::Params p;
+  p.wpack = L.wpack; p.bias = L.bias; p.out = out; p.skip = skip;
+  p.H = H; p.W = W; p.NC = L.cin / 64; p.Cout = L.cout;
+  p.tiles_x = (W + convtc::TILE_W - 1) / convtc::TILE_W;
+  p.tiles_y = (H + C::ROWS - 1) / C::ROWS;
+  p.n_img = n; p.relu = 1; p.desc_base_offset = ctx->opt_desc_base_offset;
+  const long long total = (long long)p.tiles_x * p.tiles_y * n;
+  if (total > 0x7fffffffLL) return fail(ctx, VEX_ERR_INVALID, "conv_tc: too many tiles");
+  const unsigned abit = BN == 256 ? 2u : 1u;
+  if (!(ctx->attr_mask & abit)) {            // per device, hence per ctx
+    VEX_CUDA(ctx, cudaFuncSetAttribute(convtc::conv3x3_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       C::SMEM));
+    ctx->attr_mask |= abit;
+  }
+  dim3 grid((unsigned)std::min<long long>(total, ctx->sm_count), L.cout / BN);
+  convtc::conv3x3_tc_kernel<BN><<<grid, convtc::NTHREADS, C::SMEM, s>>>(amap, p);
+  ctx->launches++;
+  VEX_CUDA(ctx, cudaGetLastError());
+  return VEX_OK;
+}
+
+int run_tc(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfloat16* out,
+           const __nv_bfloat16* skip, int n, int H, int W, cudaStream_t s) {
+  return L.bn == 256 ? launch_tc<256>(ctx, L, in, out, skip, n, H, W, s)
+                     : launch_tc<128>(ctx, L, in, out, skip, n, H, W, s);
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct Layout {
+  size_t a, b, c, x5, total;     // offsets: bufA (x1/x4), bufB (x2), bufC (x3/up), x5
+};
+Layout ws_layout(const vex_cnn_desc& d, size_t npix) {
+  Layout L;
+  size_t off = 0;
+  L.a = off; off += align_up(npix * std::max(d.c1, d.c4) * 2, 1024);
+  L.b = off; off += align_up(npix * d.c2 * 2, 1024);
+  L.c = off; off += align_up(npix * std::max(d.c3, 4 * d.up_ch) * 2, 1024);
+  L.x5 = off; off += align_up(npix * 16, 1024);
+  L.total = off;
+  return L;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------- weights
+
+int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const* t, int n_tensors) {
+  if (!arch || !t || n_tensors != VEX_CNN_NUM_TENSORS)
+    return fail(ctx, VEX_ERR_INVALID, "vex_cnn_load_weights: need 30 tensors in state_dict order");
+  for (int i = 0; i < n_tensors; ++i)
+    if (!t[i]) return fail(ctx, VEX_ERR_INVALID, "vex_cnn_load_weights: null tensor");
+  const int c1 = arch->c1, c2 = arch->c2, c3 = arch->c3, c4 = arch->c4, up = arch->up_ch;
+  auto okw = [](int c) { return c >= 128 && c <= 512 && c % 128 == 0; };
+  if (!okw(c1) || !okw(c2) || !okw(c3) || !okw(c4) || c1 != c2 || up != 64)
+    return fail(ctx, VEX_ERR_UNSUPPORTED,
+                "vex_cnn_load_weights: widths must be multiples of 128 in [128,512], c1 == c2 (skip), up_ch == 64");
+  if (!ctx->cnn) ctx->cnn = new CnnPlan();
+  CnnPlan* P = ctx->cnn;
+  P->arch = *arch;
+  if (!P->encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    VEX_CUDA(ctx, cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q));
+    if (!fn || q != cudaDriverEntryPointSuccess)
+      return fail(ctx, VEX_ERR_UNSUPPORTED, "cuTensorMapEncodeTiled not available in this driver");
+    P->encode = fn;
+  }
+  // state_dict order (include/vex.h): conv1..5 {w,b}, upconv1 {w,b}, upconv2 {w,b}, bn1..4 {w,b,mean,var}
+  const float *cw[5], *cb[5];
+  for (int i = 0; i < 5; ++i) { cw[i] = t[2 * i]; cb[i] = t[2 * i + 1]; }
+  const float *u1w = t[10], *u1b = t[11], *u2w = t[12], *u2b = t[13];
+  const int cin[5] = {3, c1, c2, c3, c4}, cout[5] = {c1, c2, c3, c4, 3};
+  // eval-mode BN fold (app.py:284-287, 331): y = (conv + b - mean) * g / sqrt(var + eps) + beta
+  std::vector<float> scale[4], shift[4];
+  for (int i = 0; i < 4; ++i) {
+    const float *g = t[14 + 4 * i], *be = t[15 + 4 * i], *mu = t[16 + 4 * i], *var = t[17 + 4 * i];
+    scale[i].resize(cout[i]); shift[i].resize(cout[i]);
+    for (int c = 0; c < cout[i]; ++c) {
+      const float s = g[c] / sqrtf(var[c] + arch->bn_eps);
+      scale[i][c] = s;
+      shift[i][c] = (cb[i][c] - mu[c]) * s + be[c];
+    }
+  }
+  int rc;
+  {  // conv1: [27][c1], k = (ky*3+kx)*3+ci; folds BN scale and the 1/255 of app.py:535
+    std::vector<float> w((size_t)27 * c1);
+    for (int co = 0; co < c1; ++co)
+      for (int ci = 0; ci < 3; ++ci)
+        for (int k = 0; k < 9; ++k)
+          w[(size_t)(k * 3 + ci) * c1 + co] = cw[0][((size_t)co * 3 + ci) * 9 + k] * scale[0][co] * (1.0f / 255.0f);
+    if ((rc = upload(ctx, &P->w1g, w.data(), w.size() * 4))) return rc;
+    if ((rc = upload(ctx, &P->b1, shift[0].data(), (size_t)c1 * 4))) return rc;
+  }
+  for (int l = 0; l < 3; ++l) {  // conv2..conv4 on tensor cores
+    TcLayer& L = P->tc[l];
+    L.cin = cin[l + 1]; L.cout = cout[l + 1];
+    const int want = (l == 1) ? ctx->opt_conv3_bn : 128;
+    L.bn = (want == 256 && L.cout % 256 == 0) ? 256 : 128;
+    L.w_folded.resize((size_t)L.cout * L.cin * 9);
+    for (int co = 0; co < L.cout; ++co)
+      for (size_t j = 0; j < (size_t)L.cin * 9; ++j)
+        L.w_folded[(size_t)co * L.cin * 9 + j] = cw[l + 1][(size_t)co * L.cin * 9 + j] * scale[l + 1][co];
+    if ((rc = pack_tc(ctx, L))) return rc;
+    if ((rc = upload(ctx, &L.bias, shift[l + 1].data(), (size_t)L.cout * 4))) return rc;
+  }
+  {  // conv5: [c4/64][9][64][4]
+    std::vector<float> w((size_t)c4 * 9 * 4, 0.f);
+    for (int co = 0; co < 3; ++co)
+      for (int ci = 0; ci < c4; ++ci)
+        for (int k = 0; k < 9; ++k)
+          w[(((size_t)(ci / 64) * 9 + k) * 64 + (ci % 64)) * 4 + co] = cw[4][((size_t)co * c4 + ci) * 9 + k];
+    if ((rc = upload(ctx, &P->w5g, w.data(), w.size() * 4))) return rc;
+    if ((rc = upload(ctx, &P->b5, cb[4], 12))) return rc;
+  }
+  {  // upconv1 (ConvTranspose2d weight [ci=3][co=up][4][4]) -> [phase][(a*2+b)*3+ci][co]
+     // (ky, dy) per phase bit p and tap index a:  p=0: {(1,0), (3,-1)}   p=1: {(0,+1), (2,0)}
+    const int kys[2][2] = {{1, 3}, {0, 2}};
+    std::vector<float> w((size_t)48 * up);
+    for (int py = 0; py < 2; ++py)
+      for (int px = 0; px < 2; ++px)
+        for (int a = 0; a < 2; ++a)
+          for (int b = 0; b < 2; ++b)
+            for (int ci = 0; ci < 3; ++ci)
+              for (int co = 0; co < up; ++co)
+                w[((size_t)(py * 2 + px) * 12 + (a * 2 + b) * 3 + ci) * up + co] =
+                    u1w[(((size_t)ci * up + co) * 4 + kys[py][a]) * 4 + kys[px][b]];
+    if ((rc = upload(ctx, &P->wu1, w.data(), w.size() * 4))) return rc;
+    if ((rc = upload(ctx, &P->bu1, u1b, (size_t)up * 4))) return rc;
+  }
+  {  // upconv2 (ConvTranspose2d weight [ci=up][co=3][3][3], s1 p1) == conv3x3 with the kernel flipped:
+     // tap (ky,kx) of the equivalent conv uses w[ci][co][2-ky][2-kx]
+    std::vector<float> w((size_t)up * 9 * 4, 0.f);
+    for (int co = 0; co < 3; ++co)
+      for (int ci = 0; ci < up; ++ci)
+        for (int ky = 0; ky < 3; ++ky)
+          for (int kx = 0; kx < 3; ++kx)
+            w[(((size_t)(ci / 64) * 9 + ky * 3 + kx) * 64 + (ci % 64)) * 4 + co] =
+                u2w[(((size_t)ci * 3 + co) * 3 + (2 - ky)) * 3 + (2 - kx)];
+    if ((rc = upload(ctx, &P->wu2, w.data(), w.size() * 4))) return rc;
+    if ((rc = upload(ctx, &P->bu2, u2b, 12))) return rc;
+  }
+  return VEX_OK;
+}
+
+// ------------------------------------------------------------------------------------------- forward
+
+size_t cnn_workspace_bytes(const vex_ctx* ctx, int n, int h, int w) {
+  if (!ctx->cnn) return 0;
+  return ws_layout(ctx->cnn->arch, (size_t)n * h * w).total;
+}
+
+static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f32, int tap, int n, int H,
+                         int W, int in_bgr, int out_bgr, cudaStream_t s) {
+  CnnPlan* P = ctx->cnn;
+  const vex_cnn_desc& d = P->arch;
+  const size_t npix = (size_t)n * H * W;
+  const Layout L = ws_layout(d, npix);
+  if (L.total > P->ws_bytes) {
+    VEX_CUDA(ctx, cudaDeviceSynchronize());
+    if (P->ws) cudaFree(P->ws);
+    P->ws = nullptr; P->ws_bytes = 0;
+    VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&P->ws), L.total));
+    P->ws_bytes = L.total;
+  }
+  __nv_bfloat16* x1 = reinterpret_cast<__nv_bfloat16*>(P->ws + L.a);
+  __nv_bfloat16* x2 = reinterpret_cast<__nv_bfloat16*>(P->ws + L.b);
+  __nv_bfloat16* x3 = reinterpret_cast<__nv_bfloat16*>(P->ws + L.c);
+  __nv_bfloat16* x4 = x1;
+  __nv_bfloat16* up = x3;
+  float* x5 = reinterpret_cast<float*>(P->ws + L.x5);
+  const int HW = H * W;
+  auto tap_bf16 = [&](const __nv_bfloat16* x, int C) -> int {
+    const size_t items = npix * (C / 8);
+    small::nhwc_bf16_to_nchw_f32_kernel<<<(unsigned)((items + 255) / 256), 256, 0, s>>>(x, out_f32, npix, HW, C);
+    ctx->launches++;
+    VEX_CUDA(ctx, cudaGetLastError());
+    return VEX_OK;
+  };
+  auto mark = [&]() {                      // layer boundary for vex_cnn_profile_ms
+    if (!ctx->opt_profile) return;
+    cudaEvent_t e;
+    if (!P->prof_pool.empty()) { e = P->prof_pool.back(); P->prof_pool.pop_back(); }
+    else if (cudaEventCreate(&e) != cudaSuccess) return;
+    cudaEventRecord(e, s);
+    P->prof.push_back(e);
+  };
+  int rc;
+  mark();
+  {
+    dim3 grid((W + 31) / 32, (H + 7) / 8, n);
+    small::conv1_u8_kernel<<<grid, dim3(32, 8), small::conv1_smem(d.c1), s>>>(in, x1, P->w1g, P->b1, H, W, d.c1,
+                                                                              in_bgr);
+    ctx->launches++;
+    VEX_CUDA(ctx, cudaGetLastError());
+  }
+  mark();
+  if (out_f32 && tap == 1) return tap_bf16(x1, d.c1);
+  if ((rc = run_tc(ctx, P->tc[0], x1, x2, x1, n, H, W, s))) return rc;        // + x1 after ReLU (app.py:292)
+  mark();
+  if (out_f32 && tap == 2) return tap_bf16(x2, d.c2);
+  if ((rc = run_tc(ctx, P->tc[1], x2, x3, nullptr, n, H, W, s))) return rc;
+  mark();
+  if (out_f32 && tap == 3) return tap_bf16(x3, d.c3);
+  if ((rc = run_tc(ctx, P->tc[2], x3, x4, nullptr, n, H, W, s))) return rc;
+  mark();
+  if (out_f32 && tap == 4) return tap_bf16(x4, d.c4);
+  if (!(ctx->attr_mask & 4u)) {
+    VEX_CUDA(ctx, cudaFuncSetAttribute(small::conv3x3_to3_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)small::T3_SMEM));
+    VEX_CUDA(ctx, cudaFuncSetAttribute(small::conv3x3_to3_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)small::T3_SMEM));
+    ctx->attr_mask |= 4u;
+  }
+  {
+    dim3 grid((W + 31) / 32, (H + small::T3_TILE_H - 1) / small::T3_TILE_H, n);
+    small::conv3x3_to3_kernel<0><<<grid, dim3(32, 8), small::T3_SMEM, s>>>(x4, P->w5g, P->b5, x5, nullptr, nullptr,
+                                                                           H, W, d.c4, 0);
+    ctx->launches++;
+    VEX_CUDA(ctx, cudaGetLastError());
+  }
+  mark();
+  if (out_f32 && tap == 5) {
+    small::nhw4_f32_to_nchw_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, s>>>(x5, out_f32, npix, HW);
+    ctx->launches++;
+    VEX_CUDA(ctx, cudaGetLastError());
+    return VEX_OK;
+  }
+  {
+    dim3 grid((W + 31) / 32, H, n);
+    small::upconv1_kernel<<<grid, 128, (size_t)49 * d.up_ch * 4, s>>>(x5, up, P->wu1, P->bu1, H, W, d.up_ch);
+    ctx->launches++;
+    VEX_CUDA(ctx, cudaGetLastError());
+  }
+  mark();
+  if (out_f32 && tap == 6) {
+    const size_t items = npix * 4 * (d.up_ch / 8);
+    small::nhwc_bf16_to_nchw_f32_kernel<<<(unsigned)((items + 255) / 256), 256, 0, s>>>(up, out_f32, npix * 4,
+                                                                                         4 * HW, d.up_ch);
+    ctx->launches++;
+    VEX_CUDA(ctx, cudaGetLastError());
+    return VEX_OK;
+  }
+  {
+    const int H2 = 2 * H, W2 = 2 * W;
+    dim3 grid((W2 + 31) / 32, (H2 + small::T3_TILE_H - 1) / small::T3_TILE_H, n);
+    small::conv3x3_to3_kernel<1><<<grid, dim3(32, 8), small::T3_SMEM, s>>>(up, P->wu2, P->bu2, nullptr, out_u8,
+                                                                           out_f32, H2, W2, d.up_ch, out_bgr);
+    ctx->launches++;
+    VEX_CUDA(ctx, cudaGetLastError());
+  }
+  mark();
+  return VEX_OK;
+}
+
+int cnn_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f32, int tap, int n, int h, int w,
+                int in_bgr, int out_bgr, cudaStream_t s) {
+  if (!ctx->cnn || !ctx->cnn->w1g)
+    return fail(ctx, VEX_ERR_NO_WEIGHTS, "vex_cnn_load_weights has not been called");
+  if ((long long)h * w > (1LL << 28)) return fail(ctx, VEX_ERR_INVALID, "frame too large");
+  // bound the activation workspace: sub-batches of at most ws_budget bytes (at least one frame)
+  for (cudaEvent_t e : ctx->cnn->prof) ctx->cnn->prof_pool.push_back(e);
+  ctx->cnn->prof.clear();
+  const size_t per_frame = ws_layout(ctx->cnn->arch, (size_t)h * w).total;
+  const size_t budget = (size_t)ctx->opt_ws_budget_mb << 20;
+  int sub = (int)std::max<size_t>(1, std::min<size_t>((size_t)n, budget / std::max<size_t>(per_frame, 1)));
+  const vex_cnn_desc& d = ctx->cnn->arch;
+  const size_t out_ch[7] = {3, (size_t)d.c1, (size_t)d.c2, (size_t)d.c3, (size_t)d.c4, 3, (size_t)d.up_ch};
+  const size_t out_px = (tap == 0 || tap == 6) ? (size_t)4 * h * w : (size_t)h * w;
+  for (int f0 = 0; f0 < n; f0 += sub) {
+    const int nf = std::min(sub, n - f0);
+    int rc = forward_chunk(ctx, in + (size_t)f0 * h * w * 3, out_u8 ? out_u8 + (size_t)f0 * h * w * 12 : nullptr,
+                           out_f32 ? out_f32 + (size_t)f0 * out_ch[tap] * out_px : nullptr, tap, nf, h, w, in_bgr,
+                           out_bgr, s);
+    if (rc) return rc;
+  }
+  return VEX_OK;
+}
+
+int cnn_profile_ms(vex_ctx* ctx, float* ms7) {
+  CnnPlan* P = ctx->cnn;
+  if (!P || P->prof.empty() || P->prof.size() % 8 != 0)
+    return fail(ctx, VEX_ERR_INVALID, "vex_cnn_profile_ms: no complete profiled forward (set option profile=1)");
+  VEX_CUDA(ctx, cudaEventSynchronize(P->prof.back()));
+  for (int i = 0; i < 7; ++i) ms7[i] = 0.f;
+  for (size_t b = 0; b < P->prof.size(); b += 8)
+    for (int i = 0; i < 7; ++i) {
+      float ms = 0.f;
+      VEX_CUDA(ctx, cudaEventElapsedTime(&ms, P->prof[b + i], P->prof[b + i + 1]));
+      ms7[i] += ms;
+    }
+  return VEX_OK;
+}
+
+int cnn_repack(vex_ctx* ctx) {
+  CnnPlan* P = ctx->cnn;
+  if (!P || !P->w1g) return VEX_OK;
+  TcLayer& L = P->tc[1];
+  const int bn = (ctx->opt_conv3_bn == 256 && L.cout % 256 == 0) ? 256 : 128;
+  if (bn == L.bn) return VEX_OK;
+  VEX_CUDA(ctx, cudaDeviceSynchronize());
+  L.bn = bn;
+  return pack_tc(ctx, L);
+}
+
+void cnn_destroy(vex_ctx* ctx) {
+  CnnPlan* P = ctx->cnn;
+  if (!P) return;
+  float* fs[] = {P->w1g, P->b1, P->w5g, P->b5, P->wu1, P->bu1, P->wu2, P->bu2};
+  for (float* f : fs)
+    if (f) cudaFree(f);
+  for (TcLayer& L : P->tc) {
+    if (L.wpack) cudaFree(L.wpack);
+    if (L.bias) cudaFree(L.bias);
+  }
+  if (P->ws) cudaFree(P->ws);
+  for (cudaEvent_t e : P->prof) cudaEventDestroy(e);
+  for (cudaEvent_t e : P->prof_pool) cudaEventDestroy(e);
+  delete P;
+  ctx->cnn = nullptr;
+}
+
 }  // namespace vex

@@ -8,9 +8,16 @@ namespace {
 std::string g_create_error;
 
 int ensure_slots(vex_ctx* ctx, size_t in_bytes, size_t out_bytes) {
-  for (int i = 0; i < 2; ++i)
-    if (!ctx->slot_stream[i])
-      VEX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->slot_stream[i], cudaStreamNonBlocking));
+  if (!ctx->st_h2d) {
+    VEX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->st_h2d, cudaStreamNonBlocking));
+    VEX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->st_comp, cudaStreamNonBlocking));
+    VEX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->st_d2h, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      VEX_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_h2d[i], cudaEventDisableTiming));
+      VEX_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_comp[i], cudaEventDisableTiming));
+      VEX_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_d2h[i], cudaEventDisableTiming));
+    }
+  }
   if (in_bytes > ctx->slot_in_bytes || out_bytes > ctx->slot_out_bytes) {
     VEX_CUDA(ctx, cudaDeviceSynchronize());
     for (int i = 0; i < 2; ++i) {
@@ -78,8 +85,13 @@ int vex_destroy(vex_ctx* ctx) {
   for (int i = 0; i < 2; ++i) {
     if (ctx->slot_in[i]) cudaFree(ctx->slot_in[i]);
     if (ctx->slot_out[i]) cudaFree(ctx->slot_out[i]);
-    if (ctx->slot_stream[i]) cudaStreamDestroy(ctx->slot_stream[i]);
+    if (ctx->ev_h2d[i]) cudaEventDestroy(ctx->ev_h2d[i]);
+    if (ctx->ev_comp[i]) cudaEventDestroy(ctx->ev_comp[i]);
+    if (ctx->ev_d2h[i]) cudaEventDestroy(ctx->ev_d2h[i]);
   }
+  if (ctx->st_h2d) cudaStreamDestroy(ctx->st_h2d);
+  if (ctx->st_comp) cudaStreamDestroy(ctx->st_comp);
+  if (ctx->st_d2h) cudaStreamDestroy(ctx->st_d2h);
   delete ctx;
   return VEX_OK;
 }
@@ -152,29 +164,43 @@ int vex_upscale_host(vex_ctx* ctx, int mode, const uint8_t* in_host, uint8_t* ou
   const size_t fin = (size_t)h * w * 3, fout = fin * 4;
   int rc = ensure_slots(ctx, fin * chunk, fout * chunk);
   if (rc) return rc;
-  // double-buffered: slot k&1 owns a stream; H2D(k+1) and D2H(k-1) overlap compute(k) because the
-  // two slots' streams are independent and a slot's buffers are reused only in stream order.
+  // Three-stage pipeline over two device slots: chunk k's H2D (copy-in stream), kernels (compute stream)
+  // and D2H (copy-out stream) are chained by events, so H2D(k+1) and D2H(k-1) overlap compute(k), and the
+  // CNN workspace is only ever touched from the compute stream.
   int k = 0;
   for (int f0 = 0; f0 < n; f0 += chunk, ++k) {
     const int nf = std::min(chunk, n - f0), sl = k & 1;
-    cudaStream_t st = ctx->slot_stream[sl];
-    VEX_CUDA(ctx, cudaMemcpyAsync(ctx->slot_in[sl], in_host + fin * f0, fin * nf,
-                                  cudaMemcpyHostToDevice, st));
+    if (k >= 2) VEX_CUDA(ctx, cudaStreamWaitEvent(ctx->st_h2d, ctx->ev_comp[sl], 0));   // input slot consumed
+    VEX_CUDA(ctx, cudaMemcpyAsync(ctx->slot_in[sl], in_host + fin * f0, fin * nf, cudaMemcpyHostToDevice,
+                                  ctx->st_h2d));
+    VEX_CUDA(ctx, cudaEventRecord(ctx->ev_h2d[sl], ctx->st_h2d));
+    VEX_CUDA(ctx, cudaStreamWaitEvent(ctx->st_comp, ctx->ev_h2d[sl], 0));
+    if (k >= 2) VEX_CUDA(ctx, cudaStreamWaitEvent(ctx->st_comp, ctx->ev_d2h[sl], 0));  // output slot drained
     if (mode == VEX_MODE_BICUBIC)
-      rc = vex::launch_bicubic2x(ctx, ctx->slot_in[sl], ctx->slot_out[sl], nf, h, w, flags & 1, st);
+      rc = vex::launch_bicubic2x(ctx, ctx->slot_in[sl], ctx->slot_out[sl], nf, h, w, flags & 1, ctx->st_comp);
     else
-      rc = vex::cnn_forward(ctx, ctx->slot_in[sl], ctx->slot_out[sl], nullptr, 0, nf, h, w,
-                            flags & 1, (flags >> 1) & 1, st);
+      rc = vex::cnn_forward(ctx, ctx->slot_in[sl], ctx->slot_out[sl], nullptr, 0, nf, h, w, flags & 1,
+                            (flags >> 1) & 1, ctx->st_comp);
     if (rc) {
       cudaDeviceSynchronize();
       return rc;
     }
-    VEX_CUDA(ctx, cudaMemcpyAsync(out_host + fout * f0, ctx->slot_out[sl], fout * nf,
-                                  cudaMemcpyDeviceToHost, st));
+    VEX_CUDA(ctx, cudaEventRecord(ctx->ev_comp[sl], ctx->st_comp));
+    VEX_CUDA(ctx, cudaStreamWaitEvent(ctx->st_d2h, ctx->ev_comp[sl], 0));
+    VEX_CUDA(ctx, cudaMemcpyAsync(out_host + fout * f0, ctx->slot_out[sl], fout * nf, cudaMemcpyDeviceToHost,
+                                  ctx->st_d2h));
+    VEX_CUDA(ctx, cudaEventRecord(ctx->ev_d2h[sl], ctx->st_d2h));
   }
-  VEX_CUDA(ctx, cudaStreamSynchronize(ctx->slot_stream[0]));
-  VEX_CUDA(ctx, cudaStreamSynchronize(ctx->slot_stream[1]));
+  VEX_CUDA(ctx, cudaStreamSynchronize(ctx->st_d2h));
+  VEX_CUDA(ctx, cudaStreamSynchronize(ctx->st_comp));
+  VEX_CUDA(ctx, cudaStreamSynchronize(ctx->st_h2d));
   return VEX_OK;
+}
+
+int vex_cnn_profile_ms(vex_ctx* ctx, float* ms7) {
+  if (!ctx || !ms7) return VEX_ERR_INVALID;
+  VEX_CUDA(ctx, cudaSetDevice(ctx->device));
+  return vex::cnn_profile_ms(ctx, ms7);
 }
 
 int vex_kernel_launches(const vex_ctx* ctx, unsigned long long* out) {
@@ -188,9 +214,16 @@ int vex_set_option(vex_ctx* ctx, const char* name, int value) {
   int* slot = nullptr;
   if (!strcmp(name, "desc_base_offset")) slot = &ctx->opt_desc_base_offset;
   else if (!strcmp(name, "force_generic_bicubic")) slot = &ctx->opt_force_generic_bicubic;
+  else if (!strcmp(name, "conv3_bn")) slot = &ctx->opt_conv3_bn;
+  else if (!strcmp(name, "ws_budget_mb")) slot = &ctx->opt_ws_budget_mb;
+  else if (!strcmp(name, "profile")) slot = &ctx->opt_profile;
   if (!slot) return vex::fail(ctx, VEX_ERR_INVALID, std::string("vex_set_option: unknown ") + name);
   const int prev = *slot;
   *slot = value;
+  if (slot == &ctx->opt_conv3_bn) {
+    cudaSetDevice(ctx->device);
+    if (int rc = vex::cnn_repack(ctx)) return rc;
+  }
   return prev;
 }
 

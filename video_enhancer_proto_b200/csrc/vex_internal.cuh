@@ -22,11 +22,13 @@ struct vex_ctx {
   std::string err;
   unsigned long long launches = 0;
 
-  // streaming path (vex_upscale_host): 2 slots, each with its own stream + device buffers
-  cudaStream_t slot_stream[2] = {nullptr, nullptr};
+  // streaming path (vex_upscale_host): H2D / compute / D2H streams over 2 device slots
+  cudaStream_t st_h2d = nullptr, st_comp = nullptr, st_d2h = nullptr;
+  cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_d2h[2] = {nullptr, nullptr};
   uint8_t* slot_in[2] = {nullptr, nullptr};
   uint8_t* slot_out[2] = {nullptr, nullptr};
   size_t slot_in_bytes = 0, slot_out_bytes = 0;
+  unsigned attr_mask = 0;         // which kernels had their max-dynamic-smem attribute set on this device
 
   // CNN state
   vex::CnnPlan* cnn = nullptr;
@@ -34,6 +36,9 @@ struct vex_ctx {
   // debug knobs (vex_set_option)
   int opt_desc_base_offset = 1;   // 1: smem-descriptor base_offset = (addr>>7)&7 (PTX ISA), 0: always 0
   int opt_force_generic_bicubic = 0;
+  int opt_conv3_bn = 256;         // Cout block of conv3 on the tensor cores (128 or 256)
+  int opt_profile = 0;            // record per-layer events in cnn_forward (vex_cnn_profile_ms)
+  int opt_ws_budget_mb = 49152;   // CNN activation workspace cap; larger batches run in sub-batches
 };
 
 namespace vex {
@@ -63,5 +68,7 @@ int cnn_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f32
                 int n, int h, int w, int in_bgr, int out_bgr, cudaStream_t s);
 size_t cnn_workspace_bytes(const vex_ctx* ctx, int n, int h, int w);
 void cnn_destroy(vex_ctx* ctx);
+int cnn_repack(vex_ctx* ctx);
+int cnn_profile_ms(vex_ctx* ctx, float* ms7);   // after opt_conv3_bn changed
 
 }  // namespace vex

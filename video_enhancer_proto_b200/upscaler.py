@@ -199,6 +199,16 @@ class B200VideoEnhancer:
         _lib.check(self._ctx, rc, "vex_cnn2x_f32_debug")
         return out
 
+    LAYER_NAMES = ("conv1", "conv2", "conv3", "conv4", "conv5", "upconv1", "upconv2")
+
+    def cnn_profile_ms(self) -> Dict[str, float]:
+        """Per-layer device ms of the last CNN call made with ``set_option("profile", 1)`` (vex_cnn_profile_ms)."""
+        self._ensure_ctx()
+        ms = (C.c_float * 7)()
+        rc = self._lib.vex_cnn_profile_ms(self._ctx, ms)
+        _lib.check(self._ctx, rc, "vex_cnn_profile_ms")
+        return dict(zip(self.LAYER_NAMES, [float(v) for v in ms]))
+
     def kernel_launches(self) -> int:
         self._ensure_ctx()
         v = C.c_ulonglong()

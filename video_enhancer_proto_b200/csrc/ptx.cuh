@@ -128,8 +128,10 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&v)[32])
 // Shared-memory matrix descriptor, K-major operand, 128-byte swizzle: rows of 64 bf16 (128 B), 8-row atoms
 // of 1024 B stacked with stride SBO = 1024 B.  bits: [0,14) addr>>4, [16,30) LBO>>4 (unused for swizzled
 // K-major), [32,46) SBO>>4, [46,48) version = 1, [49,52) base offset, [61,64) layout (2 = SWIZZLE_128B).
-// base_offset = (addr >> 7) & 7 is what the PTX ISA prescribes for a start address that is not aligned to
-// the 1024 B swizzle repeat — the 3x3 taps start `dx` rows (dx*128 B) into an atom.
+// The 3x3 taps start `dx` rows (dx*128 B) into a swizzle atom.  MEASURED on B200 (tools/cnn_diag.py, round 1):
+// the tensor core applies the 128B swizzle to the absolute shared-memory address bits, exactly as TMA does
+// when it writes the tile, so a start address advanced by whole 128 B rows needs base_offset = 0; setting
+// base_offset = (addr >> 7) & 7 double-counts the phase and permutes the 16 B chunks (x2 error 57 %).
 __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t use_base_offset) {
   const uint32_t lo = ((saddr >> 4) & 0x3FFFu) | (1u << 16);
   uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);

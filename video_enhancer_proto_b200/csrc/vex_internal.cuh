@@ -34,7 +34,7 @@ struct vex_ctx {
   vex::CnnPlan* cnn = nullptr;
 
   // debug knobs (vex_set_option)
-  int opt_desc_base_offset = 1;   // 1: smem-descriptor base_offset = (addr>>7)&7 (PTX ISA), 0: always 0
+  int opt_desc_base_offset = 0;   // smem-descriptor base_offset field: 0 (measured correct on B200), 1: (addr>>7)&7
   int opt_force_generic_bicubic = 0;
   int opt_conv3_bn = 256;         // Cout block of conv3 on the tensor cores (128 or 256)
   int opt_profile = 0;            // record per-layer events in cnn_forward (vex_cnn_profile_ms)

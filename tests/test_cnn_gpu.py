@@ -219,3 +219,24 @@ def test_batch8_1080p_frames_independent(enhancers):
     solo = enh.upscale_device(dev(pool), mode="cnn").cpu().numpy()
     for i in range(8):
         assert np.array_equal(out8[i], solo[i % 2]), i
+
+
+@pytest.mark.parametrize("h,w", [(37, 53), (130, 70)])
+def test_cuda_core_thin_layers_still_agree(enhancers, models, h, w):
+    """option thin_tc=0 routes conv1/conv5/upconv1/upconv2 through the fp32 CUDA-core kernels (cnn_small.cuh);
+    both implementations must meet the bar, and agree with each other to bf16 noise."""
+    rng = np.random.default_rng(21)
+    frames = [synth.random_frame(h, w, rng), synth.edges_frame(h, w, rng)]
+    enh = enhancers["seed0"]
+    want = O.ref_cnn_batch_f32(models["seed0"], frames).numpy()
+    a = enh.cnn_debug_f32(dev(frames), tap=0).cpu().numpy()
+    prev = enh.set_option("thin_tc", 0)
+    try:
+        b = enh.cnn_debug_f32(dev(frames), tap=0).cpu().numpy()
+        u8 = enh.upscale_device(dev(frames), mode="cnn").cpu().numpy()
+    finally:
+        enh.set_option("thin_tc", prev)
+    check_f32(a, want, f"seed0 {h}x{w} thin_tc=1")
+    check_f32(b, want, f"seed0 {h}x{w} thin_tc=0")
+    for i, f in enumerate(frames):
+        assert np.abs(u8[i].astype(int) - O.ref_cnn_frame(models["seed0"], f).astype(int)).max() <= 2

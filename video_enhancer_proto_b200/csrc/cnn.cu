@@ -13,6 +13,7 @@
 
 #include "cnn_small.cuh"
 #include "conv_tc.cuh"
+#include "thin_tc.cuh"
 #include "vex_internal.cuh"
 
 namespace vex {
@@ -32,6 +33,9 @@ struct CnnPlan {
   float *wu1 = nullptr, *bu1 = nullptr;      // upconv1: [4][12][up], [up]
   float *wu2 = nullptr, *bu2 = nullptr;      // upconv2: [up/64][9][64][4], [3]
   TcLayer tc[3];                             // conv2, conv3, conv4
+  // thin layers on the tensor cores (thin_tc.cuh): SWIZZLE_128B operand images, bf16
+  uint8_t *t1w = nullptr, *tu1w = nullptr, *t5w = nullptr, *tu2w = nullptr;
+  float* tu1b = nullptr;                     // upconv1 bias replicated per PixelShuffle phase [4*up]
   // workspace
   uint8_t* ws = nullptr;
   size_t ws_bytes = 0;
@@ -130,6 +134,62 @@ int run_tc(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfloat1
            const __nv_bfloat16* skip, int n, int H, int W, cudaStream_t s) {
   return L.bn == 256 ? launch_tc<256>(ctx, L, in, out, skip, n, H, W, s)
                      : launch_tc<128>(ctx, L, in, out, skip, n, H, W, s);
+}
+
+// rows x (nchunk x 64) bf16 matrix -> [nchunk] slices of rows x 128 B in the SWIZZLE_128B K-major image
+template <typename F>
+int pack_rows_sw128(vex_ctx* ctx, uint8_t** dst, int rows, int nchunk, F value) {
+  std::vector<uint16_t> img((size_t)nchunk * rows * 64, 0);
+  for (int c = 0; c < nchunk; ++c)
+    for (int r = 0; r < rows; ++r)
+      for (int k = 0; k < 64; ++k)
+        img[((size_t)c * rows + r) * 64 + (((k >> 3) ^ (r & 7)) << 3) + (k & 7)] = f32_to_bf16_rne(value(r, c * 64 + k));
+  return upload(ctx, dst, img.data(), img.size() * 2);
+}
+
+template <int MODE, int BN>
+int launch_i27(vex_ctx* ctx, unsigned abit, const void* in, const uint8_t* w, const float* bias, __nv_bfloat16* out,
+               int n, int H, int W, int in_bgr, cudaStream_t s) {
+  using C = thin::I27Cfg<BN>;
+  if (!(ctx->attr_mask & abit)) {
+    VEX_CUDA(ctx, cudaFuncSetAttribute(thin::im2col27_kernel<MODE, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       C::SMEM));
+    ctx->attr_mask |= abit;
+  }
+  thin::I27Params p;
+  p.in = in; p.wpack = w; p.bias = bias; p.out = out; p.H = H; p.W = W;
+  p.npix = (long long)n * H * W; p.in_bgr = in_bgr;
+  const long long items = (p.npix + 127) / 128;
+  thin::im2col27_kernel<MODE, BN><<<(unsigned)std::min<long long>(items, ctx->sm_count), thin::I27_THREADS, C::SMEM, s>>>(p);
+  ctx->launches++;
+  VEX_CUDA(ctx, cudaGetLastError());
+  return VEX_OK;
+}
+
+template <int MODE>
+int launch_g27(vex_ctx* ctx, unsigned abit, const __nv_bfloat16* in, int C, const uint8_t* w, const float* bias,
+               float* out_f4, uint8_t* out_u8, float* out_nchw, int n, int H, int W, int out_bgr, cudaStream_t s) {
+  if (!(ctx->attr_mask & abit)) {
+    VEX_CUDA(ctx, cudaFuncSetAttribute(thin::gemm27_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       thin::G27Cfg::SMEM));
+    ctx->attr_mask |= abit;
+  }
+  CUtensorMap amap;
+  int rc = make_amap(ctx, &amap, in, n, H, W, C, 8);
+  if (rc) return rc;
+  thin::G27Params p;
+  p.wpack = w; p.bias = bias; p.out_f4 = reinterpret_cast<float4*>(out_f4); p.out_u8 = out_u8; p.out_nchw = out_nchw;
+  p.H = H; p.W = W; p.NC = C / 64;
+  p.tiles_x = (W + thin::G27_TW - 1) / thin::G27_TW;
+  p.tiles_y = (H + thin::G27_ROWS - 1) / thin::G27_ROWS;
+  p.n_img = n; p.out_bgr = out_bgr;
+  const long long total = (long long)p.tiles_x * p.tiles_y * n;
+  if (total > 0x7fffffffLL) return fail(ctx, VEX_ERR_INVALID, "gemm27: too many tiles");
+  thin::gemm27_kernel<MODE><<<(unsigned)std::min<long long>(total, ctx->sm_count), thin::G27_THREADS,
+                              thin::G27Cfg::SMEM, s>>>(amap, p);
+  ctx->launches++;
+  VEX_CUDA(ctx, cudaGetLastError());
+  return VEX_OK;
 }
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -247,6 +307,42 @@ int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const*
     if ((rc = upload(ctx, &P->wu2, w.data(), w.size() * 4))) return rc;
     if ((rc = upload(ctx, &P->bu2, u2b, 12))) return rc;
   }
+  // ---- tensor-core images of the thin layers (thin_tc.cuh); k = (ky*3+kx)*3+ci, rows = output columns
+  if (c1 <= 256) {   // conv1: [c1 rows][k < 27], BN scale and 1/255 folded
+    rc = pack_rows_sw128(ctx, &P->t1w, c1, 1, [&](int r, int k) -> float {
+      if (k >= 27) return 0.f;
+      const int ci = k % 3, tap = k / 3;
+      return cw[0][((size_t)r * 3 + ci) * 9 + tap] * scale[0][r] * (1.0f / 255.0f);
+    });
+    if (rc) return rc;
+  }
+  {  // upconv1 as conv3x3 3 -> 4*up + PixelShuffle(2): row = phase*up + co, phase = py*2+px.
+     // 3x3 tap index ky' (input row y + ky' - 1) -> transposed-conv kernel row ky:  py=0: {1->1, 0->3}, py=1: {2->0, 1->2}
+    const int kmap[2][3] = {{3, 1, -1}, {-1, 2, 0}};
+    rc = pack_rows_sw128(ctx, &P->tu1w, 4 * up, 1, [&](int r, int k) -> float {
+      if (k >= 27) return 0.f;
+      const int ph = r / up, co = r % up, ci = k % 3, tap = k / 3;
+      const int ky = kmap[ph >> 1][tap / 3], kx = kmap[ph & 1][tap % 3];
+      if (ky < 0 || kx < 0) return 0.f;
+      return u1w[(((size_t)ci * up + co) * 4 + ky) * 4 + kx];
+    });
+    if (rc) return rc;
+    std::vector<float> b4((size_t)4 * up);
+    for (int i = 0; i < 4 * up; ++i) b4[i] = u1b[i % up];
+    if ((rc = upload(ctx, &P->tu1b, b4.data(), b4.size() * 4))) return rc;
+  }
+  // conv5 / upconv2 as 1x1 GEMMs: row n = tap*3+co (27 of 32), K = input channels
+  rc = pack_rows_sw128(ctx, &P->t5w, 32, c4 / 64, [&](int r, int k) -> float {
+    if (r >= 27) return 0.f;
+    return cw[4][((size_t)(r % 3) * c4 + k) * 9 + r / 3];
+  });
+  if (rc) return rc;
+  rc = pack_rows_sw128(ctx, &P->tu2w, 32, up / 64, [&](int r, int k) -> float {
+    if (r >= 27) return 0.f;
+    const int co = r % 3, tap = r / 3, ky = tap / 3, kx = tap % 3;
+    return u2w[(((size_t)k * 3 + co) * 3 + (2 - ky)) * 3 + (2 - kx)];
+  });
+  if (rc) return rc;
   return VEX_OK;
 }
 
@@ -293,8 +389,13 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
     P->prof.push_back(e);
   };
   int rc;
+  const bool thin_tc = ctx->opt_thin_tc != 0;
   mark();
-  {
+  if (thin_tc && d.c1 == 128) {
+    if ((rc = launch_i27<thin::MODE_CONV1, 128>(ctx, 8u, in, P->t1w, P->b1, x1, n, H, W, in_bgr, s))) return rc;
+  } else if (thin_tc && d.c1 == 256) {
+    if ((rc = launch_i27<thin::MODE_CONV1, 256>(ctx, 16u, in, P->t1w, P->b1, x1, n, H, W, in_bgr, s))) return rc;
+  } else {
     dim3 grid((W + 31) / 32, (H + 7) / 8, n);
     small::conv1_u8_kernel<<<grid, dim3(32, 8), small::conv1_smem(d.c1), s>>>(in, x1, P->w1g, P->b1, H, W, d.c1,
                                                                               in_bgr);
@@ -319,7 +420,10 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
                                        (int)small::T3_SMEM));
     ctx->attr_mask |= 4u;
   }
-  {
+  if (thin_tc) {
+    if ((rc = launch_g27<thin::MODE_CONV5>(ctx, 32u, x4, d.c4, P->t5w, P->b5, x5, nullptr, nullptr, n, H, W, 0, s)))
+      return rc;
+  } else {
     dim3 grid((W + 31) / 32, (H + small::T3_TILE_H - 1) / small::T3_TILE_H, n);
     small::conv3x3_to3_kernel<0><<<grid, dim3(32, 8), small::T3_SMEM, s>>>(x4, P->w5g, P->b5, x5, nullptr, nullptr,
                                                                            H, W, d.c4, 0);
@@ -333,7 +437,9 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
     VEX_CUDA(ctx, cudaGetLastError());
     return VEX_OK;
   }
-  {
+  if (thin_tc) {
+    if ((rc = launch_i27<thin::MODE_UP1, 256>(ctx, 64u, x5, P->tu1w, P->tu1b, up, n, H, W, 0, s))) return rc;
+  } else {
     dim3 grid((W + 31) / 32, H, n);
     small::upconv1_kernel<<<grid, 128, (size_t)49 * d.up_ch * 4, s>>>(x5, up, P->wu1, P->bu1, H, W, d.up_ch);
     ctx->launches++;
@@ -348,7 +454,11 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
     VEX_CUDA(ctx, cudaGetLastError());
     return VEX_OK;
   }
-  {
+  if (thin_tc) {
+    if ((rc = launch_g27<thin::MODE_UP2>(ctx, 128u, up, d.up_ch, P->tu2w, P->bu2, nullptr, out_u8, out_f32, n, 2 * H,
+                                         2 * W, out_bgr, s)))
+      return rc;
+  } else {
     const int H2 = 2 * H, W2 = 2 * W;
     dim3 grid((W2 + 31) / 32, (H2 + small::T3_TILE_H - 1) / small::T3_TILE_H, n);
     small::conv3x3_to3_kernel<1><<<grid, dim3(32, 8), small::T3_SMEM, s>>>(up, P->wu2, P->bu2, nullptr, out_u8,
@@ -413,7 +523,10 @@ int cnn_repack(vex_ctx* ctx) {
 void cnn_destroy(vex_ctx* ctx) {
   CnnPlan* P = ctx->cnn;
   if (!P) return;
-  float* fs[] = {P->w1g, P->b1, P->w5g, P->b5, P->wu1, P->bu1, P->wu2, P->bu2};
+  float* fs[] = {P->w1g, P->b1, P->w5g, P->b5, P->wu1, P->bu1, P->wu2, P->bu2, P->tu1b};
+  uint8_t* us[] = {P->t1w, P->tu1w, P->t5w, P->tu2w};
+  for (uint8_t* u : us)
+    if (u) cudaFree(u);
   for (float* f : fs)
     if (f) cudaFree(f);
   for (TcLayer& L : P->tc) {

@@ -1,0 +1,422 @@
+// The thin layers of AdvancedUpscaler on the sm_100a tensor cores (tcgen05 + TMEM), so that they run at
+// HBM speed instead of CUDA-core FMA speed.  Two kernel templates:
+//
+//  im2col27_kernel  3-channel 3x3 neighbourhood (K = 27 -> 32) x N output channels.
+//      MODE_CONV1:  uint8 HWC frame -> conv1 + bn1 + relu -> x1 bf16 NHWC             (app.py:291, 535)
+//      MODE_UP1:    x5 fp32 -> ConvTranspose2d(3,64,4,2,1) + relu -> `up` bf16 NHWC    (app.py:298)
+//                   as conv3x3 3 -> 4*64 followed by PixelShuffle(2) in the store addressing.
+//      Builder warps gather the neighbourhood of one pixel per thread and write it as one 128 B row of a
+//      K-major SWIZZLE_128B operand; one thread issues 2 tcgen05.mma (K = 2 x 16) per 128 pixels; epilogue
+//      warps drain TMEM (bias, relu, bf16) to global.  TMEM holds 512/N accumulators so the three roles overlap.
+//
+//  gemm27_kernel    3x3 conv C -> 3 channels computed as ONE 1x1 GEMM  Y[p][(tap,co)] = sum_c X[p][c] W[c][tap][co]
+//      (N = 27 -> 32) over a TMA-loaded halo tile, followed by a 9-term shifted gather-sum in shared memory.
+//      A direct implicit GEMM would waste >80 % of each MMA on padding N = 3 -> 16 and re-read the tile 9 times.
+//      MODE_CONV5:  x4 -> conv5 -> x5 fp32 [p][4]                                      (app.py:295)
+//      MODE_UP2:    up -> ConvTranspose2d(64,3,3,1,1) -> clamp -> x255 -> truncate -> uint8 HWC (app.py:299, 549)
+#pragma once
+
+#include <cuda_bf16.h>
+
+#include "ptx.cuh"
+
+namespace vex {
+namespace thin {
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// ============================================================================================ im2col27
+constexpr int MODE_CONV1 = 0, MODE_UP1 = 1;
+constexpr int I27_THREADS = 288;       // warps 0-3 build A, warp 4 issues MMAs, warps 5-8 drain TMEM
+constexpr int I27_SA = 3;              // A stages (128 rows x 128 B each)
+
+template <int BN>
+struct I27Cfg {
+  static constexpr int NACC = 512 / BN;
+  static constexpr int A_STAGE = 128 * 128;
+  static constexpr int W_BYTES = BN * 128;
+  static constexpr int W_OFF = I27_SA * A_STAGE;
+  static constexpr int BAR_OFF = W_OFF + W_BYTES;
+  static constexpr int BIAS_OFF = BAR_OFF + 256;
+  static constexpr int SMEM = BIAS_OFF + BN * 4 + 1024;
+};
+
+struct I27Params {
+  const void* in;          // MODE_CONV1: uint8 [n][H][W][3];  MODE_UP1: float4 [n][H][W]
+  const uint8_t* wpack;    // BN rows x 128 B, SWIZZLE_128B image, k = (ky*3+kx)*3+ci in the first 32 bf16
+  const float* bias;       // [BN]
+  __nv_bfloat16* out;      // MODE_CONV1: [n][H][W][BN];  MODE_UP1: [n][2H][2W][BN/4]
+  int H, W;
+  long long npix;          // n*H*W
+  int in_bgr;
+};
+
+template <int MODE, int BN>
+__global__ void __launch_bounds__(I27_THREADS, 1)
+im2col27_kernel(const I27Params p) {
+  using C = I27Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = ptx::smem_u32(smem_raw);
+  const uint32_t sbase = (raw + 1023u) & ~1023u;
+  uint8_t* sm = smem_raw + (sbase - raw);
+  const uint32_t bar0 = sbase + C::BAR_OFF;
+  const uint32_t a_full = bar0, a_empty = bar0 + 8 * I27_SA;
+  const uint32_t acc_full = a_empty + 8 * I27_SA, acc_empty = acc_full + 8 * C::NACC;
+  const uint32_t w_bar = acc_empty + 8 * C::NACC, tmem_slot = w_bar + 8;
+  volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(sm + C::BAR_OFF + (tmem_slot - bar0));
+  float* bias_s = reinterpret_cast<float*>(sm + C::BIAS_OFF);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long items = (p.npix + 127) / 128;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < I27_SA; ++i) { ptx::mbar_init(a_full + 8 * i, 128); ptx::mbar_init(a_empty + 8 * i, 1); }
+    for (int i = 0; i < C::NACC; ++i) { ptx::mbar_init(acc_full + 8 * i, 1); ptx::mbar_init(acc_empty + 8 * i, 4); }
+    ptx::mbar_init(w_bar, 1);
+    ptx::fence_mbar_init();
+  }
+  for (int i = threadIdx.x; i < BN; i += I27_THREADS) bias_s[i] = p.bias[i];
+  if (warp == 4) {
+    ptx::tmem_alloc(tmem_slot, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot_p;
+
+  if (warp < 4) {
+    // ================================ A builders: one pixel (= one 128 B operand row) per thread
+    const int r = threadIdx.x;                       // row within the stage
+    uint32_t sa = 0, pa = 0;
+    for (long long it = blockIdx.x; it < items; it += gridDim.x) {
+      const long long pix = it * 128 + r;
+      uint32_t w[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) w[j] = 0u;
+      if (pix < p.npix) {
+        const int x = (int)(pix % p.W);
+        const long long t = pix / p.W;
+        const int y = (int)(t % p.H);
+        const long long img = t / p.H;
+        float v[27];
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
+          const int yy = y + ky - 1;
+#pragma unroll
+          for (int kx = 0; kx < 3; ++kx) {
+            const int xx = x + kx - 1;
+            const bool ok = yy >= 0 && yy < p.H && xx >= 0 && xx < p.W;
+            const long long q = (img * p.H + yy) * p.W + xx;
+            if (MODE == MODE_CONV1) {
+              const uint8_t* s = reinterpret_cast<const uint8_t*>(p.in) + q * 3;
+#pragma unroll
+              for (int c = 0; c < 3; ++c)
+                v[(ky * 3 + kx) * 3 + c] = ok ? (float)__ldg(s + (p.in_bgr ? 2 - c : c)) : 0.f;
+            } else {
+              float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (ok) f = __ldg(reinterpret_cast<const float4*>(p.in) + q);
+              v[(ky * 3 + kx) * 3 + 0] = f.x; v[(ky * 3 + kx) * 3 + 1] = f.y; v[(ky * 3 + kx) * 3 + 2] = f.z;
+            }
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 13; ++j) w[j] = ptx::pack_bf16x2(v[2 * j], v[2 * j + 1]);
+        w[13] = ptx::pack_bf16x2(v[26], 0.f);
+      }
+      ptx::mbar_wait(a_empty + 8 * sa, pa ^ 1);
+      uint8_t* row = sm + sa * C::A_STAGE + r * 128;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        *reinterpret_cast<uint4*>(row + ((j ^ (r & 7)) << 4)) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+      ptx::fence_proxy_async_smem();                 // generic-proxy stores -> visible to the tensor core
+      ptx::mbar_arrive(a_full + 8 * sa);
+      if (++sa == I27_SA) { sa = 0; pa ^= 1; }
+    }
+  } else if (warp == 4) {
+    // ================================ weights once, then 2 MMAs per item
+    if (lane == 0) {
+      ptx::mbar_expect_tx(w_bar, C::W_BYTES);
+      ptx::bulk_load(sbase + C::W_OFF, p.wpack, C::W_BYTES, w_bar);
+      ptx::mbar_wait(w_bar, 0);
+      constexpr uint32_t idesc = ptx::idesc_bf16_f32(128, BN);
+      uint32_t sa = 0, pa = 0, b = 0, pb = 0;
+      for (long long it = blockIdx.x; it < items; it += gridDim.x) {
+        ptx::mbar_wait(acc_empty + 8 * b, pb ^ 1);
+        ptx::mbar_wait(a_full + 8 * sa, pa);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const uint64_t ad = ptx::smem_desc_sw128(sbase + sa * C::A_STAGE + k * 32, 0);
+          const uint64_t bd = ptx::smem_desc_sw128(sbase + C::W_OFF + k * 32, 0);
+          ptx::mma_bf16_ss(tmem + b * BN, ad, bd, idesc, k);
+        }
+        ptx::tc_commit(a_empty + 8 * sa);
+        ptx::tc_commit(acc_full + 8 * b);
+        if (++sa == I27_SA) { sa = 0; pa ^= 1; }
+        if (++b == C::NACC) { b = 0; pb ^= 1; }
+      }
+    }
+  } else {
+    // ================================ epilogue: TMEM -> bias, relu, bf16 -> global
+    const int q = warp & 3;
+    uint32_t b = 0, pb = 0;
+    for (long long it = blockIdx.x; it < items; it += gridDim.x) {
+      const long long pix = it * 128 + q * 32 + lane;
+      const bool valid = pix < p.npix;
+      __nv_bfloat16* obase = nullptr;
+      if (valid) {
+        if (MODE == MODE_CONV1) {
+          obase = p.out + pix * BN;
+        } else {
+          const int x = (int)(pix % p.W);
+          const long long t = pix / p.W;
+          const int y = (int)(t % p.H);
+          const long long img = t / p.H;
+          obase = p.out + ((img * 2 * p.H + 2 * y) * (2LL * p.W) + 2 * x) * (BN / 4);
+        }
+      }
+      ptx::mbar_wait(acc_full + 8 * b, pb);
+      ptx::tc_fence_after();
+#pragma unroll 1
+      for (int g = 0; g < BN / 32; ++g) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + b * BN + g * 32, v);
+        ptx::tmem_ld_wait();
+        if (valid) {
+          __nv_bfloat16* o;
+          if (MODE == MODE_CONV1) {
+            o = obase + g * 32;
+          } else {                                   // column = phase*64 + co, phase = py*2+px: PixelShuffle(2)
+            const int ph = (g * 32) / (BN / 4), co = (g * 32) % (BN / 4);
+            o = obase + ((long long)(ph >> 1) * (2LL * p.W) + (ph & 1)) * (BN / 4) + co;
+          }
+          uint4* o4 = reinterpret_cast<uint4*>(o);
+#pragma unroll
+          for (int j4 = 0; j4 < 4; ++j4) {
+            float f[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = fmaxf(__uint_as_float(v[j4 * 8 + e]) + bias_s[g * 32 + j4 * 8 + e], 0.f);
+            o4[j4] = make_uint4(ptx::pack_bf16x2(f[0], f[1]), ptx::pack_bf16x2(f[2], f[3]),
+                                ptx::pack_bf16x2(f[4], f[5]), ptx::pack_bf16x2(f[6], f[7]));
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(acc_empty + 8 * b);
+      if (++b == C::NACC) { b = 0; pb ^= 1; }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    __syncwarp();
+    ptx::tmem_dealloc(tmem, 512);
+  }
+}
+
+// ============================================================================================== gemm27
+constexpr int MODE_CONV5 = 0, MODE_UP2 = 1;
+constexpr int G27_THREADS = 192;       // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
+constexpr int G27_ROWS = 6;            // output rows per item; halo tile = 8 rows x 32 px = 256 GEMM rows
+constexpr int G27_TW = 30;
+constexpr int G27_SA = 4;
+constexpr int G27_A_STAGE = 8 * 32 * 128;            // 32 KB: one 64-channel chunk of the halo tile
+constexpr int G27_YS_PITCH = 256;                    // Ys[k][m], k < 27, m = halo-flat pixel
+constexpr int G27_OB_PITCH = 104;                    // staged uint8 output row (<= 3 + 90 bytes), word aligned
+
+struct G27Cfg {
+  static constexpr int W_OFF = G27_SA * G27_A_STAGE;               // up to 8 chunks x 4 KB of weights
+  static constexpr int YS_OFF = W_OFF + 8 * 4096;
+  static constexpr int OB_OFF = YS_OFF + 27 * G27_YS_PITCH * 4;
+  static constexpr int BAR_OFF = OB_OFF + G27_ROWS * G27_OB_PITCH + 16;
+  static constexpr int SMEM = BAR_OFF + 256 + 1024;
+};
+
+struct G27Params {
+  const uint8_t* wpack;    // [C/64] slices of 32 rows x 128 B (SWIZZLE_128B image); row n = tap*3+co
+  const float* bias;       // [3]
+  float4* out_f4;          // MODE_CONV5: [n][H][W]
+  uint8_t* out_u8;         // MODE_UP2:   [n][H][W][3]
+  float* out_nchw;         // MODE_UP2, optional: [n][3][H][W] clamp(...) before quantisation
+  int H, W, NC;            // NC = C / 64
+  int tiles_x, tiles_y, n_img;
+  int out_bgr;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(G27_THREADS, 1)
+gemm27_kernel(const __grid_constant__ CUtensorMap amap, const G27Params p) {
+  using C = G27Cfg;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = ptx::smem_u32(smem_raw);
+  const uint32_t sbase = (raw + 1023u) & ~1023u;
+  uint8_t* sm = smem_raw + (sbase - raw);
+  const uint32_t bar0 = sbase + C::BAR_OFF;
+  const uint32_t a_full = bar0, a_empty = bar0 + 8 * G27_SA;
+  const uint32_t acc_full = a_empty + 8 * G27_SA, acc_empty = acc_full + 16;
+  const uint32_t w_bar = acc_empty + 16, tmem_slot = w_bar + 8;
+  volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(sm + C::BAR_OFF + (tmem_slot - bar0));
+  float* Ys = reinterpret_cast<float*>(sm + C::YS_OFF);
+  uint8_t* ob = sm + C::OB_OFF;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total = p.tiles_x * p.tiles_y * p.n_img;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < G27_SA; ++i) { ptx::mbar_init(a_full + 8 * i, 1); ptx::mbar_init(a_empty + 8 * i, 1); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full + 8 * i, 1); ptx::mbar_init(acc_empty + 8 * i, 4); }
+    ptx::mbar_init(w_bar, 1);
+    ptx::fence_mbar_init();
+    ptx::prefetch_tensormap(&amap);
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, 128);                 // 2 buffers x (2 groups x 32 columns)
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot_p;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      ptx::mbar_expect_tx(w_bar, p.NC * 4096);
+      ptx::bulk_load(sbase + C::W_OFF, p.wpack, p.NC * 4096, w_bar);
+      uint32_t sa = 0, pa = 0;
+      for (int it = blockIdx.x; it < total; it += gridDim.x) {
+        const int txi = it % p.tiles_x, r = it / p.tiles_x;
+        const int tyi = r % p.tiles_y, n = r / p.tiles_y;
+        for (int c = 0; c < p.NC; ++c) {
+          ptx::mbar_wait(a_empty + 8 * sa, pa ^ 1);
+          ptx::mbar_expect_tx(a_full + 8 * sa, G27_A_STAGE);
+          ptx::tma_load_4d(sbase + sa * G27_A_STAGE, &amap, a_full + 8 * sa, c * 64, txi * G27_TW - 1,
+                           tyi * G27_ROWS - 1, n);
+          if (++sa == G27_SA) { sa = 0; pa ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      ptx::mbar_wait(w_bar, 0);
+      constexpr uint32_t idesc = ptx::idesc_bf16_f32(128, 32);
+      uint32_t sa = 0, pa = 0, b = 0, pb = 0;
+      for (int it = blockIdx.x; it < total; it += gridDim.x) {
+        ptx::mbar_wait(acc_empty + 8 * b, pb ^ 1);
+        ptx::tc_fence_after();
+        for (int c = 0; c < p.NC; ++c) {
+          ptx::mbar_wait(a_full + 8 * sa, pa);
+          ptx::tc_fence_after();
+#pragma unroll
+          for (int g = 0; g < 2; ++g)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const uint64_t ad = ptx::smem_desc_sw128(sbase + sa * G27_A_STAGE + g * 16384 + k * 32, 0);
+              const uint64_t bd = ptx::smem_desc_sw128(sbase + C::W_OFF + c * 4096 + k * 32, 0);
+              ptx::mma_bf16_ss(tmem + b * 64 + g * 32, ad, bd, idesc, (c | k) != 0);
+            }
+          ptx::tc_commit(a_empty + 8 * sa);
+          if (++sa == G27_SA) { sa = 0; pa ^= 1; }
+        }
+        ptx::tc_commit(acc_full + 8 * b);
+        if (++b == 2) { b = 0; pb ^= 1; }
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int et = (warp - 2) * 32 + lane;           // 0..127 among the epilogue threads
+    const float b0 = p.bias[0], b1 = p.bias[1], b2 = p.bias[2];
+    uint32_t b = 0, pb = 0;
+    for (int it = blockIdx.x; it < total; it += gridDim.x) {
+      const int txi = it % p.tiles_x, r = it / p.tiles_x;
+      const int tyi = r % p.tiles_y, n = r / p.tiles_y;
+      const int x0 = txi * G27_TW, y0 = tyi * G27_ROWS;
+      ptx::mbar_wait(acc_full + 8 * b, pb);
+      ptx::tc_fence_after();
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + b * 64 + g * 32, v);
+        ptx::tmem_ld_wait();
+        const int m = g * 128 + q * 32 + lane;
+#pragma unroll
+        for (int k = 0; k < 27; ++k) Ys[k * G27_YS_PITCH + m] = __uint_as_float(v[k]);
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(acc_empty + 8 * b);      // TMEM buffer free: next-but-one item may start
+      if (++b == 2) { b = 0; pb ^= 1; }
+      named_bar_sync(1, 128);
+      // 9-tap gather-sum: out(ty,tx) = bias + sum_t Y[(ty+t/3)*32 + tx+t%3][t*3+co]
+      const int nvx = min(G27_TW, p.W - x0);                    // valid pixels per row of this tile
+#pragma unroll 1
+      for (int idx = et; idx < G27_ROWS * G27_TW; idx += 128) {
+        const int ty = idx / G27_TW, tx = idx - ty * G27_TW;
+        const int y = y0 + ty, x = x0 + tx;
+        float s0 = b0, s1 = b1, s2 = b2;
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+          const int m = (ty + t / 3) * 32 + tx + t % 3;
+          s0 += Ys[(t * 3 + 0) * G27_YS_PITCH + m];
+          s1 += Ys[(t * 3 + 1) * G27_YS_PITCH + m];
+          s2 += Ys[(t * 3 + 2) * G27_YS_PITCH + m];
+        }
+        if (y < p.H && x < p.W) {
+          const size_t pix = ((size_t)n * p.H + y) * p.W + x;
+          if (MODE == MODE_CONV5) {
+            p.out_f4[pix] = make_float4(s0, s1, s2, 0.f);
+          } else {
+            const float c0 = fminf(fmaxf(s0, 0.f), 1.f), c1 = fminf(fmaxf(s1, 0.f), 1.f), c2 = fminf(fmaxf(s2, 0.f), 1.f);
+            if (p.out_nchw) {
+              const size_t plane = (size_t)p.H * p.W;
+              float* o = p.out_nchw + (size_t)n * 3 * plane + (size_t)y * p.W + x;
+              o[0] = c0; o[plane] = c1; o[2 * plane] = c2;
+            }
+            if (p.out_u8) {
+              // np.clip(x*255, 0, 255).astype(np.uint8): fp32 product, truncation (app.py:549)
+              const uint8_t q0 = (uint8_t)__float2uint_rz(c0 * 255.0f), q1 = (uint8_t)__float2uint_rz(c1 * 255.0f),
+                            q2 = (uint8_t)__float2uint_rz(c2 * 255.0f);
+              // staged with the same (address & 3) phase as the global row so that words line up
+              const size_t rowb = (((size_t)n * p.H + y) * p.W + x0) * 3;
+              const int ph = (int)(reinterpret_cast<uintptr_t>(p.out_u8 + rowb) & 3);
+              uint8_t* s = ob + ty * G27_OB_PITCH + ph + tx * 3;
+              s[0] = p.out_bgr ? q2 : q0; s[1] = q1; s[2] = p.out_bgr ? q0 : q2;
+            }
+          }
+        }
+      }
+      if (MODE == MODE_UP2 && p.out_u8) {
+        named_bar_sync(1, 128);
+        // cooperative row stores: aligned 32-bit words in the middle, bytes at the ragged ends
+        for (int wi = et; wi < G27_ROWS * 24; wi += 128) {
+          const int ty = wi / 24, j = wi - ty * 24;
+          const int y = y0 + ty;
+          if (y >= p.H) continue;
+          const size_t rowb = (((size_t)n * p.H + y) * p.W + x0) * 3;
+          const int ph = (int)(reinterpret_cast<uintptr_t>(p.out_u8 + rowb) & 3), nbytes = nvx * 3;
+          const int lo = j * 4, hi = lo + 4;                   // staged byte range of this word
+          if (lo >= ph + nbytes || hi <= ph) continue;
+          uint8_t* g = p.out_u8 + (rowb - ph) + lo;
+          const uint8_t* s = ob + ty * G27_OB_PITCH + lo;
+          if (lo >= ph && hi <= ph + nbytes) {
+            *reinterpret_cast<uint32_t*>(g) = *reinterpret_cast<const uint32_t*>(s);
+          } else {
+            for (int e = 0; e < 4; ++e)
+              if (lo + e >= ph && lo + e < ph + nbytes) g[e] = s[e];
+          }
+        }
+      }
+      named_bar_sync(1, 128);                                   // Ys / ob reusable
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    ptx::tmem_dealloc(tmem, 128);
+  }
+}
+
+}  // namespace thin
+}  // namespace vex

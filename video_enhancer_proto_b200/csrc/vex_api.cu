@@ -217,6 +217,7 @@ int vex_set_option(vex_ctx* ctx, const char* name, int value) {
   else if (!strcmp(name, "conv3_bn")) slot = &ctx->opt_conv3_bn;
   else if (!strcmp(name, "ws_budget_mb")) slot = &ctx->opt_ws_budget_mb;
   else if (!strcmp(name, "profile")) slot = &ctx->opt_profile;
+  else if (!strcmp(name, "thin_tc")) slot = &ctx->opt_thin_tc;
   if (!slot) return vex::fail(ctx, VEX_ERR_INVALID, std::string("vex_set_option: unknown ") + name);
   const int prev = *slot;
   *slot = value;

@@ -37,6 +37,7 @@ struct vex_ctx {
   int opt_desc_base_offset = 0;   // smem-descriptor base_offset field: 0 (measured correct on B200), 1: (addr>>7)&7
   int opt_force_generic_bicubic = 0;
   int opt_conv3_bn = 256;         // Cout block of conv3 on the tensor cores (128 or 256)
+  int opt_thin_tc = 1;            // thin layers on tcgen05 (thin_tc.cuh); 0 = fp32 CUDA-core kernels (cnn_small.cuh)
   int opt_profile = 0;            // record per-layer events in cnn_forward (vex_cnn_profile_ms)
   int opt_ws_budget_mb = 49152;   // CNN activation workspace cap; larger batches run in sub-batches
 };

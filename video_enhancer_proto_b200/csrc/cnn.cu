@@ -102,7 +102,7 @@ int make_amap(vex_ctx* ctx, CUtensorMap* map, const void* base, int n, int H, in
   return VEX_OK;
 }
 
-template <int BN>
+template <int BN, bool SKIP>
 int launch_tc(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfloat16* out,
               const __nv_bfloat16* skip, int n, int H, int W, cudaStream_t s) {
   using C = convtc::Cfg<BN>;
@@ -114,26 +114,49 @@ int launch_tc(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bflo
   p.H = H; p.W = W; p.NC = L.cin / 64; p.Cout = L.cout;
   p.tiles_x = (W + convtc::TILE_W - 1) / convtc::TILE_W;
   p.tiles_y = (H + C::ROWS - 1) / C::ROWS;
-  p.n_img = n; p.relu = 1; p.desc_base_offset = ctx->opt_desc_base_offset;
+  p.n_img = n; p.desc_base_offset = ctx->opt_desc_base_offset;
+  p.dbg = nullptr;
+  p.epi_variant = ctx->opt_epi_variant;
+  if (ctx->opt_conv_dbg) {                   // bring-up: per-CTA cycle counters, printed after the launch
+    VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&p.dbg), (size_t)ctx->sm_count * 64));
+    VEX_CUDA(ctx, cudaMemsetAsync(p.dbg, 0, (size_t)ctx->sm_count * 64, s));
+  }
   const long long total = (long long)p.tiles_x * p.tiles_y * n;
   if (total > 0x7fffffffLL) return fail(ctx, VEX_ERR_INVALID, "conv_tc: too many tiles");
-  const unsigned abit = BN == 256 ? 2u : 1u;
+  const unsigned abit = (BN == 256 ? 2u : 1u) << (SKIP ? 8 : 0);
   if (!(ctx->attr_mask & abit)) {            // per device, hence per ctx
-    VEX_CUDA(ctx, cudaFuncSetAttribute(convtc::conv3x3_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    VEX_CUDA(ctx, cudaFuncSetAttribute(convtc::conv3x3_tc_kernel<BN, SKIP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        C::SMEM));
     ctx->attr_mask |= abit;
   }
   dim3 grid((unsigned)std::min<long long>(total, ctx->sm_count), L.cout / BN);
-  convtc::conv3x3_tc_kernel<BN><<<grid, convtc::NTHREADS, C::SMEM, s>>>(amap, p);
+  convtc::conv3x3_tc_kernel<BN, SKIP><<<grid, convtc::NTHREADS, C::SMEM, s>>>(amap, p);
   ctx->launches++;
   VEX_CUDA(ctx, cudaGetLastError());
+  if (p.dbg) {
+    std::vector<long long> h((size_t)ctx->sm_count * 8);
+    VEX_CUDA(ctx, cudaStreamSynchronize(s));
+    VEX_CUDA(ctx, cudaMemcpy(h.data(), p.dbg, h.size() * 8, cudaMemcpyDeviceToHost));
+    cudaFree(p.dbg);
+    double a[6] = {0, 0, 0, 0, 0, 0};
+    for (unsigned b = 0; b < grid.x; ++b)
+      for (int i = 0; i < 6; ++i) a[i] += (double)h[(size_t)b * 8 + i] / grid.x;
+    const double items = (double)total / grid.x;
+    fprintf(stderr, "[conv_dbg] cin=%d cout=%d bn=%d items/cta=%.1f cycles/item: total=%.0f mma_wait_acc=%.0f "
+                    "mma_wait_a=%.0f mma_wait_w=%.0f | epi_wait_full=%.0f epi_work=%.0f\n",
+            L.cin, L.cout, BN, items, a[0] / items, a[1] / items, a[2] / items, a[3] / items, a[4] / items,
+            a[5] / items);
+  }
   return VEX_OK;
 }
 
 int run_tc(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfloat16* out,
            const __nv_bfloat16* skip, int n, int H, int W, cudaStream_t s) {
-  return L.bn == 256 ? launch_tc<256>(ctx, L, in, out, skip, n, H, W, s)
-                     : launch_tc<128>(ctx, L, in, out, skip, n, H, W, s);
+  if (skip)
+    return L.bn == 256 ? launch_tc<256, true>(ctx, L, in, out, skip, n, H, W, s)
+                       : launch_tc<128, true>(ctx, L, in, out, skip, n, H, W, s);
+  return L.bn == 256 ? launch_tc<256, false>(ctx, L, in, out, skip, n, H, W, s)
+                     : launch_tc<128, false>(ctx, L, in, out, skip, n, H, W, s);
 }
 
 // rows x (nchunk x 64) bf16 matrix -> [nchunk] slices of rows x 128 B in the SWIZZLE_128B K-major image

@@ -11,8 +11,8 @@
 // M index runs over the flat [row][32] grid; the last two columns of each row are computed on wrapped data
 // and discarded (30 valid output columns per 32: 6.25 % redundant MMA work, zero redundant loads).
 //
-// CTA = 6 warps: warp 0 TMA producer (1 lane), warp 1 MMA issuer (1 lane) + TMEM owner, warps 2-5 epilogue
-// (TMEM lane quarter = warp & 3).  TMEM: all 512 columns = NACC accumulators of 128 pixels x BN channels.
+// CTA = 10 warps: warp 0 TMA producer (1 lane), warp 1 MMA issuer (1 lane) + TMEM owner, warps 2-9 epilogue
+// (TMEM lane quarter = warp & 3; two warps per quarter split the 32-column groups).  TMEM: all 512 columns = NACC accumulators of 128 pixels x BN channels.
 // Persistent grid; work item = (image, 16- or 8-row x 30-column tile).
 #pragma once
 
@@ -25,7 +25,7 @@ constexpr int PITCH = 32;     // pixels per smem tile row (30 valid outputs + 2 
 constexpr int TILE_W = 30;
 constexpr int KC = 64;        // channels per K chunk = one 128 B swizzle row
 constexpr int SA = 2;         // activation stages
-constexpr int NTHREADS = 192;
+constexpr int NTHREADS = 320;    // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
 
 template <int BN>
 struct Cfg {
@@ -37,7 +37,8 @@ struct Cfg {
   static constexpr int SW = 4;
   static constexpr int BAR_OFF = SA * A_STAGE + SW * W_STAGE;
   static constexpr int BIAS_OFF = BAR_OFF + 256;
-  static constexpr int SMEM = BIAS_OFF + BN * 4 + 1024; // + alignment slack
+  static constexpr int STAGE_OFF = BIAS_OFF + BN * 4;   // 8 epilogue warps x 2 KB transpose stage
+  static constexpr int SMEM = STAGE_OFF + 8 * 2048 + 1024; // + alignment slack
 };
 
 struct Params {
@@ -47,11 +48,12 @@ struct Params {
   const __nv_bfloat16* skip;  // NHWC [n][H][W][Cout] added AFTER the ReLU (app.py:292), or nullptr
   int H, W, NC, Cout;     // NC = Cin / 64
   int tiles_x, tiles_y, n_img;
-  int relu;
   int desc_base_offset;   // debug knob, see ptx::smem_desc_sw128
+  int epi_variant;        // bring-up timing probes (WRONG RESULTS): 1 = no global stores, 2 = no tcgen05.ld, 4 = no skip loads
+  long long* dbg;         // optional [gridDim.x][8] cycle counters (MMA thread: total, wait_acc, wait_a, wait_w; epilogue: wait_full, work)
 };
 
-template <int BN>
+template <int BN, bool SKIP>
 __global__ void __launch_bounds__(NTHREADS, 1)
 conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
   using C = Cfg<BN>;
@@ -79,7 +81,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
     for (int i = 0; i < SA; ++i) { ptx::mbar_init(a_full + 8 * i, 1); ptx::mbar_init(a_empty + 8 * i, 1); }
     for (int i = 0; i < C::SW; ++i) { ptx::mbar_init(w_full + 8 * i, 1); ptx::mbar_init(w_empty + 8 * i, 1); }
     ptx::mbar_init(acc_full, 1);
-    ptx::mbar_init(acc_empty, 4);
+    ptx::mbar_init(acc_empty, 8);
     ptx::fence_mbar_init();
     ptx::prefetch_tensormap(&amap);
   }
@@ -122,14 +124,23 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
     if (lane == 0) {
       constexpr uint32_t idesc = ptx::idesc_bf16_f32(128, BN);
       uint32_t sa = 0, pa = 0, sw = 0, pw = 0, pacc = 0;
+      long long t_acc = 0, t_a = 0, t_w = 0, t0 = 0, t1;
+      const bool dbg = p.dbg != nullptr;
+      const long long t_begin = dbg ? clock64() : 0;
       for (int it = blockIdx.x; it < total; it += gridDim.x) {
-        ptx::mbar_wait(acc_empty, pacc ^ 1);            // epilogue has drained the previous item
+        if (dbg) t0 = clock64();
+        ptx::mbar_wait(acc_empty, pacc);                // accumulators drained and re-initialised with the bias
+        if (dbg) { t1 = clock64(); t_acc += t1 - t0; }
         ptx::tc_fence_after();
         for (int c = 0; c < p.NC; ++c) {
+          if (dbg) t0 = clock64();
           ptx::mbar_wait(a_full + 8 * sa, pa);
+          if (dbg) { t1 = clock64(); t_a += t1 - t0; }
           const uint32_t abase = a_stage0 + sa * C::A_STAGE;
           for (int t = 0; t < 9; ++t) {
+            if (dbg) t0 = clock64();
             ptx::mbar_wait(w_full + 8 * sw, pw);
+            if (dbg) { t1 = clock64(); t_w += t1 - t0; }
             ptx::tc_fence_after();
             const uint32_t wbase = w_stage0 + sw * C::W_STAGE;
             const uint32_t tap_off = ((t / 3) * PITCH + (t % 3)) * 128;
@@ -140,7 +151,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
                 const uint64_t ad = ptx::smem_desc_sw128(abase + tap_off + a * (128 * 128) + k * 32,
                                                          p.desc_base_offset);
                 const uint64_t bd = ptx::smem_desc_sw128(wbase + k * 32, 0);
-                ptx::mma_bf16_ss(tmem + a * BN, ad, bd, idesc, (c | t | k) != 0);
+                ptx::mma_bf16_ss(tmem + a * BN, ad, bd, idesc, 1u);   // TMEM was pre-loaded with the bias
               }
             }
             ptx::tc_commit(w_empty + 8 * sw);           // slice consumed once these MMAs retire
@@ -152,65 +163,137 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
         ptx::tc_commit(acc_full);
         pacc ^= 1;
       }
+      if (dbg && blockIdx.y == 0) {
+        long long* d = p.dbg + (size_t)blockIdx.x * 8;
+        d[0] = clock64() - t_begin; d[1] = t_acc; d[2] = t_a; d[3] = t_w;
+      }
     }
   } else {
     // ============================== epilogue ==================================
-    const int q = warp & 3;                             // TMEM lane quarter this warp may read
+    // 8 warps: TMEM lane quarter q = warp & 3 (hardware rule), column-group parity `par` = (warp-2) >> 2.
+    // Units (accumulator a, 32-column group g) are software-pipelined: the tcgen05.ld (and the skip loads)
+    // of unit u+1 are in flight while unit u is converted and stored.  The epilogue is instruction-issue
+    // bound (measured), so: the folded bias lives IN the accumulator (each drained unit is immediately
+    // re-initialised with tcgen05.st, MMAs always accumulate), ReLU is fused into cvt.rn.relu.bf16x2, and
+    // the skip path is a template parameter.
+    const int q = warp & 3, par = (warp - 2) >> 2;
+    uint8_t* stage = sm + C::STAGE_OFF + (warp - 2) * 2048;
+    constexpr int GPW = BN / 64;                        // column groups per warp per accumulator
+    constexpr int UNITS = C::NACC * GPW;
+    const uint32_t tq = tmem + ((uint32_t)(q * 32) << 16);
+    auto store_bias = [&](int a, int g) {
+      uint32_t bv[32];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint4 t = *reinterpret_cast<const uint4*>(bias_s + g * 32 + j * 4);
+        bv[4 * j] = t.x; bv[4 * j + 1] = t.y; bv[4 * j + 2] = t.z; bv[4 * j + 3] = t.w;
+      }
+      ptx::tmem_st_32x32(tq + a * BN + g * 32, bv);
+    };
+#pragma unroll
+    for (int u = 0; u < UNITS; ++u) store_bias(u / GPW, (u % GPW) * 2 + par);
+    ptx::tmem_st_wait();
+    ptx::tc_fence_before();
+    __syncwarp();
+    if (lane == 0) ptx::mbar_arrive(acc_empty);         // completion 0: accumulators hold the bias
+    // Global accesses go through a 2 KB per-warp stage so that one instruction covers 8 pixels x 64 B
+    // (lane l <-> pixel 8i + (l >> 2), 16-byte chunk l & 3) instead of 32 lines at a 256 B stride.
+    // Stage layout: pixel px at px*64, chunk j at (j ^ ((px >> 1) & 3)) * 16: conflict-free both ways.
+    const int cpx = lane >> 2, cch = lane & 3;
+    int own_off[4], co_off[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      own_off[j] = lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4);
+      const int px = 8 * j + cpx;
+      co_off[j] = px * 64 + ((cch ^ ((px >> 1) & 3)) << 4);
+    }
     uint32_t pacc = 0;
     for (int it = blockIdx.x; it < total; it += gridDim.x) {
       const int txi = it % p.tiles_x, r = it / p.tiles_x;
       const int tyi = r % p.tiles_y, n = r / p.tiles_y;
-      const int x = txi * TILE_W + lane;
+      const int x0 = txi * TILE_W;
+      const int ybase = tyi * C::ROWS + q;              // accumulator row m = a*128 + q*32 + lane -> y = ybase + 4a
+      // element offset of (pixel (ybase, x0 + cpx), channel nb*BN + cch*8); + 8*i pixels, + 4a rows, + g*32 channels
+      const size_t e0 = (((size_t)n * p.H + ybase) * p.W + x0 + cpx) * p.Cout + nb * BN + cch * 8;
+      const size_t acc_stride = (size_t)4 * p.W * p.Cout;
+      const size_t px8 = (size_t)8 * p.Cout;
+      bool pxok[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) pxok[i] = (8 * i + cpx < TILE_W) && (x0 + 8 * i + cpx < p.W);
+      uint32_t v[2][32];
+      uint4 sk[2][4];
+      auto issue = [&](int u, int buf) {
+        const int a = u / GPW, g = (u % GPW) * 2 + par;
+        if (!(p.epi_variant & 2)) ptx::tmem_ld_32x32(tq + a * BN + g * 32, v[buf]);
+        if (SKIP && !(p.epi_variant & 4)) {
+          const bool yok = ybase + 4 * a < p.H;
+          const __nv_bfloat16* sp = p.skip + e0 + a * acc_stride + g * 32;
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            sk[buf][i] = (yok && pxok[i]) ? __ldg(reinterpret_cast<const uint4*>(sp + i * px8)) : make_uint4(0, 0, 0, 0);
+        }
+      };
+      const bool dbg = p.dbg != nullptr && warp == 2 && lane == 0 && blockIdx.y == 0;
+      long long e0c = 0, e1c = 0;
+      if (dbg) e0c = clock64();
       ptx::mbar_wait(acc_full, pacc);
+      if (dbg) { e1c = clock64(); p.dbg[(size_t)blockIdx.x * 8 + 4] += e1c - e0c; }
       pacc ^= 1;
       ptx::tc_fence_after();
-#pragma unroll 1
-      for (int a = 0; a < C::NACC; ++a) {
-        const int y = tyi * C::ROWS + a * 4 + q;        // accumulator row m = a*128 + q*32 + lane
-        const bool valid = (lane < TILE_W) && (x < p.W) && (y < p.H);
-        const size_t pix = ((size_t)n * p.H + y) * p.W + x;
-        __nv_bfloat16* optr = p.out + pix * p.Cout + nb * BN;
-        const __nv_bfloat16* sptr = p.skip ? p.skip + pix * p.Cout + nb * BN : nullptr;
-#pragma unroll 1
-        for (int g = 0; g < BN / 32; ++g) {
-          uint32_t v[32];
-          ptx::tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + a * BN + g * 32, v);
-          ptx::tmem_ld_wait();
-          if (valid) {
-            float f[32];
+      issue(0, 0);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              f[j] = __uint_as_float(v[j]) + bias_s[g * 32 + j];
-              if (p.relu) f[j] = fmaxf(f[j], 0.0f);
+      for (int u = 0; u < UNITS; ++u) {
+        const int buf = u & 1;
+        const int a = u / GPW, g = (u % GPW) * 2 + par;
+        ptx::tmem_ld_wait();
+        store_bias(a, g);                               // unit drained into registers: re-arm it for the next item
+        if (u + 1 < UNITS) issue(u + 1, buf ^ 1);
+        const bool yok = ybase + 4 * a < p.H;
+        if (SKIP) {
+          uint4 sv[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) *reinterpret_cast<uint4*>(stage + co_off[i]) = sk[buf][i];
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 4; ++j) sv[j] = *reinterpret_cast<const uint4*>(stage + own_off[j]);
+          __syncwarp();
+#pragma unroll
+          for (int j4 = 0; j4 < 4; ++j4) {              // relu(acc) + x1, the skip AFTER the ReLU (app.py:292)
+            const uint32_t w[4] = {sv[j4].x, sv[j4].y, sv[j4].z, sv[j4].w};
+            uint32_t o[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float lo = fmaxf(__uint_as_float(v[buf][j4 * 8 + 2 * e]), 0.f) + ptx::bf16lo_to_f32(w[e]);
+              const float hi = fmaxf(__uint_as_float(v[buf][j4 * 8 + 2 * e + 1]), 0.f) + ptx::bf16hi_to_f32(w[e]);
+              o[e] = ptx::pack_bf16x2(lo, hi);
             }
-            if (sptr) {
-              const uint4* s4 = reinterpret_cast<const uint4*>(sptr + g * 32);
+            *reinterpret_cast<uint4*>(stage + own_off[j4]) = make_uint4(o[0], o[1], o[2], o[3]);
+          }
+        } else {
 #pragma unroll
-              for (int j4 = 0; j4 < 4; ++j4) {
-                const uint4 s = __ldg(s4 + j4);
-                const uint32_t w[4] = {s.x, s.y, s.z, s.w};
+          for (int j4 = 0; j4 < 4; ++j4) {
+            uint32_t o[4];
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  f[j4 * 8 + 2 * e] += ptx::bf16lo_to_f32(w[e]);
-                  f[j4 * 8 + 2 * e + 1] += ptx::bf16hi_to_f32(w[e]);
-                }
-              }
-            }
-            uint4* o4 = reinterpret_cast<uint4*>(optr + g * 32);
-#pragma unroll
-            for (int j4 = 0; j4 < 4; ++j4) {
-              uint4 o;
-              o.x = ptx::pack_bf16x2(f[j4 * 8 + 0], f[j4 * 8 + 1]);
-              o.y = ptx::pack_bf16x2(f[j4 * 8 + 2], f[j4 * 8 + 3]);
-              o.z = ptx::pack_bf16x2(f[j4 * 8 + 4], f[j4 * 8 + 5]);
-              o.w = ptx::pack_bf16x2(f[j4 * 8 + 6], f[j4 * 8 + 7]);
-              o4[j4] = o;
-            }
+            for (int e = 0; e < 4; ++e)
+              o[e] = ptx::pack_relu_bf16x2(__uint_as_float(v[buf][j4 * 8 + 2 * e]), __uint_as_float(v[buf][j4 * 8 + 2 * e + 1]));
+            *reinterpret_cast<uint4*>(stage + own_off[j4]) = make_uint4(o[0], o[1], o[2], o[3]);
           }
         }
+        __syncwarp();
+        {
+          __nv_bfloat16* op = p.out + e0 + a * acc_stride + g * 32;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint4 o = *reinterpret_cast<const uint4*>(stage + co_off[i]);
+            if (yok && pxok[i] && !(p.epi_variant & 1)) *reinterpret_cast<uint4*>(op + i * px8) = o;
+          }
+        }
+        __syncwarp();
       }
+      ptx::tmem_st_wait();
       ptx::tc_fence_before();
       __syncwarp();
+      if (dbg) p.dbg[(size_t)blockIdx.x * 8 + 5] += clock64() - e1c;
       if (lane == 0) ptx::mbar_arrive(acc_empty);
     }
   }

@@ -218,6 +218,8 @@ int vex_set_option(vex_ctx* ctx, const char* name, int value) {
   else if (!strcmp(name, "ws_budget_mb")) slot = &ctx->opt_ws_budget_mb;
   else if (!strcmp(name, "profile")) slot = &ctx->opt_profile;
   else if (!strcmp(name, "thin_tc")) slot = &ctx->opt_thin_tc;
+  else if (!strcmp(name, "conv_dbg")) slot = &ctx->opt_conv_dbg;
+  else if (!strcmp(name, "epi_variant")) slot = &ctx->opt_epi_variant;
   if (!slot) return vex::fail(ctx, VEX_ERR_INVALID, std::string("vex_set_option: unknown ") + name);
   const int prev = *slot;
   *slot = value;

@@ -38,6 +38,8 @@ struct vex_ctx {
   int opt_force_generic_bicubic = 0;
   int opt_conv3_bn = 256;         // Cout block of conv3 on the tensor cores (128 or 256)
   int opt_thin_tc = 1;            // thin layers on tcgen05 (thin_tc.cuh); 0 = fp32 CUDA-core kernels (cnn_small.cuh)
+  int opt_epi_variant = 0;        // bring-up timing probes for the conv_tc epilogue (produce wrong results)
+  int opt_conv_dbg = 0;           // bring-up: print per-role cycle counters of every conv_tc launch (synchronises)
   int opt_profile = 0;            // record per-layer events in cnn_forward (vex_cnn_profile_ms)
   int opt_ws_budget_mb = 49152;   // CNN activation workspace cap; larger batches run in sub-batches
 };

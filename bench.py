@@ -230,9 +230,9 @@ def gpu_workload(workload, enh, args, world, rank, local, warmup, peaks, torch, 
     e2e_value = world * e2e_frames * e2e_steps / float(dt.item())
 
     if workload == "bicubic":
-        kern_ms = float(np.mean(step_ms))                    # the step IS one launch of bicubic2x_tile_kernel
+        kern_ms = float(np.mean(step_ms))                    # the step IS one launch of bicubic2x_strip_kernel
         achieved = BICUBIC_BYTES_PER_FRAME * fps_step / (kern_ms / 1e3) / 1e9
-        roof = {"bound": "hbm", "kernel": "bicubic2x_tile_kernel", "achieved": achieved, "peak": peaks["hbm_gbs"],
+        roof = {"bound": "hbm", "kernel": "bicubic2x_strip_kernel", "achieved": achieved, "peak": peaks["hbm_gbs"],
                 "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks["source"],
                 "algorithmic_bytes_per_launch": BICUBIC_BYTES_PER_FRAME * fps_step, "launch_ms": kern_ms}
         dtype = "u8"

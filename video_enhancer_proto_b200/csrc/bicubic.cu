@@ -1,4 +1,4 @@
-// 2x bicubic upscale, uint8 HWC -> uint8 HWC, for sm_100a.  HBM-bound: 3*H*W bytes in, 12*H*W out.
+// 2x bicubic upscale, uint8 HWC -> uint8 HWC, for sm_100a.  Algorithmic HBM traffic: 3*H*W bytes in, 12*H*W out.
 //
 // Replaces GPUVideoEnhancer._enhance_frame_cpu_fallback (reference app.py:359-385):
 //   F.interpolate(x/255, scale_factor=2, mode='bicubic', align_corners=False) -> clip(*255) -> uint8
@@ -7,31 +7,63 @@
 // Math.  out index d -> source s=(d+0.5)/2-0.5, i=floor(s), t=s-i in {0.75 (d even), 0.25 (d odd)};
 // taps i-1..i+2 clamped to the image (border replicate); Keys cubic with A=-0.75 gives the exact
 // dyadic weights  t=0.75: [-9, 67, 225, -27]/256   t=0.25: [-27, 225, 67, -9]/256.
-// Separable (x then y).  All products are carried as integers (weights*256) in fp32: the horizontal
-// sum is < 2^17 and every in-range vertical sum is < 2^24, so fp32 FMAs are EXACT; the result is the
-// mathematically exact value of the interpolant, scaled by 65536.  round_mode 0 truncates
-// (app.py:376 astype(uint8) after clip), round_mode 1 rounds half up (cv2's fixed-point rounding).
-// The reference's float path differs from the exact value only by fp32 rounding at integer
-// boundaries (<= 1 LSB, see tests/test_bicubic_oracle.py).
+// Separable (x then y), carried as integers in fp32: the horizontal sums are integers < 2^17, the
+// vertical sums are multiples of 2^-16 below 2^8, so every FMA is exact as long as the running sum
+// stays below 2^24 units.  The vertical chain adds the 225-tap first, then the two negative taps,
+// then the 67-tap, so for ordinary content the running sum never exceeds the final value; it can
+// leave the exact range only when a near-saturated 2-px stripe row sits next to rows of the inverse
+// stripe (negative h on a negative-weight tap), and then the result is perturbed by 2^-16 LSB,
+// which is visible only on an exact tie.  round_mode 0 truncates (app.py:376 astype(uint8) after clip),
+// round_mode 1 rounds half up (cv2's fixed-point rounding).  The reference's float path differs from
+// the exact value only by fp32 rounding at integer boundaries (<= 1 LSB, tests/test_bicubic_gpu.py).
+//
+// Why it looks like this.  With 16 taps per output byte and 4 output bytes per input byte the kernel is
+// CUDA-core issue-bound long before it is HBM-bound (measured on B200, tools/ubench/pipes.cu: FFMA ~90,
+// FFMA2 63 x 2 lanes, ALU-pipe ops 63, F2I 16 (!), F2IP.U8.F32 66 x 2 lanes per clock per SM; at 80 % of HBM
+// an SM must emit ~15 output bytes per clock, i.e. < 9 issue slots per byte).  So:
+//   * all arithmetic is packed fp32x2 (FFMA2): one thread runs two column strips in the two lanes;
+//   * uint8 -> fp32 is ONE byte-permute: PRMT builds the float 2^15 + p, and the bias (256 * 2^15 = 2^23)
+//     is removed exactly by the addend of the first FMA of the horizontal chain (weights sum to 256);
+//   * the even and the odd output of a tap window share the 225-tap product: 7 FMAs per output pair;
+//   * fp32 -> uint8 with clamp and pack is F2IP.U8.F32.TRUNC: two values per instruction
+//     (cvt.rzi.s32.f32 + cvt.pack.sat.u8.s32 fuse in ptxas), rounding folded into the horizontal bias;
+//   * a thread walks down a strip of rows keeping a 4-row window of horizontal sums in registers
+//     (row halo cost 4/R), input rows come straight from global/L1 one row ahead, output rows are
+//     staged per warp in shared memory and leave as 16-byte fully coalesced stores (768 B per warp row).
 #include "vex_internal.cuh"
+
+#include <algorithm>
 
 namespace vex {
 namespace {
 
-constexpr int TPX = 128;       // input pixels per tile in x
-constexpr int TR = 32;         // input rows per tile
-constexpr int RG = 8;          // input rows per row group (one warp pair)
-constexpr int NTHREADS = 256;  // 64 column groups (2 input px each) x 4 row groups
-constexpr int IN_VECS = (TPX * 3 + 32) / 16;   // 26 x 16B per smem row: [X0*3-16, X0*3+400)
-constexpr int PITCH = IN_VECS * 16;            // 416
-constexpr int SROWS = TR + 4;                  // rows R0-2 .. R0+TR+1
-constexpr int STAGE_BYTES = 2 * 384;           // per warp: 2 output rows x 64 in-px x 6 B
+typedef unsigned long long u64;
 
-__device__ __forceinline__ uint4 ldg_nc_v4(const void* p) {
-  uint4 r;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-               : "l"(p));
+__device__ __forceinline__ u64 pk(uint32_t lo, uint32_t hi) {
+  u64 r;
+  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpk(u64 v, float& lo, float& hi) {
+  asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ u64 bc(float w) {   // broadcast constant to both lanes (ptxas folds it to an immediate)
+  const uint32_t u = __float_as_uint(w);
+  return pk(u, u);
+}
+__device__ __forceinline__ u64 fma2(u64 a, float w, u64 c) {
+  u64 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(bc(w)), "l"(c));
+  return d;
+}
+__device__ __forceinline__ u64 mul2(u64 a, float w) {
+  u64 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(bc(w)));
+  return d;
+}
+__device__ __forceinline__ uint32_t ldg_nc(const uint32_t* p) {
+  uint32_t r;
+  asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(r) : "l"(p));
   return r;
 }
 __device__ __forceinline__ void stg_v4(void* p, const uint4& v) {
@@ -39,28 +71,180 @@ __device__ __forceinline__ void stg_v4(void* p, const uint4& v) {
                "r"(v.z), "r"(v.w)
                : "memory");
 }
+// four floats (already in [0,256) scale) -> 4 clamped, truncated bytes, b0 at the lowest address.
+// cvt.pack: d = (c << 16) | sat(a) << 8 | sat(b)   (measured, tools/ubench/packtest.cu)
+__device__ __forceinline__ uint32_t pack4(float b0, float b1, float b2, float b3) {
+  const int i0 = __float2int_rz(b0), i1 = __float2int_rz(b1), i2 = __float2int_rz(b2), i3 = __float2int_rz(b3);
+  uint32_t hi, r;
+  asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, 0;" : "=r"(hi) : "r"(i3), "r"(i2));
+  asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(i1), "r"(i0), "r"(hi));
+  return r;
+}
 
-__device__ __forceinline__ float byte_f(uint32_t w, int k) { return (float)((w >> (8 * k)) & 0xffu); }
+constexpr int STRIP_WARPS = 4;            // warps per block, each fully independent
+constexpr int WARP_PX = 128;              // input pixels per warp row segment: lane = 4 px = 2 strips x 2 px
+constexpr int STAGE_ROW = WARP_PX * 6;    // 768 output bytes per warp per output row
+constexpr float VS = 1.0f / 65536.0f;     // vertical weights carry the 2^-16 so the sum lands in [0,256)
 
-// horizontal pass for one smem row: 18 bytes (6 px) -> 12 values (4 out px x 3 ch), scaled by 256
-__device__ __forceinline__ void hpass(const uint8_t* srow, int wi, int sh, float (&h)[12]) {
-  const uint32_t* wp = reinterpret_cast<const uint32_t*>(srow) + wi;
-  uint32_t w[6];
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t d;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+  return d;
+}
+// byte k of w -> the float 2^15 + byte (byte lands in mantissa bits 8..15 of 0x47000000)
+template <int IDX>
+__device__ __forceinline__ uint32_t magic_f(const uint32_t (&raw)[7]) {
+  return prmt(raw[IDX >> 2], 0x47000000u, 0x7404u | ((IDX & 3) << 4));
+}
+
+// One input row of one warp segment.  raw[] = the 28 bytes [12*lane-8, 12*lane+20) of the row segment:
+// pixels 4*lane-2 .. 4*lane+5 start at byte index 2.  Lane = strip A (px 4l, 4l+1; fp32x2 low lane) +
+// strip B (px 4l+2, 4l+3; high lane).  Produces the 12 horizontal sums per strip (out px 2u+e, channel c
+// at j = (2u+e)*3+c), and, if EMIT, output rows 2i and 2i+1 of input row i whose window is
+// S[(K+2)&3] = row i-2, S[(K+3)&3] = i-1, S[K] = i, S[(K+1)&3] = i+1, new = i+2.
+template <int ROUND, int K, bool EMIT>
+__device__ __forceinline__ void strip_step(u64 (&S)[4][12], uint32_t (&raw)[7], bool left, bool right,
+                                           uint8_t* stage, uint8_t* orow, size_t out_row_bytes,
+                                           bool store_ok, int lane, int valid_vecs) {
+  // border replicate in x on the raw bytes (app.py:372 -> ATen clamps tap indices)
+  if (left) {            // px -2, -1 <- px 0 : bytes 2..7 <- bytes 8,9,10
+    raw[0] = prmt(raw[2], raw[2], 0x1000u);
+    raw[1] = prmt(raw[2], raw[2], 0x2102u);
+  }
+  if (right) {           // px +4, +5 <- px 3 : bytes 20..25 <- bytes 17,18,19
+    raw[5] = prmt(raw[4], raw[4], 0x1321u);
+    raw[6] = prmt(raw[4], raw[4], 0x0032u);
+  }
+  u64 hn[12];
+  {
+    u64 P[6][3];
+#define VEX_CONV(T, C) P[T][C] = pk(magic_f<3 * T + C + 2>(raw), magic_f<3 * T + C + 8>(raw));
+#define VEX_CONV3(T) VEX_CONV(T, 0) VEX_CONV(T, 1) VEX_CONV(T, 2)
+    VEX_CONV3(0) VEX_CONV3(1) VEX_CONV3(2) VEX_CONV3(3) VEX_CONV3(4) VEX_CONV3(5)
+#undef VEX_CONV3
+#undef VEX_CONV
+    // sum of weights = 256, so the 2^15 conversion bias contributes exactly 2^23; round-half-up = +128 here
+    const u64 bias = bc(-8388608.0f + (ROUND ? 128.0f : 0.0f));
 #pragma unroll
-  for (int j = 0; j < 5; ++j) w[j] = wp[j];
-  w[5] = 0;
+    for (int u = 0; u < 2; ++u) {
 #pragma unroll
-  for (int j = 0; j < 5; ++j) w[j] = __funnelshift_r(w[j], w[j + 1], sh);
-  float p[18];
+      for (int c = 0; c < 3; ++c) {
+        const u64 X = fma2(P[u + 2][c], 225.f, bias);
+        hn[(2 * u) * 3 + c] = fma2(P[u + 1][c], 67.f, fma2(P[u + 3][c], -27.f, fma2(P[u][c], -9.f, X)));
+        hn[(2 * u + 1) * 3 + c] = fma2(P[u + 3][c], 67.f, fma2(P[u + 4][c], -9.f, fma2(P[u + 1][c], -27.f, X)));
+      }
+    }
+  }
+  if constexpr (!EMIT) {
 #pragma unroll
-  for (int k = 0; k < 18; ++k) p[k] = byte_f(w[k >> 2], k & 3);
+    for (int j = 0; j < 12; ++j) S[(K + 2) & 3][j] = hn[j];
+  } else {
+  float ea[12], eb[12], oa[12], ob[12];
 #pragma unroll
-  for (int c = 0; c < 3; ++c) {
-    // even out px (t=0.75) of input px q0+2 and q0+3 ; odd out px (t=0.25)
-    h[0 + c] = -9.f * p[0 + c] + 67.f * p[3 + c] + 225.f * p[6 + c] - 27.f * p[9 + c];
-    h[3 + c] = -27.f * p[3 + c] + 225.f * p[6 + c] + 67.f * p[9 + c] - 9.f * p[12 + c];
-    h[6 + c] = -9.f * p[3 + c] + 67.f * p[6 + c] + 225.f * p[9 + c] - 27.f * p[12 + c];
-    h[9 + c] = -27.f * p[6 + c] + 225.f * p[9 + c] + 67.f * p[12 + c] - 9.f * p[15 + c];
+  for (int j = 0; j < 12; ++j) {
+    const u64 A = S[(K + 2) & 3][j], B = S[(K + 3) & 3][j], C = S[K][j], D = S[(K + 1) & 3][j];
+    const u64 X = mul2(C, 225.f * VS);
+    const u64 E = fma2(B, 67.f * VS, fma2(D, -27.f * VS, fma2(A, -9.f * VS, X)));
+    const u64 O = fma2(D, 67.f * VS, fma2(hn[j], -9.f * VS, fma2(B, -27.f * VS, X)));
+    S[(K + 2) & 3][j] = hn[j];
+    unpk(E, ea[j], eb[j]);
+    unpk(O, oa[j], ob[j]);
+  }
+  // lane's 24 output bytes per row: strip A (12 B) then strip B (12 B)
+  uint2* se = reinterpret_cast<uint2*>(stage + 24 * lane);
+  uint2* so = reinterpret_cast<uint2*>(stage + STAGE_ROW + 24 * lane);
+  {
+    const uint32_t a0 = pack4(ea[0], ea[1], ea[2], ea[3]), a1 = pack4(ea[4], ea[5], ea[6], ea[7]),
+                   a2 = pack4(ea[8], ea[9], ea[10], ea[11]);
+    const uint32_t b0 = pack4(eb[0], eb[1], eb[2], eb[3]), b1 = pack4(eb[4], eb[5], eb[6], eb[7]),
+                   b2 = pack4(eb[8], eb[9], eb[10], eb[11]);
+    se[0] = make_uint2(a0, a1);
+    se[1] = make_uint2(a2, b0);
+    se[2] = make_uint2(b1, b2);
+  }
+  {
+    const uint32_t a0 = pack4(oa[0], oa[1], oa[2], oa[3]), a1 = pack4(oa[4], oa[5], oa[6], oa[7]),
+                   a2 = pack4(oa[8], oa[9], oa[10], oa[11]);
+    const uint32_t b0 = pack4(ob[0], ob[1], ob[2], ob[3]), b1 = pack4(ob[4], ob[5], ob[6], ob[7]),
+                   b2 = pack4(ob[8], ob[9], ob[10], ob[11]);
+    so[0] = make_uint2(a0, a1);
+    so[1] = make_uint2(a2, b0);
+    so[2] = make_uint2(b1, b2);
+  }
+  __syncwarp();
+  if (store_ok) {
+    // 96 x 16 B (2 rows x 48): three fully coalesced passes
+    const uint4* sv = reinterpret_cast<const uint4*>(stage);
+    if (lane < valid_vecs) stg_v4(orow + 16 * lane, sv[lane]);
+    {
+      const int row = lane >> 4, vv = row ? lane - 16 : lane + 32;
+      if (vv < valid_vecs) stg_v4(orow + row * out_row_bytes + 16 * vv, sv[row * 48 + vv]);
+    }
+    if (lane + 16 < valid_vecs) stg_v4(orow + out_row_bytes + 16 * (lane + 16), sv[48 + 16 + lane]);
+  }
+  }
+}
+
+// Fast path: W % 16 == 0 (3W and 6W multiples of 16) and 16B-aligned buffers.  R = rows per strip (multiple of 4).
+template <int ROUND>
+__global__ void __launch_bounds__(STRIP_WARPS * 32, 3)
+bicubic2x_strip_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int H, int W, int R,
+                       int wpr, int nstrips, int total_warps) {
+  __shared__ __align__(16) uint8_t s_stage[STRIP_WARPS][2][2 * STAGE_ROW];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int gw = blockIdx.x * STRIP_WARPS + warp;
+  if (gw >= total_warps) return;
+  const int xw = gw % wpr;
+  const int t = gw / wpr;
+  const int strip = t % nstrips, f = t / nstrips;
+  const int r0 = strip * R;
+  const int px0 = xw * WARP_PX + 4 * lane;
+  const bool valid = px0 < W;
+  const bool left = px0 == 0, right = px0 + 4 == W;
+  const size_t in_row = (size_t)W * 3, out_row = (size_t)W * 6;
+  const uint8_t* fin = in + (size_t)f * H * in_row + ((ptrdiff_t)px0 * 3 - 8);
+  uint8_t* fout = out + (size_t)f * 2 * H * out_row + (size_t)xw * STAGE_ROW;
+  const int valid_vecs = min(48, (W - xw * WARP_PX) * 6 / 16);
+  // the two words left of the image / right of the image are never read (they are rebuilt by the replicate)
+  const bool p01 = valid && !left, p234 = valid, p56 = valid && !right;
+
+  auto load_row = [&](int y, uint32_t(&r)[7]) {
+    y = min(max(y, 0), H - 1);
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(fin + (size_t)y * in_row);
+    r[0] = p01 ? ldg_nc(p + 0) : 0u;
+    r[1] = p01 ? ldg_nc(p + 1) : 0u;
+    r[2] = p234 ? ldg_nc(p + 2) : 0u;
+    r[3] = p234 ? ldg_nc(p + 3) : 0u;
+    r[4] = p234 ? ldg_nc(p + 4) : 0u;
+    r[5] = p56 ? ldg_nc(p + 5) : 0u;
+    r[6] = p56 ? ldg_nc(p + 6) : 0u;
+  };
+
+  u64 S[4][12];
+  uint32_t ra[7], rb[7];
+  uint8_t* st0 = s_stage[warp][0];
+  uint8_t* st1 = s_stage[warp][1];
+  load_row(r0 - 2, ra);
+  load_row(r0 - 1, rb);
+  strip_step<ROUND, 0, false>(S, ra, left, right, st0, nullptr, 0, false, lane, 0);
+  load_row(r0, ra);
+  strip_step<ROUND, 1, false>(S, rb, left, right, st0, nullptr, 0, false, lane, 0);
+  load_row(r0 + 1, rb);
+  strip_step<ROUND, 2, false>(S, ra, left, right, st0, nullptr, 0, false, lane, 0);
+  load_row(r0 + 2, ra);
+  strip_step<ROUND, 3, false>(S, rb, left, right, st0, nullptr, 0, false, lane, 0);
+  const int iend = min(r0 + R, H);
+#pragma unroll 1
+  for (int i = r0; i < iend; i += 4) {
+    uint8_t* orow = fout + (size_t)(2 * i) * out_row;
+    load_row(i + 3, rb);
+    strip_step<ROUND, 0, true>(S, ra, left, right, st0, orow, out_row, true, lane, valid_vecs);
+    load_row(i + 4, ra);
+    strip_step<ROUND, 1, true>(S, rb, left, right, st1, orow + 2 * out_row, out_row, i + 1 < iend, lane, valid_vecs);
+    load_row(i + 5, rb);
+    strip_step<ROUND, 2, true>(S, ra, left, right, st0, orow + 4 * out_row, out_row, i + 2 < iend, lane, valid_vecs);
+    load_row(i + 6, ra);
+    strip_step<ROUND, 3, true>(S, rb, left, right, st1, orow + 6 * out_row, out_row, i + 3 < iend, lane, valid_vecs);
   }
 }
 
@@ -69,128 +253,6 @@ __device__ __forceinline__ uint32_t quant(float v) {
   // v = exact value * 65536.  clip to [0,255] then truncate (ROUND=0) or round half up (ROUND=1).
   float s = fmaf(v, 1.0f / 65536.0f, ROUND ? 0.5f : 0.0f);
   return min(__float2uint_rz(s), 255u);   // float->uint conversion clamps negatives to 0
-}
-
-template <int ROUND>
-__device__ __forceinline__ void emit_row(uint8_t* stage_row, int lane, const float (&a)[12],
-                                         const float (&b)[12], const float (&c)[12],
-                                         const float (&d)[12], float w0, float w1, float w2,
-                                         float w3) {
-  uint32_t o[3];
-#pragma unroll
-  for (int j = 0; j < 3; ++j) {
-    uint32_t word = 0;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int e = 4 * j + k;
-      // negatives first keeps every partial sum of an in-range result below 2^24 (exact)
-      float v = w0 * a[e] + w3 * d[e];
-      v = (w1 < w2) ? fmaf(w1, b[e], v) : fmaf(w2, c[e], v);
-      v = (w1 < w2) ? fmaf(w2, c[e], v) : fmaf(w1, b[e], v);
-      word |= quant<ROUND>(v) << (8 * k);
-    }
-    o[j] = word;
-  }
-  uint32_t* sp = reinterpret_cast<uint32_t*>(stage_row) + 3 * lane;
-  sp[0] = o[0];
-  sp[1] = o[1];
-  sp[2] = o[2];
-}
-
-// Fast path: W % 16 == 0 (so 3W and 6W are multiples of 16) and 16B-aligned buffers.
-template <int ROUND>
-__global__ void __launch_bounds__(NTHREADS, 2)
-bicubic2x_tile_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int H, int W) {
-  __shared__ __align__(16) uint8_t s_in[SROWS * PITCH];
-  __shared__ __align__(16) uint8_t s_stage[(NTHREADS / 32) * STAGE_BYTES];
-
-  const int tid = threadIdx.x;
-  const int X0 = blockIdx.x * TPX;
-  const int R0 = blockIdx.y * TR;
-  const size_t in_row_bytes = (size_t)W * 3;
-  const size_t out_row_bytes = (size_t)W * 6;
-  const uint8_t* fin = in + (size_t)blockIdx.z * H * in_row_bytes;
-  uint8_t* fout = out + (size_t)blockIdx.z * (2 * (size_t)H) * out_row_bytes;
-
-  // ---- stage the input tile (+2 px / +2 rows halo) with coalesced 16B loads
-  const int cb0 = X0 * 3 - 16;
-  for (int idx = tid; idx < SROWS * IN_VECS; idx += NTHREADS) {
-    const int rr = idx / IN_VECS, v = idx - rr * IN_VECS;
-    int y = R0 - 2 + rr;
-    y = min(max(y, 0), H - 1);
-    const int cb = cb0 + 16 * v;
-    uint4 val = make_uint4(0, 0, 0, 0);
-    if (cb >= 0 && cb + 16 <= (int)in_row_bytes) val = ldg_nc_v4(fin + (size_t)y * in_row_bytes + cb);
-    *reinterpret_cast<uint4*>(s_in + rr * PITCH + 16 * v) = val;
-  }
-  __syncthreads();
-  // ---- border replicate in x (only tiles touching the left/right image edge)
-  const bool left = (X0 == 0), right = (X0 + TPX + 2 > W);
-  if (left || right) {
-    if (tid < SROWS) {
-      uint8_t* r = s_in + tid * PITCH;
-      if (left) {
-#pragma unroll
-        for (int c = 0; c < 3; ++c) r[10 + c] = r[13 + c] = r[16 + c];
-      }
-      if (right) {
-        const int sb = 16 + (W - 1 - X0) * 3;   // last real pixel
-#pragma unroll
-        for (int c = 0; c < 3; ++c) r[sb + 3 + c] = r[sb + 6 + c] = r[sb + c];
-      }
-    }
-    __syncthreads();
-  }
-
-  // ---- compute: thread = 2 input px (4 out px = 12 B) x RG input rows (2*RG out rows)
-  const int lane = tid & 31, warp = tid >> 5;
-  const int tx = tid & 63, rg = tid >> 6;
-  const int sbase = 10 + 6 * tx;
-  const int wi = sbase >> 2, sh = (sbase & 3) * 8;
-  uint8_t* stage = s_stage + warp * STAGE_BYTES;
-  const int Xw = X0 + 64 * (warp & 1);                 // first input px of this warp
-  const int valid_vecs = min(24, max(0, (W - Xw) * 6 / 16));
-
-  float h0[12], h1[12], h2[12], h3[12], h4[12];
-  const uint8_t* srow = s_in + (rg * RG) * PITCH;
-  hpass(srow + 0 * PITCH, wi, sh, h0);
-  hpass(srow + 1 * PITCH, wi, sh, h1);
-  hpass(srow + 2 * PITCH, wi, sh, h2);
-  hpass(srow + 3 * PITCH, wi, sh, h3);
-#pragma unroll
-  for (int j = 0; j < RG; ++j) {
-    hpass(srow + (j + 4) * PITCH, wi, sh, h4);
-    // out row 2i (t=0.75): rows i-2..i+1 ; out row 2i+1 (t=0.25): rows i-1..i+2
-    emit_row<ROUND>(stage, lane, h0, h1, h2, h3, -9.f, 67.f, 225.f, -27.f);
-    emit_row<ROUND>(stage + 384, lane, h1, h2, h3, h4, -27.f, 225.f, 67.f, -9.f);
-    __syncwarp();
-    const int i = R0 + rg * RG + j;
-    if (i < H) {
-      uint8_t* orow = fout + (size_t)(2 * i) * out_row_bytes + (size_t)Xw * 6;
-      // 48 vectors (2 rows x 24): lanes 0..31 then 0..15
-      {
-        const int v = lane;                       // 0..31
-        const int row = v >= 24, vv = row ? v - 24 : v;
-        if (vv < valid_vecs)
-          stg_v4(orow + row * out_row_bytes + 16 * vv,
-                 *reinterpret_cast<const uint4*>(stage + row * 384 + 16 * vv));
-      }
-      if (lane < 16) {
-        const int vv = lane + 8;
-        if (vv < valid_vecs)
-          stg_v4(orow + out_row_bytes + 16 * vv,
-                 *reinterpret_cast<const uint4*>(stage + 384 + 16 * vv));
-      }
-    }
-    __syncwarp();
-#pragma unroll
-    for (int e = 0; e < 12; ++e) {
-      h0[e] = h1[e];
-      h1[e] = h2[e];
-      h2[e] = h3[e];
-      h3[e] = h4[e];
-    }
-  }
 }
 
 // Generic path: any H, W >= 1 and any alignment.  One thread per output byte.
@@ -242,13 +304,26 @@ int launch_bicubic2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h
     return fail(ctx, VEX_ERR_INVALID, "vex_bicubic2x_u8: bad argument");
   const bool aligned = ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
   if (w % 16 == 0 && aligned && !ctx->opt_force_generic_bicubic) {
-    for (int f0 = 0; f0 < n; f0 += 65535) {
-      const int nf = min(n - f0, 65535);
-      dim3 grid((w + TPX - 1) / TPX, (h + TR - 1) / TR, nf);
+    const int wpr = (w + WARP_PX - 1) / WARP_PX;
+    // rows per strip: tall strips amortise the 4-row window warm-up; shrink them until the launch
+    // fills the machine (3 blocks x 4 warps resident per SM)
+    int R = 40;
+    const long long want = 2LL * ctx->sm_count * 3 * STRIP_WARPS;
+    while (R > 8 && (long long)n * ((h + R - 1) / R) * wpr < want) R -= 8;
+    if (ctx->opt_bicubic_rows > 0) R = (ctx->opt_bicubic_rows + 3) / 4 * 4;
+    const int nstrips = (h + R - 1) / R;
+    const long long per_frame = (long long)nstrips * wpr;
+    const int max_frames = (int)std::max<long long>(1, (1LL << 30) / per_frame);
+    for (int f0 = 0; f0 < n; f0 += max_frames) {
+      const int nf = min(n - f0, max_frames);
+      const int total_warps = (int)(per_frame * nf);
+      const int blocks = (total_warps + STRIP_WARPS - 1) / STRIP_WARPS;
       const uint8_t* pin = in + (size_t)f0 * h * w * 3;
       uint8_t* pout = out + (size_t)f0 * h * w * 12;
-      if (round_mode) bicubic2x_tile_kernel<1><<<grid, NTHREADS, 0, s>>>(pin, pout, h, w);
-      else            bicubic2x_tile_kernel<0><<<grid, NTHREADS, 0, s>>>(pin, pout, h, w);
+      if (round_mode)
+        bicubic2x_strip_kernel<1><<<blocks, STRIP_WARPS * 32, 0, s>>>(pin, pout, h, w, R, wpr, nstrips, total_warps);
+      else
+        bicubic2x_strip_kernel<0><<<blocks, STRIP_WARPS * 32, 0, s>>>(pin, pout, h, w, R, wpr, nstrips, total_warps);
       ctx->launches++;
     }
   } else {

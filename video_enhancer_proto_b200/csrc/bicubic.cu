@@ -61,16 +61,6 @@ __device__ __forceinline__ u64 mul2(u64 a, float w) {
   asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(bc(w)));
   return d;
 }
-__device__ __forceinline__ uint32_t ldg_nc(const uint32_t* p) {
-  uint32_t r;
-  asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(r) : "l"(p));
-  return r;
-}
-__device__ __forceinline__ void stg_v4(void* p, const uint4& v) {
-  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
-               "r"(v.z), "r"(v.w)
-               : "memory");
-}
 // four floats (already in [0,256) scale) -> 4 clamped, truncated bytes, b0 at the lowest address.
 // cvt.pack: d = (c << 16) | sat(a) << 8 | sat(b)   (measured, tools/ubench/packtest.cu)
 __device__ __forceinline__ uint32_t pack4(float b0, float b1, float b2, float b3) {
@@ -84,6 +74,9 @@ __device__ __forceinline__ uint32_t pack4(float b0, float b1, float b2, float b3
 constexpr int STRIP_WARPS = 4;            // warps per block, each fully independent
 constexpr int WARP_PX = 128;              // input pixels per warp row segment: lane = 4 px = 2 strips x 2 px
 constexpr int STAGE_ROW = WARP_PX * 6;    // 768 output bytes per warp per output row
+constexpr int RING_D = 3;                 // input rows in flight per warp (cp.async groups)
+constexpr int RING_SLOTS = 4;             // ring slots (RING_D + 1, and 4 keeps slot = step & 3)
+constexpr int RING_ROW = 416;             // 26 x 16 B: bytes [S-16, S+400) of a row
 constexpr float VS = 1.0f / 65536.0f;     // vertical weights carry the 2^-16 so the sum lands in [0,256)
 
 __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
@@ -92,9 +85,27 @@ __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
   return d;
 }
 // byte k of w -> the float 2^15 + byte (byte lands in mantissa bits 8..15 of 0x47000000)
-template <int IDX>
+// ZSEL picks which zero byte of the magic constant fills byte 0 / 2 of the result: a byte that feeds both strips is
+// converted once per strip with different (equivalent) selectors on purpose - with identical selectors ptxas shares
+// the PRMT and then pays several MOVs per shared value to build the two aligned register pairs.
+template <int IDX, int ZSEL>
 __device__ __forceinline__ uint32_t magic_f(const uint32_t (&raw)[7]) {
-  return prmt(raw[IDX >> 2], 0x47000000u, 0x7404u | ((IDX & 3) << 4));
+  return prmt(raw[IDX >> 2], 0x47000000u, 0x7000u | (ZSEL << 8) | ((IDX & 3) << 4) | ZSEL);
+}
+
+// this lane's three 16-byte destinations of an output row pair (2 rows x 48 vectors per warp)
+struct LaneOut {
+  uint8_t* p1;          // running: output row 2i, vector `lane`
+  uint32_t d2, d3;      // byte distance from p1 to the second / third destination
+  int s2;               // staging vector of the second destination (first = lane, third = 64 + lane)
+  bool ok1, ok2, ok3;
+};
+__device__ __forceinline__ void stg_v4_if(void* p, const uint4& v, bool pred) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+      "@q st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};\n\t}"
+      ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"((int)pred)
+      : "memory");
 }
 
 // One input row of one warp segment.  raw[] = the 28 bytes [12*lane-8, 12*lane+20) of the row segment:
@@ -104,8 +115,7 @@ __device__ __forceinline__ uint32_t magic_f(const uint32_t (&raw)[7]) {
 // S[(K+2)&3] = row i-2, S[(K+3)&3] = i-1, S[K] = i, S[(K+1)&3] = i+1, new = i+2.
 template <int ROUND, int K, bool EMIT>
 __device__ __forceinline__ void strip_step(u64 (&S)[4][12], uint32_t (&raw)[7], bool left, bool right,
-                                           uint8_t* stage, uint8_t* orow, size_t out_row_bytes,
-                                           bool store_ok, int lane, int valid_vecs) {
+                                           uint8_t* stage, const LaneOut& o, bool store_ok, int lane) {
   // border replicate in x on the raw bytes (app.py:372 -> ATen clamps tap indices)
   if (left) {            // px -2, -1 <- px 0 : bytes 2..7 <- bytes 8,9,10
     raw[0] = prmt(raw[2], raw[2], 0x1000u);
@@ -115,82 +125,88 @@ __device__ __forceinline__ void strip_step(u64 (&S)[4][12], uint32_t (&raw)[7], 
     raw[5] = prmt(raw[4], raw[4], 0x1321u);
     raw[6] = prmt(raw[4], raw[4], 0x0032u);
   }
-  u64 hn[12];
-  {
-    u64 P[6][3];
-#define VEX_CONV(T, C) P[T][C] = pk(magic_f<3 * T + C + 2>(raw), magic_f<3 * T + C + 8>(raw));
+  u64 P[6][3];
+#define VEX_CONV(T, C) P[T][C] = pk(magic_f<3 * T + C + 2, 4>(raw), magic_f<3 * T + C + 8, 5>(raw));
 #define VEX_CONV3(T) VEX_CONV(T, 0) VEX_CONV(T, 1) VEX_CONV(T, 2)
-    VEX_CONV3(0) VEX_CONV3(1) VEX_CONV3(2) VEX_CONV3(3) VEX_CONV3(4) VEX_CONV3(5)
+  VEX_CONV3(0) VEX_CONV3(1) VEX_CONV3(2) VEX_CONV3(3) VEX_CONV3(4) VEX_CONV3(5)
 #undef VEX_CONV3
 #undef VEX_CONV
-    // sum of weights = 256, so the 2^15 conversion bias contributes exactly 2^23; round-half-up = +128 here
-    const u64 bias = bc(-8388608.0f + (ROUND ? 128.0f : 0.0f));
+  // sum of weights = 256, so the 2^15 conversion bias contributes exactly 2^23; round-half-up = +128 here
+  const u64 bias = bc(-8388608.0f + (ROUND ? 128.0f : 0.0f));
+  constexpr int SA = (K + 2) & 3, SB = (K + 3) & 3, SC = K, SD = (K + 1) & 3;
+  float ea[12], eb[12], oa[12], ob[12];
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+  for (int u = 0; u < 2; ++u) {
 #pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const u64 X = fma2(P[u + 2][c], 225.f, bias);
-        hn[(2 * u) * 3 + c] = fma2(P[u + 1][c], 67.f, fma2(P[u + 3][c], -27.f, fma2(P[u][c], -9.f, X)));
-        hn[(2 * u + 1) * 3 + c] = fma2(P[u + 3][c], 67.f, fma2(P[u + 4][c], -9.f, fma2(P[u + 1][c], -27.f, X)));
+    for (int c = 0; c < 3; ++c) {
+      const int j1 = 6 * u + c, j2 = j1 + 3;     // even / odd output pixel of input pixel u
+      u64 X1, X2, T1, T2;
+      if constexpr (EMIT) {
+        // start both vertical chains with the row that is about to be overwritten (row i-2)
+        X1 = mul2(S[SC][j1], 225.f * VS);
+        X2 = mul2(S[SC][j2], 225.f * VS);
+        T1 = fma2(S[SA][j1], -9.f * VS, X1);
+        T2 = fma2(S[SA][j2], -9.f * VS, X2);
+      }
+      const u64 Xh = fma2(P[u + 2][c], 225.f, bias);
+      const u64 hE = fma2(P[u + 1][c], 67.f, fma2(P[u + 3][c], -27.f, fma2(P[u][c], -9.f, Xh)));
+      const u64 hO = fma2(P[u + 3][c], 67.f, fma2(P[u + 4][c], -9.f, fma2(P[u + 1][c], -27.f, Xh)));
+      S[SA][j1] = hE;
+      S[SA][j2] = hO;
+      if constexpr (EMIT) {
+        const u64 E1 = fma2(S[SB][j1], 67.f * VS, fma2(S[SD][j1], -27.f * VS, T1));
+        const u64 E2 = fma2(S[SB][j2], 67.f * VS, fma2(S[SD][j2], -27.f * VS, T2));
+        const u64 O1 = fma2(S[SD][j1], 67.f * VS, fma2(hE, -9.f * VS, fma2(S[SB][j1], -27.f * VS, X1)));
+        const u64 O2 = fma2(S[SD][j2], 67.f * VS, fma2(hO, -9.f * VS, fma2(S[SB][j2], -27.f * VS, X2)));
+        unpk(E1, ea[j1], eb[j1]);
+        unpk(E2, ea[j2], eb[j2]);
+        unpk(O1, oa[j1], ob[j1]);
+        unpk(O2, oa[j2], ob[j2]);
       }
     }
   }
-  if constexpr (!EMIT) {
-#pragma unroll
-    for (int j = 0; j < 12; ++j) S[(K + 2) & 3][j] = hn[j];
-  } else {
-  float ea[12], eb[12], oa[12], ob[12];
-#pragma unroll
-  for (int j = 0; j < 12; ++j) {
-    const u64 A = S[(K + 2) & 3][j], B = S[(K + 3) & 3][j], C = S[K][j], D = S[(K + 1) & 3][j];
-    const u64 X = mul2(C, 225.f * VS);
-    const u64 E = fma2(B, 67.f * VS, fma2(D, -27.f * VS, fma2(A, -9.f * VS, X)));
-    const u64 O = fma2(D, 67.f * VS, fma2(hn[j], -9.f * VS, fma2(B, -27.f * VS, X)));
-    S[(K + 2) & 3][j] = hn[j];
-    unpk(E, ea[j], eb[j]);
-    unpk(O, oa[j], ob[j]);
-  }
-  // lane's 24 output bytes per row: strip A (12 B) then strip B (12 B)
-  uint2* se = reinterpret_cast<uint2*>(stage + 24 * lane);
-  uint2* so = reinterpret_cast<uint2*>(stage + STAGE_ROW + 24 * lane);
-  {
-    const uint32_t a0 = pack4(ea[0], ea[1], ea[2], ea[3]), a1 = pack4(ea[4], ea[5], ea[6], ea[7]),
-                   a2 = pack4(ea[8], ea[9], ea[10], ea[11]);
-    const uint32_t b0 = pack4(eb[0], eb[1], eb[2], eb[3]), b1 = pack4(eb[4], eb[5], eb[6], eb[7]),
-                   b2 = pack4(eb[8], eb[9], eb[10], eb[11]);
-    se[0] = make_uint2(a0, a1);
-    se[1] = make_uint2(a2, b0);
-    se[2] = make_uint2(b1, b2);
-  }
-  {
-    const uint32_t a0 = pack4(oa[0], oa[1], oa[2], oa[3]), a1 = pack4(oa[4], oa[5], oa[6], oa[7]),
-                   a2 = pack4(oa[8], oa[9], oa[10], oa[11]);
-    const uint32_t b0 = pack4(ob[0], ob[1], ob[2], ob[3]), b1 = pack4(ob[4], ob[5], ob[6], ob[7]),
-                   b2 = pack4(ob[8], ob[9], ob[10], ob[11]);
-    so[0] = make_uint2(a0, a1);
-    so[1] = make_uint2(a2, b0);
-    so[2] = make_uint2(b1, b2);
-  }
-  __syncwarp();
-  if (store_ok) {
-    // 96 x 16 B (2 rows x 48): three fully coalesced passes
-    const uint4* sv = reinterpret_cast<const uint4*>(stage);
-    if (lane < valid_vecs) stg_v4(orow + 16 * lane, sv[lane]);
+  if constexpr (EMIT) {
+    // lane's 24 output bytes per row: strip A (12 B) then strip B (12 B)
+    uint2* se = reinterpret_cast<uint2*>(stage + 24 * lane);
+    uint2* so = reinterpret_cast<uint2*>(stage + STAGE_ROW + 24 * lane);
     {
-      const int row = lane >> 4, vv = row ? lane - 16 : lane + 32;
-      if (vv < valid_vecs) stg_v4(orow + row * out_row_bytes + 16 * vv, sv[row * 48 + vv]);
+      const uint32_t a0 = pack4(ea[0], ea[1], ea[2], ea[3]), a1 = pack4(ea[4], ea[5], ea[6], ea[7]),
+                     a2 = pack4(ea[8], ea[9], ea[10], ea[11]);
+      const uint32_t b0 = pack4(eb[0], eb[1], eb[2], eb[3]), b1 = pack4(eb[4], eb[5], eb[6], eb[7]),
+                     b2 = pack4(eb[8], eb[9], eb[10], eb[11]);
+      se[0] = make_uint2(a0, a1);
+      se[1] = make_uint2(a2, b0);
+      se[2] = make_uint2(b1, b2);
     }
-    if (lane + 16 < valid_vecs) stg_v4(orow + out_row_bytes + 16 * (lane + 16), sv[48 + 16 + lane]);
-  }
+    {
+      const uint32_t a0 = pack4(oa[0], oa[1], oa[2], oa[3]), a1 = pack4(oa[4], oa[5], oa[6], oa[7]),
+                     a2 = pack4(oa[8], oa[9], oa[10], oa[11]);
+      const uint32_t b0 = pack4(ob[0], ob[1], ob[2], ob[3]), b1 = pack4(ob[4], ob[5], ob[6], ob[7]),
+                     b2 = pack4(ob[8], ob[9], ob[10], ob[11]);
+      so[0] = make_uint2(a0, a1);
+      so[1] = make_uint2(a2, b0);
+      so[2] = make_uint2(b1, b2);
+    }
+    __syncwarp();
+    // 96 x 16 B (2 rows x 48) leave in three fully coalesced passes; o1/o2/o3 are this lane's three
+    // destinations, sidx* the matching staging vectors, pr* the (row-in-image && column-in-image) predicates
+    const uint4* sv = reinterpret_cast<const uint4*>(stage);
+    stg_v4_if(o.p1, sv[lane], o.ok1 && store_ok);
+    stg_v4_if(o.p1 + o.d2, sv[o.s2], o.ok2 && store_ok);
+    stg_v4_if(o.p1 + o.d3, sv[64 + lane], o.ok3 && store_ok);
   }
 }
 
 // Fast path: W % 16 == 0 (3W and 6W multiples of 16) and 16B-aligned buffers.  R = rows per strip (multiple of 4).
+// Input rows reach the lanes through a per-warp cp.async ring in shared memory (RING_D rows in flight, no
+// registers held while they fly): 26 lanes copy the warp's 416-byte row segment [S-16, S+400) as 16-byte chunks,
+// chunks outside the row are zero-filled (src-size 0) and rebuilt by the border replicate.
 template <int ROUND>
 __global__ void __launch_bounds__(STRIP_WARPS * 32, 3)
 bicubic2x_strip_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int H, int W, int R,
                        int wpr, int nstrips, int total_warps) {
-  __shared__ __align__(16) uint8_t s_stage[STRIP_WARPS][2][2 * STAGE_ROW];
+  __shared__ __align__(16) uint8_t s_stage[STRIP_WARPS][2 * STAGE_ROW];
+  __shared__ __align__(16) uint8_t s_ring[STRIP_WARPS][RING_SLOTS][RING_ROW];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int gw = blockIdx.x * STRIP_WARPS + warp;
   if (gw >= total_warps) return;
@@ -199,53 +215,79 @@ bicubic2x_strip_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out
   const int strip = t % nstrips, f = t / nstrips;
   const int r0 = strip * R;
   const int px0 = xw * WARP_PX + 4 * lane;
-  const bool valid = px0 < W;
   const bool left = px0 == 0, right = px0 + 4 == W;
-  const size_t in_row = (size_t)W * 3, out_row = (size_t)W * 6;
-  const uint8_t* fin = in + (size_t)f * H * in_row + ((ptrdiff_t)px0 * 3 - 8);
-  uint8_t* fout = out + (size_t)f * 2 * H * out_row + (size_t)xw * STAGE_ROW;
+  const uint32_t in_row = (uint32_t)W * 3;
+  const size_t out_row = (size_t)W * 6;
   const int valid_vecs = min(48, (W - xw * WARP_PX) * 6 / 16);
-  // the two words left of the image / right of the image are never read (they are rebuilt by the replicate)
-  const bool p01 = valid && !left, p234 = valid, p56 = valid && !right;
 
-  auto load_row = [&](int y, uint32_t(&r)[7]) {
+  // cp.async source of this lane: chunk `lane` of the segment, if it lies inside the row
+  const int chunk_off = xw * (WARP_PX * 3) - 16 + 16 * lane;
+  const bool chunk_lane = lane < RING_ROW / 16;
+  const uint32_t chunk_bytes = (chunk_lane && chunk_off >= 0 && chunk_off < (int)in_row) ? 16u : 0u;
+  const uint8_t* fsrc = in + (size_t)f * H * in_row + (chunk_bytes ? chunk_off : 0);
+  const uint32_t ring_base = (uint32_t)__cvta_generic_to_shared(&s_ring[warp][0][0]);
+  const uint32_t ring_dst = ring_base + 16 * lane;
+  const uint8_t* ring_src = &s_ring[warp][0][0] + 12 * lane + 8;   // bytes [12*lane-8, 12*lane+20) of the segment
+  uint8_t* stage = s_stage[warp];
+
+  auto issue_row = [&](int y, int slot) {                    // y is clamped: border replicate in y
     y = min(max(y, 0), H - 1);
-    const uint32_t* p = reinterpret_cast<const uint32_t*>(fin + (size_t)y * in_row);
-    r[0] = p01 ? ldg_nc(p + 0) : 0u;
-    r[1] = p01 ? ldg_nc(p + 1) : 0u;
-    r[2] = p234 ? ldg_nc(p + 2) : 0u;
-    r[3] = p234 ? ldg_nc(p + 3) : 0u;
-    r[4] = p234 ? ldg_nc(p + 4) : 0u;
-    r[5] = p56 ? ldg_nc(p + 5) : 0u;
-    r[6] = p56 ? ldg_nc(p + 6) : 0u;
+    if (chunk_lane)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(ring_dst + slot * RING_ROW),
+                   "l"(fsrc + (size_t)((uint32_t)y * in_row)), "r"(chunk_bytes)
+                   : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  auto fetch_row = [&](int slot, uint32_t(&r)[7]) {          // the row issued RING_D steps ago has landed
+    asm volatile("cp.async.wait_group %0;" ::"n"(RING_D - 1) : "memory");
+    __syncwarp();
+    const volatile uint32_t* a = reinterpret_cast<const volatile uint32_t*>(ring_src + slot * RING_ROW);
+#pragma unroll
+    for (int k = 0; k < 7; ++k) r[k] = a[k];
   };
 
   u64 S[4][12];
-  uint32_t ra[7], rb[7];
-  uint8_t* st0 = s_stage[warp][0];
-  uint8_t* st1 = s_stage[warp][1];
-  load_row(r0 - 2, ra);
-  load_row(r0 - 1, rb);
-  strip_step<ROUND, 0, false>(S, ra, left, right, st0, nullptr, 0, false, lane, 0);
-  load_row(r0, ra);
-  strip_step<ROUND, 1, false>(S, rb, left, right, st0, nullptr, 0, false, lane, 0);
-  load_row(r0 + 1, rb);
-  strip_step<ROUND, 2, false>(S, ra, left, right, st0, nullptr, 0, false, lane, 0);
-  load_row(r0 + 2, ra);
-  strip_step<ROUND, 3, false>(S, rb, left, right, st0, nullptr, 0, false, lane, 0);
+  uint32_t raw[7];
+  LaneOut o;
+  {
+    uint8_t* orow = out + (size_t)f * 2 * H * out_row + (size_t)xw * STAGE_ROW + (size_t)(2 * r0) * out_row;
+    const int row = lane >> 4, vv = row ? lane - 16 : lane + 32;
+    o.p1 = orow + 16 * lane;
+    o.ok1 = lane < valid_vecs;
+    o.d2 = (uint32_t)(row * out_row + 16 * vv - 16 * lane);
+    o.s2 = row * 48 + vv;
+    o.ok2 = vv < valid_vecs;
+    o.d3 = (uint32_t)(out_row + 256);
+    o.ok3 = lane + 16 < valid_vecs;
+  }
+  const size_t adv = 2 * out_row;
+  // step s handles input row q = r0 - 2 + s from ring slot s % RING_SLOTS and issues row q + RING_D
+  int q = r0 - 2;
+#pragma unroll
+  for (int d = 0; d < RING_D; ++d) issue_row(q + d, d);
+#define VEX_STEP(K, EMIT, SLOT, OK)                                   \
+  fetch_row(SLOT, raw);                                               \
+  issue_row(q + RING_D, (SLOT + RING_D) % RING_SLOTS);                \
+  ++q;                                                                \
+  strip_step<ROUND, K, EMIT>(S, raw, left, right, stage, o, OK, lane);
+  VEX_STEP(0, false, 0, false)
+  VEX_STEP(1, false, 1, false)
+  VEX_STEP(2, false, 2, false)
+  VEX_STEP(3, false, 3, false)
   const int iend = min(r0 + R, H);
 #pragma unroll 1
   for (int i = r0; i < iend; i += 4) {
-    uint8_t* orow = fout + (size_t)(2 * i) * out_row;
-    load_row(i + 3, rb);
-    strip_step<ROUND, 0, true>(S, ra, left, right, st0, orow, out_row, true, lane, valid_vecs);
-    load_row(i + 4, ra);
-    strip_step<ROUND, 1, true>(S, rb, left, right, st1, orow + 2 * out_row, out_row, i + 1 < iend, lane, valid_vecs);
-    load_row(i + 5, rb);
-    strip_step<ROUND, 2, true>(S, ra, left, right, st0, orow + 4 * out_row, out_row, i + 2 < iend, lane, valid_vecs);
-    load_row(i + 6, ra);
-    strip_step<ROUND, 3, true>(S, rb, left, right, st1, orow + 6 * out_row, out_row, i + 3 < iend, lane, valid_vecs);
+    VEX_STEP(0, true, 0, true)
+    o.p1 += adv;
+    VEX_STEP(1, true, 1, i + 1 < iend)
+    o.p1 += adv;
+    VEX_STEP(2, true, 2, i + 2 < iend)
+    o.p1 += adv;
+    VEX_STEP(3, true, 3, i + 3 < iend)
+    o.p1 += adv;
   }
+#undef VEX_STEP
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
 template <int ROUND>

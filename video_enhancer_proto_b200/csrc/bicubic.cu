@@ -74,8 +74,8 @@ __device__ __forceinline__ uint32_t pack4(float b0, float b1, float b2, float b3
 constexpr int STRIP_WARPS = 4;            // warps per block, each fully independent
 constexpr int WARP_PX = 128;              // input pixels per warp row segment: lane = 4 px = 2 strips x 2 px
 constexpr int STAGE_ROW = WARP_PX * 6;    // 768 output bytes per warp per output row
-constexpr int RING_D = 3;                 // input rows in flight per warp (cp.async groups)
-constexpr int RING_SLOTS = 4;             // ring slots (RING_D + 1, and 4 keeps slot = step & 3)
+constexpr int RING_D = 6;                 // input rows in flight per warp (cp.async groups)
+constexpr int RING_SLOTS = 8;             // ring slots (power of two > RING_D; slot = step & 7)
 constexpr int RING_ROW = 416;             // 26 x 16 B: bytes [S-16, S+400) of a row
 constexpr float VS = 1.0f / 65536.0f;     // vertical weights carry the 2^-16 so the sum lands in [0,256)
 
@@ -233,7 +233,7 @@ bicubic2x_strip_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out
   auto issue_row = [&](int y, int slot) {                    // y is clamped: border replicate in y
     y = min(max(y, 0), H - 1);
     if (chunk_lane)
-      asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(ring_dst + slot * RING_ROW),
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(ring_dst + slot * RING_ROW),
                    "l"(fsrc + (size_t)((uint32_t)y * in_row)), "r"(chunk_bytes)
                    : "memory");
     asm volatile("cp.async.commit_group;" ::: "memory");
@@ -266,24 +266,29 @@ bicubic2x_strip_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out
 #pragma unroll
   for (int d = 0; d < RING_D; ++d) issue_row(q + d, d);
 #define VEX_STEP(K, EMIT, SLOT, OK)                                   \
-  fetch_row(SLOT, raw);                                               \
-  issue_row(q + RING_D, (SLOT + RING_D) % RING_SLOTS);                \
+  {                                                                   \
+  const bool ok_ = OK;                                                \
+  fetch_row((SLOT) & (RING_SLOTS - 1), raw);                          \
+  issue_row(q + RING_D, ((SLOT) + RING_D) & (RING_SLOTS - 1));        \
   ++q;                                                                \
-  strip_step<ROUND, K, EMIT>(S, raw, left, right, stage, o, OK, lane);
+  strip_step<ROUND, K, EMIT>(S, raw, left, right, stage, o, ok_, lane); \
+  }
   VEX_STEP(0, false, 0, false)
   VEX_STEP(1, false, 1, false)
   VEX_STEP(2, false, 2, false)
   VEX_STEP(3, false, 3, false)
-  const int iend = min(r0 + R, H);
+  // main loop: the step that consumes input row q emits output rows 2(q-2), 2(q-2)+1
+  const int qend = min(r0 + R, H) + 2;
+  int sl = 4;
 #pragma unroll 1
-  for (int i = r0; i < iend; i += 4) {
-    VEX_STEP(0, true, 0, true)
+  for (; q < qend; sl += 4) {
+    VEX_STEP(0, true, sl, true)
     o.p1 += adv;
-    VEX_STEP(1, true, 1, i + 1 < iend)
+    VEX_STEP(1, true, sl + 1, q < qend)
     o.p1 += adv;
-    VEX_STEP(2, true, 2, i + 2 < iend)
+    VEX_STEP(2, true, sl + 2, q < qend)
     o.p1 += adv;
-    VEX_STEP(3, true, 3, i + 3 < iend)
+    VEX_STEP(3, true, sl + 3, q < qend)
     o.p1 += adv;
   }
 #undef VEX_STEP
@@ -347,11 +352,13 @@ int launch_bicubic2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h
   const bool aligned = ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
   if (w % 16 == 0 && aligned && !ctx->opt_force_generic_bicubic) {
     const int wpr = (w + WARP_PX - 1) / WARP_PX;
-    // rows per strip: tall strips amortise the 4-row window warm-up; shrink them until the launch
-    // fills the machine (3 blocks x 4 warps resident per SM)
-    int R = 40;
-    const long long want = 2LL * ctx->sm_count * 3 * STRIP_WARPS;
-    while (R > 8 && (long long)n * ((h + R - 1) / R) * wpr < want) R -= 8;
+    // rows per strip: tall strips amortise the 4-row window warm-up (measured: 120 rows +3 % over 40); take the
+    // tallest strip that still gives every resident warp slot (3 blocks x 4 warps per SM) one strip
+    int R = 8;
+    const long long want = (long long)ctx->sm_count * 3 * STRIP_WARPS;
+    for (int cand : {120, 60, 40, 24, 16}) {
+      if ((long long)n * ((h + cand - 1) / cand) * wpr >= want) { R = cand; break; }
+    }
     if (ctx->opt_bicubic_rows > 0) R = (ctx->opt_bicubic_rows + 3) / 4 * 4;
     const int nstrips = (h + R - 1) / R;
     const long long per_frame = (long long)nstrips * wpr;

@@ -219,7 +219,7 @@ im2col27_kernel(const I27Params p) {
 
 // ============================================================================================== gemm27
 constexpr int MODE_CONV5 = 0, MODE_UP2 = 1;
-constexpr int G27_THREADS = 192;       // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
+constexpr int G27_THREADS = 320;       // warp 0 TMA, warp 1 MMA, warps 2-5 / 6-9 two epilogue groups (even / odd items)
 constexpr int G27_ROWS = 6;            // output rows per item; halo tile = 8 rows x 32 px = 256 GEMM rows
 constexpr int G27_TW = 30;
 constexpr int G27_SA = 4;
@@ -230,8 +230,10 @@ constexpr int G27_OB_PITCH = 104;                    // staged uint8 output row 
 struct G27Cfg {
   static constexpr int W_OFF = G27_SA * G27_A_STAGE;               // up to 8 chunks x 4 KB of weights
   static constexpr int YS_OFF = W_OFF + 8 * 4096;
-  static constexpr int OB_OFF = YS_OFF + 27 * G27_YS_PITCH * 4;
-  static constexpr int BAR_OFF = OB_OFF + G27_ROWS * G27_OB_PITCH + 16;
+  static constexpr int YS_BYTES = 27 * G27_YS_PITCH * 4;            // per epilogue group
+  static constexpr int OB_OFF = YS_OFF + 2 * YS_BYTES;
+  static constexpr int OB_BYTES = G27_ROWS * G27_OB_PITCH + 16;     // per epilogue group
+  static constexpr int BAR_OFF = OB_OFF + 2 * OB_BYTES;
   static constexpr int SMEM = BAR_OFF + 256 + 1024;
 };
 
@@ -259,10 +261,13 @@ gemm27_kernel(const __grid_constant__ CUtensorMap amap, const G27Params p) {
   const uint32_t acc_full = a_empty + 8 * G27_SA, acc_empty = acc_full + 16;
   const uint32_t w_bar = acc_empty + 16, tmem_slot = w_bar + 8;
   volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(sm + C::BAR_OFF + (tmem_slot - bar0));
-  float* Ys = reinterpret_cast<float*>(sm + C::YS_OFF);
-  uint8_t* ob = sm + C::OB_OFF;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total = p.tiles_x * p.tiles_y * p.n_img;
+  // The epilogue (TMEM drain, 9-tap gather, quantise, row stores) is a long dependent chain with three barriers;
+  // two groups of 4 warps work on alternate items, each with its own TMEM buffer, Ys planes and output stage.
+  const int grp = warp >= 6 ? 1 : 0;
+  float* Ys = reinterpret_cast<float*>(sm + C::YS_OFF + grp * C::YS_BYTES);
+  uint8_t* ob = sm + C::OB_OFF + grp * C::OB_BYTES;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < G27_SA; ++i) { ptx::mbar_init(a_full + 8 * i, 1); ptx::mbar_init(a_empty + 8 * i, 1); }
@@ -325,10 +330,11 @@ gemm27_kernel(const __grid_constant__ CUtensorMap amap, const G27Params p) {
     }
   } else {
     const int q = warp & 3;
-    const int et = (warp - 2) * 32 + lane;           // 0..127 among the epilogue threads
+    const int et = ((warp - 2) & 3) * 32 + lane;     // 0..127 among the threads of this epilogue group
     const float b0 = p.bias[0], b1 = p.bias[1], b2 = p.bias[2];
-    uint32_t b = 0, pb = 0;
-    for (int it = blockIdx.x; it < total; it += gridDim.x) {
+    const uint32_t b = grp;                          // item sequence parity = TMEM buffer = group
+    uint32_t pb = 0;
+    for (int it = blockIdx.x + grp * gridDim.x; it < total; it += 2 * gridDim.x) {
       const int txi = it % p.tiles_x, r = it / p.tiles_x;
       const int tyi = r % p.tiles_y, n = r / p.tiles_y;
       const int x0 = txi * G27_TW, y0 = tyi * G27_ROWS;
@@ -346,8 +352,8 @@ gemm27_kernel(const __grid_constant__ CUtensorMap amap, const G27Params p) {
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(acc_empty + 8 * b);      // TMEM buffer free: next-but-one item may start
-      if (++b == 2) { b = 0; pb ^= 1; }
-      named_bar_sync(1, 128);
+      pb ^= 1;
+      named_bar_sync(1 + grp, 128);
       // 9-tap gather-sum: out(ty,tx) = bias + sum_t Y[(ty+t/3)*32 + tx+t%3][t*3+co]
       const int nvx = min(G27_TW, p.W - x0);                    // valid pixels per row of this tile
 #pragma unroll 1
@@ -387,7 +393,7 @@ gemm27_kernel(const __grid_constant__ CUtensorMap amap, const G27Params p) {
         }
       }
       if (MODE == MODE_UP2 && p.out_u8) {
-        named_bar_sync(1, 128);
+        named_bar_sync(1 + grp, 128);
         // cooperative row stores: aligned 32-bit words in the middle, bytes at the ragged ends
         for (int wi = et; wi < G27_ROWS * 24; wi += 128) {
           const int ty = wi / 24, j = wi - ty * 24;
@@ -407,7 +413,7 @@ gemm27_kernel(const __grid_constant__ CUtensorMap amap, const G27Params p) {
           }
         }
       }
-      named_bar_sync(1, 128);                                   // Ys / ob reusable
+      named_bar_sync(1 + grp, 128);                             // Ys / ob reusable
     }
   }
   ptx::tc_fence_before();

@@ -29,8 +29,11 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 
 // ============================================================================================ im2col27
 constexpr int MODE_CONV1 = 0, MODE_UP1 = 1;
-constexpr int I27_THREADS = 288;       // warps 0-3 build A, warp 4 issues MMAs, warps 5-8 drain TMEM
-constexpr int I27_SA = 3;              // A stages (128 rows x 128 B each)
+constexpr int I27_THREADS = 544;       // warps 0-3 / 4-7 two A-builder groups, warp 8 MMA, warps 9-12 / 13-16 two drain groups
+constexpr int I27_SA = 4;              // A stages (128 rows x 128 B each); item sequence k uses stage k & 3
+constexpr int I27_MMA_WARP = 8;
+constexpr int I27_EPI_WARP0 = 9;
+constexpr int I27_STG = 8192;          // per drain warp: 32 pixels x 256 B staged for coalesced stores
 
 template <int BN>
 struct I27Cfg {
@@ -38,7 +41,8 @@ struct I27Cfg {
   static constexpr int A_STAGE = 128 * 128;
   static constexpr int W_BYTES = BN * 128;
   static constexpr int W_OFF = I27_SA * A_STAGE;
-  static constexpr int BAR_OFF = W_OFF + W_BYTES;
+  static constexpr int STG_OFF = W_OFF + W_BYTES;
+  static constexpr int BAR_OFF = STG_OFF + 8 * I27_STG;
   static constexpr int BIAS_OFF = BAR_OFF + 256;
   static constexpr int SMEM = BIAS_OFF + BN * 4 + 1024;
 };
@@ -77,7 +81,7 @@ im2col27_kernel(const I27Params p) {
     ptx::fence_mbar_init();
   }
   for (int i = threadIdx.x; i < BN; i += I27_THREADS) bias_s[i] = p.bias[i];
-  if (warp == 4) {
+  if (warp == I27_MMA_WARP) {
     ptx::tmem_alloc(tmem_slot, 512);
     ptx::tmem_relinquish();
   }
@@ -86,11 +90,14 @@ im2col27_kernel(const I27Params p) {
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot_p;
 
-  if (warp < 4) {
-    // ================================ A builders: one pixel (= one 128 B operand row) per thread
-    const int r = threadIdx.x;                       // row within the stage
-    uint32_t sa = 0, pa = 0;
-    for (long long it = blockIdx.x; it < items; it += gridDim.x) {
+  if (warp < 8) {
+    // ================================ A builders: one pixel (= one 128 B operand row) per thread.
+    // The gather is latency-bound (9-27 dependent-free loads, then a barrier), so two groups of 128 threads
+    // build alternate items: group gi owns item sequence numbers k = gi, gi+2, ... and stages gi, gi+2.
+    const int gi = warp >> 2;
+    const int r = threadIdx.x & 127;                 // row within the stage
+    uint32_t sa = gi, pa = 0;
+    for (long long it = blockIdx.x + (long long)gi * gridDim.x; it < items; it += 2LL * gridDim.x) {
       const long long pix = it * 128 + r;
       uint32_t w[16];
 #pragma unroll
@@ -132,9 +139,10 @@ im2col27_kernel(const I27Params p) {
         *reinterpret_cast<uint4*>(row + ((j ^ (r & 7)) << 4)) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
       ptx::fence_proxy_async_smem();                 // generic-proxy stores -> visible to the tensor core
       ptx::mbar_arrive(a_full + 8 * sa);
-      if (++sa == I27_SA) { sa = 0; pa ^= 1; }
+      sa += 2;
+      if (sa >= I27_SA) { sa -= I27_SA; pa ^= 1; }
     }
-  } else if (warp == 4) {
+  } else if (warp == I27_MMA_WARP) {
     // ================================ weights once, then 2 MMAs per item
     if (lane == 0) {
       ptx::mbar_expect_tx(w_bar, C::W_BYTES);
@@ -159,59 +167,85 @@ im2col27_kernel(const I27Params p) {
       }
     }
   } else {
-    // ================================ epilogue: TMEM -> bias, relu, bf16 -> global
-    const int q = warp & 3;
-    uint32_t b = 0, pb = 0;
-    for (long long it = blockIdx.x; it < items; it += gridDim.x) {
-      const long long pix = it * 128 + q * 32 + lane;
+    // ================================ drain: TMEM -> bias, relu, bf16 -> shared stage -> coalesced global stores.
+    // Two groups of 4 warps take alternate items.  A warp owns 32 pixels (TMEM lane quarter q); per 128 output
+    // columns it stages [32 px][256 B] (16-byte chunk c of pixel r at c ^ (r & 7): conflict-free both ways) and
+    // writes it back as 16 instructions of 32 x 16 B = 512 contiguous bytes:
+    //   CONV1: the 32 pixels x 128 channels are 8 KB contiguous in x1;
+    //   UP1:   columns [128*py, 128*py+128) are the 64 hi-res pixels of row 2y+py (PixelShuffle), 8 KB contiguous.
+    const int ew = warp - I27_EPI_WARP0;
+    const int ge = ew >> 2, q = warp & 3;
+    uint8_t* stg = sm + C::STG_OFF + ew * I27_STG;
+    constexpr int HALVES = BN / 128;
+    long long k = ge;
+    for (long long it = blockIdx.x + (long long)ge * gridDim.x; it < items; it += 2LL * gridDim.x, k += 2) {
+      const uint32_t b = (uint32_t)(k % C::NACC), pb = (uint32_t)((k / C::NACC) & 1);
+      const long long pix0 = it * 128 + q * 32;      // first pixel of this warp
+      const long long pix = pix0 + lane;
       const bool valid = pix < p.npix;
-      __nv_bfloat16* obase = nullptr;
-      if (valid) {
-        if (MODE == MODE_CONV1) {
-          obase = p.out + pix * BN;
-        } else {
-          const int x = (int)(pix % p.W);
-          const long long t = pix / p.W;
-          const int y = (int)(t % p.H);
-          const long long img = t / p.H;
-          obase = p.out + ((img * 2 * p.H + 2 * y) * (2LL * p.W) + 2 * x) * (BN / 4);
-        }
+      unsigned long long obase = 0;                  // UP1: address of hi-res pixel (2y, 2x) of this lane's pixel
+      if (MODE == MODE_UP1 && valid) {
+        const int x = (int)(pix % p.W);
+        const long long t = pix / p.W;
+        const int y = (int)(t % p.H);
+        const long long img = t / p.H;
+        obase = reinterpret_cast<unsigned long long>(p.out + ((img * 2 * p.H + 2 * y) * (2LL * p.W) + 2 * x) * (BN / 4));
       }
       ptx::mbar_wait(acc_full + 8 * b, pb);
       ptx::tc_fence_after();
 #pragma unroll 1
-      for (int g = 0; g < BN / 32; ++g) {
-        uint32_t v[32];
-        ptx::tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + b * BN + g * 32, v);
-        ptx::tmem_ld_wait();
-        if (valid) {
-          __nv_bfloat16* o;
-          if (MODE == MODE_CONV1) {
-            o = obase + g * 32;
-          } else {                                   // column = phase*64 + co, phase = py*2+px: PixelShuffle(2)
-            const int ph = (g * 32) / (BN / 4), co = (g * 32) % (BN / 4);
-            o = obase + ((long long)(ph >> 1) * (2LL * p.W) + (ph & 1)) * (BN / 4) + co;
-          }
-          uint4* o4 = reinterpret_cast<uint4*>(o);
+      for (int hf = 0; hf < HALVES; ++hf) {
+#pragma unroll 1
+        for (int g = 0; g < 4; ++g) {
+          uint32_t v[32];
+          const int col = hf * 128 + g * 32;
+          ptx::tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + b * BN + col, v);
+          ptx::tmem_ld_wait();
 #pragma unroll
           for (int j4 = 0; j4 < 4; ++j4) {
             float f[8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) f[e] = fmaxf(__uint_as_float(v[j4 * 8 + e]) + bias_s[g * 32 + j4 * 8 + e], 0.f);
-            o4[j4] = make_uint4(ptx::pack_bf16x2(f[0], f[1]), ptx::pack_bf16x2(f[2], f[3]),
-                                ptx::pack_bf16x2(f[4], f[5]), ptx::pack_bf16x2(f[6], f[7]));
+            for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[j4 * 8 + e]) + bias_s[col + j4 * 8 + e];
+            const int c = g * 4 + j4;
+            *reinterpret_cast<uint4*>(stg + lane * 256 + ((c ^ (lane & 7)) << 4)) =
+                make_uint4(ptx::pack_relu_bf16x2(f[0], f[1]), ptx::pack_relu_bf16x2(f[2], f[3]),
+                           ptx::pack_relu_bf16x2(f[4], f[5]), ptx::pack_relu_bf16x2(f[6], f[7]));
           }
         }
+        if (hf == HALVES - 1) {                      // accumulator fully read: hand it back before the stores
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(acc_empty + 8 * b);
+        } else {
+          __syncwarp();
+        }
+        if (MODE == MODE_CONV1) {
+          uint8_t* gbase = reinterpret_cast<uint8_t*>(p.out + pix0 * BN);
+#pragma unroll 4
+          for (int i = 0; i < 16; ++i) {
+            const int px = 2 * i + (lane >> 4), c = lane & 15;
+            const uint4 o = *reinterpret_cast<const uint4*>(stg + px * 256 + ((c ^ (px & 7)) << 4));
+            if (pix0 + px < p.npix) *reinterpret_cast<uint4*>(gbase + i * 512 + lane * 16) = o;
+          }
+        } else {
+          const unsigned long long rowoff = (unsigned long long)hf * (2ULL * p.W) * (BN / 4) * 2;   // hi-res row 2y+py
+#pragma unroll 4
+          for (int i = 0; i < 16; ++i) {
+            const int h = 4 * i + (lane >> 3), cc = lane & 7;     // hi-res pixel within the warp's 64, chunk
+            const int xl = h >> 1, pxp = h & 1;
+            const unsigned long long ob = __shfl_sync(0xffffffffu, obase, xl);
+            const int c = pxp * 8 + cc;
+            const uint4 o = *reinterpret_cast<const uint4*>(stg + xl * 256 + ((c ^ (xl & 7)) << 4));
+            if (ob) *reinterpret_cast<uint4*>(ob + rowoff + pxp * (BN / 4) * 2 + cc * 16) = o;
+          }
+        }
+        __syncwarp();
       }
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(acc_empty + 8 * b);
-      if (++b == C::NACC) { b = 0; pb ^= 1; }
     }
   }
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == I27_MMA_WARP) {
     __syncwarp();
     ptx::tmem_dealloc(tmem, 512);
   }

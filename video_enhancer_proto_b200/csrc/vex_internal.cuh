@@ -36,6 +36,8 @@ struct vex_ctx {
   // debug knobs (vex_set_option)
   int opt_desc_base_offset = 0;   // smem-descriptor base_offset field: 0 (measured correct on B200), 1: (addr>>7)&7
   int opt_force_generic_bicubic = 0;
+  int opt_conv_variant = 0;          // 0 = conv_tc2 (cluster pairs, double-buffered TMEM), 1 = conv_tc v1
+  int max_pairs = 0;                 // co-resident 2-CTA clusters of conv_tc2 (queried once)
   int opt_bicubic_rows = 0;          // rows per strip override (0 = auto)
   int opt_conv3_bn = 256;         // Cout block of conv3 on the tensor cores (128 or 256)
   int opt_thin_tc = 1;            // thin layers on tcgen05 (thin_tc.cuh); 0 = fp32 CUDA-core kernels (cnn_small.cuh)

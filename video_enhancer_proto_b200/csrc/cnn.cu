@@ -152,7 +152,7 @@ int launch_tc(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bflo
 }
 
 // v2: cluster-of-two kernel with double-buffered TMEM slots and multicast weights (conv_tc2.cuh)
-template <int BN, bool SKIP>
+template <int BN, bool SKIP, bool DIRECT>
 int launch_tc2(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfloat16* out,
                const __nv_bfloat16* skip, int n, int H, int W, cudaStream_t s) {
   using C = convtc2::Cfg<BN>;
@@ -173,7 +173,7 @@ int launch_tc2(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfl
   }
   const long long total = (long long)p.tiles_x * p.tiles_y * n;
   if (total > 0x3fffffffLL) return fail(ctx, VEX_ERR_INVALID, "conv_tc2: too many tiles");
-  auto kern = convtc2::conv3x3_tc_kernel<BN, SKIP>;
+  auto kern = convtc2::conv3x3_tc_kernel<BN, SKIP, DIRECT>;
   cudaLaunchConfig_t cfg = {};
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -182,7 +182,7 @@ int launch_tc2(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfl
   cfg.dynamicSmemBytes = C::SMEM;
   cfg.stream = s;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  const unsigned abit = ((BN == 256 ? 2u : 1u) << (SKIP ? 8 : 0)) << 16;
+  const unsigned abit = ((BN == 256 ? 2u : 1u) << (SKIP ? 8 : 0)) << (DIRECT ? 20 : 16);
   if (!(ctx->attr_mask & abit)) {            // per device, hence per ctx
     VEX_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
     ctx->attr_mask |= abit;
@@ -222,11 +222,19 @@ int run_tc(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfloat1
   // Cin = 128, v1 for Cin = 256 where the lock-step weight ring costs more than the epilogue overlap gains)
   const bool v2 = ctx->opt_conv_variant == 2 || (ctx->opt_conv_variant == 0 && L.cin <= 128);
   if (v2) {
+    const bool direct = (ctx->opt_epi_variant & 8) != 0;
+    if (direct) {
+      if (skip)
+        return L.bn == 256 ? launch_tc2<256, true, true>(ctx, L, in, out, skip, n, H, W, s)
+                           : launch_tc2<128, true, true>(ctx, L, in, out, skip, n, H, W, s);
+      return L.bn == 256 ? launch_tc2<256, false, true>(ctx, L, in, out, skip, n, H, W, s)
+                         : launch_tc2<128, false, true>(ctx, L, in, out, skip, n, H, W, s);
+    }
     if (skip)
-      return L.bn == 256 ? launch_tc2<256, true>(ctx, L, in, out, skip, n, H, W, s)
-                         : launch_tc2<128, true>(ctx, L, in, out, skip, n, H, W, s);
-    return L.bn == 256 ? launch_tc2<256, false>(ctx, L, in, out, skip, n, H, W, s)
-                       : launch_tc2<128, false>(ctx, L, in, out, skip, n, H, W, s);
+      return L.bn == 256 ? launch_tc2<256, true, false>(ctx, L, in, out, skip, n, H, W, s)
+                         : launch_tc2<128, true, false>(ctx, L, in, out, skip, n, H, W, s);
+    return L.bn == 256 ? launch_tc2<256, false, false>(ctx, L, in, out, skip, n, H, W, s)
+                       : launch_tc2<128, false, false>(ctx, L, in, out, skip, n, H, W, s);
   }
   if (skip)
     return L.bn == 256 ? launch_tc<256, true>(ctx, L, in, out, skip, n, H, W, s)

@@ -64,7 +64,10 @@ struct Params {
   long long* dbg;         // optional [gridDim.x][8] cycle counters (MMA thread: total, wait_acc, wait_a, wait_w; epilogue: wait_full, work)
 };
 
-template <int BN, bool SKIP>
+// DIRECT: the epilogue reads the skip and writes the output straight from/to global (64 contiguous bytes per
+// lane) instead of transposing through shared memory.  The SS MMAs of this kernel already consume the whole
+// shared-memory bandwidth (M=128, N=128: 8 KB of operands per 64 tensor cycles), so staging traffic costs MMA time.
+template <int BN, bool SKIP, bool DIRECT>
 __global__ void __launch_bounds__(NTHREADS, 1)
 conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
   using C = Cfg<BN>;
@@ -241,6 +244,9 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
       bool pxok[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) pxok[i] = live && (8 * i + cpx < TILE_W) && (x0 + 8 * i + cpx < p.W);
+      // DIRECT: this lane's own pixel (row ybase + 4a, column x0 + lane), channels nb*BN + g*32 ...
+      const size_t eown = (((size_t)n * p.H + ybase) * p.W + x0 + lane) * p.Cout + nb * BN;
+      const bool ownok = live && lane < TILE_W && x0 + lane < p.W;
       uint32_t v[2][32];
       uint4 sk[2][4];
       auto issue = [&](int u, int buf) {
@@ -248,10 +254,17 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
         if (!(p.epi_variant & 2)) ptx::tmem_ld_32x32(tq + (slot * C::APS + a) * BN + g * 32, v[buf]);
         if (SKIP && !(p.epi_variant & 4)) {
           const bool yok = ybase + 4 * a < p.H;
-          const __nv_bfloat16* sp = p.skip + e0 + a * acc_stride + g * 32;
+          if (DIRECT) {
+            const __nv_bfloat16* sp = p.skip + eown + a * acc_stride + g * 32;
 #pragma unroll
-          for (int i = 0; i < 4; ++i)
-            sk[buf][i] = (yok && pxok[i]) ? __ldg(reinterpret_cast<const uint4*>(sp + i * px8)) : make_uint4(0, 0, 0, 0);
+            for (int i = 0; i < 4; ++i)
+              sk[buf][i] = (yok && ownok) ? __ldg(reinterpret_cast<const uint4*>(sp + i * 8)) : make_uint4(0, 0, 0, 0);
+          } else {
+            const __nv_bfloat16* sp = p.skip + e0 + a * acc_stride + g * 32;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              sk[buf][i] = (yok && pxok[i]) ? __ldg(reinterpret_cast<const uint4*>(sp + i * px8)) : make_uint4(0, 0, 0, 0);
+          }
         }
       };
       const bool dbg = p.dbg != nullptr && warp == 2 && lane == 0 && blockIdx.y == 0;
@@ -269,6 +282,29 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
         store_bias(slot * C::APS + a, g);               // unit drained into registers: re-arm it for the next item
         if (u + 1 < UNITS) issue(u + 1, buf ^ 1);
         const bool yok = ybase + 4 * a < p.H;
+        if (DIRECT) {
+          uint4* op = reinterpret_cast<uint4*>(p.out + eown + a * acc_stride + g * 32);
+          const bool ok = yok && ownok && !(p.epi_variant & 1);
+#pragma unroll
+          for (int j4 = 0; j4 < 4; ++j4) {
+            uint32_t o[4];
+            if (SKIP) {
+              const uint32_t w[4] = {sk[buf][j4].x, sk[buf][j4].y, sk[buf][j4].z, sk[buf][j4].w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float lo = fmaxf(__uint_as_float(v[buf][j4 * 8 + 2 * e]), 0.f) + ptx::bf16lo_to_f32(w[e]);
+                const float hi = fmaxf(__uint_as_float(v[buf][j4 * 8 + 2 * e + 1]), 0.f) + ptx::bf16hi_to_f32(w[e]);
+                o[e] = ptx::pack_bf16x2(lo, hi);
+              }
+            } else {
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                o[e] = ptx::pack_relu_bf16x2(__uint_as_float(v[buf][j4 * 8 + 2 * e]), __uint_as_float(v[buf][j4 * 8 + 2 * e + 1]));
+            }
+            if (ok) op[j4] = make_uint4(o[0], o[1], o[2], o[3]);
+          }
+          continue;
+        }
         if (SKIP) {
           uint4 sv[4];
 #pragma unroll

@@ -233,7 +233,11 @@ def gpu_workload(workload, enh, args, world, rank, local, warmup, peaks, torch, 
         kern_ms = float(np.mean(step_ms))                    # the step IS one launch of bicubic2x_strip_kernel
         achieved = BICUBIC_BYTES_PER_FRAME * fps_step / (kern_ms / 1e3) / 1e9
         roof = {"bound": "hbm", "kernel": "bicubic2x_strip_kernel", "achieved": achieved, "peak": peaks["hbm_gbs"],
-                "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks["source"],
+                "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
+                # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/r1_v4_ncu_full_bicubic.csv:
+                # 1.877 + 7.421 GB for 300 frames), scaled to this launch's frame count
+                "traffic": int(9.297e9 * fps_step / 300), "traffic_source": "profiles/r1_v4_ncu_full_bicubic.csv",
+                "peak_source": peaks["source"],
                 "algorithmic_bytes_per_launch": BICUBIC_BYTES_PER_FRAME * fps_step, "launch_ms": kern_ms}
         dtype = "u8"
     else:
@@ -243,7 +247,10 @@ def gpu_workload(workload, enh, args, world, rank, local, warmup, peaks, torch, 
         achieved = tc_flop / (tc_ms / 1e3) / 1e12
         peak = peaks["bf16_tflops_sustained"]
         roof = {"bound": "tensor", "kernel": "conv3x3_tc_kernel (conv2+conv3+conv4, 3 launches/step)",
-                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                # DRAM bytes per launch (mean of the 3 launches), ncu --set full on batch 8 (profiles/r1_v4_ncu_full_cnn.csv:
+                # conv2 4.26+4.21, conv3 5.28+8.45, conv4 9.05+4.22 GB), scaled to this step's frame count
+                "traffic": int(11.82e9 * fps_step / 8), "traffic_source": "profiles/r1_v4_ncu_full_cnn.csv",
                 "peak_source": peaks["source"] + " (sustained cuBLAS bf16)",
                 "algorithmic_flop_per_step": tc_flop, "kernel_ms_per_step": tc_ms,
                 "kernel_share_of_step": tc_ms / float(np.mean(step_ms)), "layer_ms": prof,

@@ -7,10 +7,10 @@ from video_enhancer_proto_b200 import B200VideoEnhancer
 H, W = 1080, 1920
 peak = json.load(open("MEASURED_PEAKS.json"))["hbm_gbs"] if os.path.exists("MEASURED_PEAKS.json") else 6483.0
 enh = B200VideoEnhancer(device="cuda:0", seed=0)
-for n in (300, 8, 1):
+for n in ((300,) if len(sys.argv) > 1 else (300, 8, 1)):
     x = torch.randint(0, 256, (n, H, W, 3), dtype=torch.uint8, device="cuda")
     out = torch.empty((n, 2 * H, 2 * W, 3), dtype=torch.uint8, device="cuda")
-    for rows in (0, 8, 24, 40, 60, 120, 216, 360):
+    for rows in ([int(a) for a in sys.argv[1:]] or (0, 8, 24, 40, 60, 120, 216, 360)):
         enh.set_option("bicubic_rows", rows)
         for _ in range(3):
             enh.upscale_device(x, mode="bicubic", out=out)

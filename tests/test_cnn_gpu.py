@@ -160,6 +160,37 @@ def test_conv3_block_variants_agree(enhancers):
     assert np.abs(a - b).max() <= 2.0 ** -7 * np.abs(a).max()
 
 
+def test_conv_kernel_variants_bit_identical(enhancers):
+    """conv_tc v1 (single CTA, all TMEM columns per item) and conv_tc2 (cluster pairs, two TMEM slots, multicast
+    weights) run the same MMAs in the same K order per accumulator, so every layer tap must be bit-identical.
+    Shapes: an odd number of work items (one CTA of the last pair repeats an item with its stores masked), a
+    single item, a ragged tile grid, and a batch."""
+    rng = np.random.default_rng(15)
+    enh = enhancers["stress"]
+    cases = [(1, 8, 90), (1, 5, 7), (3, 37, 53), (2, 130, 70), (5, 24, 31)]
+    for n, h, w in cases:
+        d = dev([synth.random_frame(h, w, rng) for _ in range(n)])
+        outs = {}
+        for variant in (1, 2, 0):
+            prev = enh.set_option("conv_variant", variant)
+            try:
+                outs[variant] = [enh.cnn_debug_f32(d, tap=t).cpu().numpy() for t in (2, 3, 4, 0)]
+            finally:
+                enh.set_option("conv_variant", prev)
+        for t in range(4):
+            assert np.array_equal(outs[1][t], outs[2][t]), (n, h, w, t)
+            assert np.array_equal(outs[1][t], outs[0][t]), (n, h, w, t)
+        prev = enh.set_option("conv_variant", 2)
+        pe = enh.set_option("epi_variant", 8)               # direct (unstaged) epilogue of conv_tc2
+        try:
+            direct = [enh.cnn_debug_f32(d, tap=t).cpu().numpy() for t in (2, 3, 4, 0)]
+        finally:
+            enh.set_option("epi_variant", pe)
+            enh.set_option("conv_variant", prev)
+        for t in range(4):
+            assert np.array_equal(outs[1][t], direct[t]), (n, h, w, t)
+
+
 def test_sub_batching_matches(enhancers):
     rng = np.random.default_rng(14)
     frames = [synth.random_frame(33, 47, rng) for _ in range(5)]

@@ -191,6 +191,36 @@ def test_conv_kernel_variants_bit_identical(enhancers):
             assert np.array_equal(outs[1][t], direct[t]), (n, h, w, t)
 
 
+@pytest.mark.parametrize("widths", [(256, 256, 512, 256), (128, 128, 512, 512), (384, 384, 128, 256)])
+def test_widened_variant(widths):
+    """BASELINE.json configs[4]: widened random-init variant of the same layer kinds (channel plan through
+    vex_cnn_desc).  Exercises Cin chunks up to 8, two Cout blocks per layer (grid.y = 2 for the cluster kernel),
+    and the 256/384/512-channel tail.  Same bars as the reference-width model."""
+    model = O.make_model(0, widths=widths)
+    enh = B200VideoEnhancer(device="cuda:0", state_dict=O.export_state(model))
+    try:
+        assert enh.load_models()
+        rng = np.random.default_rng(21)
+        frames = [synth.random_frame(41, 67, rng), synth.edges_frame(41, 67, rng)]
+        taps = {}
+        want = O.ref_cnn_batch_f32(model, frames, taps).numpy()
+        d = dev(frames)
+        for t, name in TAP_NAMES.items():
+            if t == 0:
+                continue
+            got = enh.cnn_debug_f32(d, tap=t).cpu().numpy()
+            ref = taps[name].numpy()
+            rel = float(np.abs(got - ref).max() / max(np.abs(ref).max(), 1e-12))
+            assert rel <= 2 * TAP_REL_TOL[name], (widths, name, rel)
+        got = enh.cnn_debug_f32(d, tap=0).cpu().numpy()
+        check_f32(got, want, f"widened{widths}")
+        u8 = enh.upscale_device(d, mode="cnn").cpu().numpy()
+        ref8 = np.stack([O.ref_cnn_frame(model, f) for f in frames])
+        assert np.abs(u8.astype(int) - ref8.astype(int)).max() <= 2
+    finally:
+        enh.close()
+
+
 def test_sub_batching_matches(enhancers):
     rng = np.random.default_rng(14)
     frames = [synth.random_frame(33, 47, rng) for _ in range(5)]

@@ -220,12 +220,13 @@ im2col27_kernel(const I27Params p) {
           __syncwarp();
         }
         if (MODE == MODE_CONV1) {
-          uint8_t* gbase = reinterpret_cast<uint8_t*>(p.out + pix0 * BN);
+          // pixel px, channels [128*hf, 128*hf+128): 256 contiguous bytes (the whole pixel when BN == 128)
+          uint8_t* gbase = reinterpret_cast<uint8_t*>(p.out + pix0 * BN + hf * 128);
 #pragma unroll 4
           for (int i = 0; i < 16; ++i) {
             const int px = 2 * i + (lane >> 4), c = lane & 15;
             const uint4 o = *reinterpret_cast<const uint4*>(stg + px * 256 + ((c ^ (px & 7)) << 4));
-            if (pix0 + px < p.npix) *reinterpret_cast<uint4*>(gbase + i * 512 + lane * 16) = o;
+            if (pix0 + px < p.npix) *reinterpret_cast<uint4*>(gbase + (size_t)px * (BN * 2) + c * 16) = o;
           }
         } else {
           const unsigned long long rowoff = (unsigned long long)hf * (2ULL * p.W) * (BN / 4) * 2;   // hi-res row 2y+py

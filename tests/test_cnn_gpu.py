@@ -171,7 +171,7 @@ def test_conv_kernel_variants_bit_identical(enhancers):
     for n, h, w in cases:
         d = dev([synth.random_frame(h, w, rng) for _ in range(n)])
         outs = {}
-        for variant in (1, 2, 0):
+        for variant in (1, 2, 3, 0):
             prev = enh.set_option("conv_variant", variant)
             try:
                 outs[variant] = [enh.cnn_debug_f32(d, tap=t).cpu().numpy() for t in (2, 3, 4, 0)]
@@ -179,6 +179,7 @@ def test_conv_kernel_variants_bit_identical(enhancers):
                 enh.set_option("conv_variant", prev)
         for t in range(4):
             assert np.array_equal(outs[1][t], outs[2][t]), (n, h, w, t)
+            assert np.array_equal(outs[1][t], outs[3][t]), (n, h, w, t)
             assert np.array_equal(outs[1][t], outs[0][t]), (n, h, w, t)
         prev = enh.set_option("conv_variant", 2)
         pe = enh.set_option("epi_variant", 8)               # direct (unstaged) epilogue of conv_tc2

@@ -14,6 +14,7 @@
 #include "cnn_small.cuh"
 #include "conv_tc.cuh"
 #include "conv_tc2.cuh"
+#include "conv_tc3.cuh"
 #include "thin_tc.cuh"
 #include "vex_internal.cuh"
 
@@ -216,10 +217,90 @@ int launch_tc2(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfl
   return VEX_OK;
 }
 
+// v3: cluster-of-two kernel issuing cta_group::2 MMAs (M = 256 over the pair, B split across the pair; conv_tc3.cuh)
+template <int BN, bool SKIP, bool DIRECT>
+int launch_tc3(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfloat16* out,
+               const __nv_bfloat16* skip, int n, int H, int W, cudaStream_t s) {
+  using C = convtc3::Cfg<BN>;
+  CUtensorMap amap;
+  int rc = make_amap(ctx, &amap, in, n, H, W, L.cin, C::ROWS + 2);
+  if (rc) return rc;
+  convtc3::Params p;
+  p.wpack = L.wpack; p.bias = L.bias; p.out = out; p.skip = skip;
+  p.H = H; p.W = W; p.NC = L.cin / 64; p.Cout = L.cout;
+  p.tiles_x = (W + convtc3::TILE_W - 1) / convtc3::TILE_W;
+  p.tiles_y = (H + C::ROWS - 1) / C::ROWS;
+  p.n_img = n; p.desc_base_offset = ctx->opt_desc_base_offset;
+  p.dbg = nullptr;
+  p.epi_variant = ctx->opt_epi_variant;
+  if (ctx->opt_conv_dbg) {
+    VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&p.dbg), (size_t)ctx->sm_count * 64));
+    VEX_CUDA(ctx, cudaMemsetAsync(p.dbg, 0, (size_t)ctx->sm_count * 64, s));
+  }
+  const long long total = (long long)p.tiles_x * p.tiles_y * n;
+  if (total > 0x3fffffffLL) return fail(ctx, VEX_ERR_INVALID, "conv_tc3: too many tiles");
+  auto kern = convtc3::conv3x3_tc_kernel<BN, SKIP, DIRECT>;
+  cudaLaunchConfig_t cfg = {};
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.blockDim = dim3(convtc3::NTHREADS);
+  cfg.dynamicSmemBytes = C::SMEM;
+  cfg.stream = s;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  const unsigned abit = ((BN == 256 ? 2u : 1u) << (SKIP ? 8 : 0)) << (DIRECT ? 20 : 16);
+  if (!(ctx->attr_mask3 & abit)) {            // per device, hence per ctx
+    VEX_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+    ctx->attr_mask3 |= abit;
+  }
+  if (ctx->max_pairs3 <= 0) {                 // how many 2-CTA clusters of this footprint are co-resident
+    cfg.gridDim = dim3(2 * (unsigned)(ctx->sm_count / 2), 1);
+    int nc = 0;
+    VEX_CUDA(ctx, cudaOccupancyMaxActiveClusters(&nc, kern, &cfg));
+    ctx->max_pairs3 = std::max(1, std::min(nc, ctx->sm_count / 2));
+  }
+  const int nby = L.cout / BN;
+  const long long pairs = std::min<long long>((total + 1) / 2, std::max(1, ctx->max_pairs3 / nby));
+  cfg.gridDim = dim3((unsigned)(2 * pairs), nby);
+  VEX_CUDA(ctx, cudaLaunchKernelEx(&cfg, kern, amap, p));
+  ctx->launches++;
+  VEX_CUDA(ctx, cudaGetLastError());
+  if (p.dbg) {
+    std::vector<long long> h((size_t)ctx->sm_count * 8);
+    VEX_CUDA(ctx, cudaStreamSynchronize(s));
+    VEX_CUDA(ctx, cudaMemcpy(h.data(), p.dbg, h.size() * 8, cudaMemcpyDeviceToHost));
+    cudaFree(p.dbg);
+    double a[6] = {0, 0, 0, 0, 0, 0};
+    for (unsigned b = 0; b < cfg.gridDim.x; ++b)
+      for (int i = 0; i < 6; ++i) a[i] += (double)h[(size_t)b * 8 + i] / cfg.gridDim.x;
+    const double items = (double)total / cfg.gridDim.x;
+    fprintf(stderr, "[conv_dbg v3] cin=%d cout=%d bn=%d pairs=%lld items/cta=%.1f cycles/item: total=%.0f mma_wait_acc=%.0f "
+                    "mma_wait_a=%.0f mma_wait_w=%.0f | epi_wait_full=%.0f epi_work=%.0f\n",
+            L.cin, L.cout, BN, pairs, items, a[0] / items, a[1] / items, a[2] / items, a[3] / items, a[4] / items,
+            a[5] / items);
+  }
+  return VEX_OK;
+}
+
 int run_tc(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfloat16* out,
            const __nv_bfloat16* skip, int n, int H, int W, cudaStream_t s) {
   // conv_variant: 1 = v1 single-CTA kernel, 2 = v2 cluster pairs, 0 = auto (measured per layer on B200: v2 wins for
   // Cin = 128, v1 for Cin = 256 where the lock-step weight ring costs more than the epilogue overlap gains)
+  if (ctx->opt_conv_variant == 3) {
+    const bool direct = (ctx->opt_epi_variant & 8) != 0;
+    if (direct) {
+      if (skip)
+        return L.bn == 256 ? launch_tc3<256, true, true>(ctx, L, in, out, skip, n, H, W, s)
+                           : launch_tc3<128, true, true>(ctx, L, in, out, skip, n, H, W, s);
+      return L.bn == 256 ? launch_tc3<256, false, true>(ctx, L, in, out, skip, n, H, W, s)
+                         : launch_tc3<128, false, true>(ctx, L, in, out, skip, n, H, W, s);
+    }
+    if (skip)
+      return L.bn == 256 ? launch_tc3<256, true, false>(ctx, L, in, out, skip, n, H, W, s)
+                         : launch_tc3<128, true, false>(ctx, L, in, out, skip, n, H, W, s);
+    return L.bn == 256 ? launch_tc3<256, false, false>(ctx, L, in, out, skip, n, H, W, s)
+                       : launch_tc3<128, false, false>(ctx, L, in, out, skip, n, H, W, s);
+  }
   const bool v2 = ctx->opt_conv_variant == 2 || (ctx->opt_conv_variant == 0 && L.cin <= 128);
   if (v2) {
     const bool direct = (ctx->opt_epi_variant & 8) != 0;

@@ -28,6 +28,7 @@ struct vex_ctx {
   uint8_t* slot_in[2] = {nullptr, nullptr};
   uint8_t* slot_out[2] = {nullptr, nullptr};
   size_t slot_in_bytes = 0, slot_out_bytes = 0;
+  unsigned attr_mask3 = 0;        // same for the conv_tc3 instantiations
   unsigned attr_mask = 0;         // which kernels had their max-dynamic-smem attribute set on this device
 
   // CNN state
@@ -37,6 +38,7 @@ struct vex_ctx {
   int opt_desc_base_offset = 0;   // smem-descriptor base_offset field: 0 (measured correct on B200), 1: (addr>>7)&7
   int opt_force_generic_bicubic = 0;
   int opt_conv_variant = 0;          // 0 = conv_tc2 (cluster pairs, double-buffered TMEM), 1 = conv_tc v1
+  int max_pairs3 = 0;                // same for conv_tc3
   int max_pairs = 0;                 // co-resident 2-CTA clusters of conv_tc2 (queried once)
   int opt_bicubic_rows = 0;          // rows per strip override (0 = auto)
   int opt_conv3_bn = 256;         // Cout block of conv3 on the tensor cores (128 or 256)

@@ -284,24 +284,7 @@ int launch_tc3(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfl
 
 int run_tc(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfloat16* out,
            const __nv_bfloat16* skip, int n, int H, int W, cudaStream_t s) {
-  // conv_variant: 1 = v1 single-CTA kernel, 2 = v2 cluster pairs, 0 = auto (measured per layer on B200: v2 wins for
-  // Cin = 128, v1 for Cin = 256 where the lock-step weight ring costs more than the epilogue overlap gains)
-  if (ctx->opt_conv_variant == 3) {
-    const bool direct = (ctx->opt_epi_variant & 8) != 0;
-    if (direct) {
-      if (skip)
-        return L.bn == 256 ? launch_tc3<256, true, true>(ctx, L, in, out, skip, n, H, W, s)
-                           : launch_tc3<128, true, true>(ctx, L, in, out, skip, n, H, W, s);
-      return L.bn == 256 ? launch_tc3<256, false, true>(ctx, L, in, out, skip, n, H, W, s)
-                         : launch_tc3<128, false, true>(ctx, L, in, out, skip, n, H, W, s);
-    }
-    if (skip)
-      return L.bn == 256 ? launch_tc3<256, true, false>(ctx, L, in, out, skip, n, H, W, s)
-                         : launch_tc3<128, true, false>(ctx, L, in, out, skip, n, H, W, s);
-    return L.bn == 256 ? launch_tc3<256, false, false>(ctx, L, in, out, skip, n, H, W, s)
-                       : launch_tc3<128, false, false>(ctx, L, in, out, skip, n, H, W, s);
-  }
-  const bool v2 = ctx->opt_conv_variant == 2 || (ctx->opt_conv_variant == 0 && L.cin <= 128);
+  const bool v2 = ctx->opt_conv_variant == 2;
   if (v2) {
     const bool direct = (ctx->opt_epi_variant & 8) != 0;
     if (direct) {

@@ -97,7 +97,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
 
   if (warp == 0) {
     // ============================== TMA producer ==============================
-    if (lane == 0) {
+    if (ptx::elect_one()) {
       const uint8_t* wsrc = p.wpack + (size_t)nb * p.NC * 9 * C::W_STAGE;
       uint32_t sa = 0, pa = 0, sw = 0, pw = 0;
       for (int it = blockIdx.x; it < total; it += gridDim.x) {
@@ -121,7 +121,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
     }
   } else if (warp == 1) {
     // ============================== MMA issuer ================================
-    if (lane == 0) {
+    if (ptx::elect_one()) {
       constexpr uint32_t idesc = ptx::idesc_bf16_f32(128, BN);
       uint32_t sa = 0, pa = 0, sw = 0, pw = 0, pacc = 0;
       long long t_acc = 0, t_a = 0, t_w = 0, t0 = 0, t1;
@@ -144,13 +144,14 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
             ptx::tc_fence_after();
             const uint32_t wbase = w_stage0 + sw * C::W_STAGE;
             const uint32_t tap_off = ((t / 3) * PITCH + (t % 3)) * 128;
+const uint64_t ad0 = ptx::smem_desc_sw128(abase + tap_off, p.desc_base_offset);
+            const uint64_t bd0 = ptx::smem_desc_sw128(wbase, 0);
 #pragma unroll
             for (int a = 0; a < C::NACC; ++a) {
 #pragma unroll
               for (int k = 0; k < KC / 16; ++k) {
-                const uint64_t ad = ptx::smem_desc_sw128(abase + tap_off + a * (128 * 128) + k * 32,
-                                                         p.desc_base_offset);
-                const uint64_t bd = ptx::smem_desc_sw128(wbase + k * 32, 0);
+                const uint64_t ad = ptx::desc_advance(ad0, a * (128 * 128) + k * 32);
+                const uint64_t bd = ptx::desc_advance(bd0, k * 32);
                 ptx::mma_bf16_ss(tmem + a * BN, ad, bd, idesc, 1u);   // TMEM was pre-loaded with the bias
               }
             }

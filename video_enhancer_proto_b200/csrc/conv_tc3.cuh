@@ -55,7 +55,7 @@ struct Cfg {
   static constexpr int A_STAGE = (ROWS + 2) * PITCH * 128;
   static constexpr int W_SLICE = BN * 128;              // one (chunk, tap) weight slice in global: BN rows x 64 bf16
   static constexpr int W_STAGE = W_SLICE / 2;           // this CTA's half of it (BN/2 rows)
-  static constexpr int SW = BN == 128 ? 10 : 6;
+  static constexpr int SW = BN == 128 ? 14 : 8;
   static constexpr int BAR_OFF = SA * A_STAGE + SW * W_STAGE;
   static constexpr int BIAS_OFF = BAR_OFF + 512;
   static constexpr int STAGE_OFF = BIAS_OFF + BN * 4;   // 8 epilogue warps x 2 KB transpose stage
@@ -125,7 +125,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
 
   if (warp == 0) {
     // ============================== TMA producer ==============================
-    if (lane == 0) {
+    if (ptx::elect_one()) {
       const uint8_t* wsrc = p.wpack + (size_t)nb * p.NC * 9 * C::W_SLICE + rank * C::W_STAGE;   // this CTA's rows of B
       uint32_t sa = 0, pa = 0, sw = 0, pw = 0;
       for (int kk = 0; kk < iters; ++kk) {
@@ -150,23 +150,24 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
     }
   } else if (warp == 1) {
     // ============================== MMA issuer ================================
-    if (lane == 0 && rank != 0) {
+    const bool elected = ptx::elect_one();
+    if (elected && rank != 0) {
       // ---- peer: relay "stage full" to the leader (same loop structure as the issuer below)
       uint32_t sa = 0, pa = 0, sw = 0, pw = 0;
       const uint32_t ra = ptx::mapa(a_peer, 0), rw = ptx::mapa(w_peer, 0);
       for (int kk = 0; kk < iters; ++kk) {
         for (int c = 0; c < p.NC; ++c) {
           ptx::mbar_wait(a_full + 8 * sa, pa);
-          ptx::mbar_arrive_remote(ra + 8 * sa);
+          ptx::mbar_arrive_remote_relaxed(ra + 8 * sa);
           if (++sa == SA) { sa = 0; pa ^= 1; }
           for (int t = 0; t < 9; ++t) {
             ptx::mbar_wait(w_full + 8 * sw, pw);
-            ptx::mbar_arrive_remote(rw + 8 * sw);
+            ptx::mbar_arrive_remote_relaxed(rw + 8 * sw);
             if (++sw == C::SW) { sw = 0; pw ^= 1; }
           }
         }
       }
-    } else if (lane == 0) {
+    } else if (elected) {
       constexpr uint32_t idesc = ptx::idesc_bf16_f32(256, BN);
       uint32_t sa = 0, pa = 0, sw = 0, pw = 0;
       long long t_acc = 0, t_a = 0, t_w = 0, t0 = 0, t1;
@@ -181,25 +182,27 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
         for (int c = 0; c < p.NC; ++c) {
           if (dbg) t0 = clock64();
           ptx::mbar_wait(a_full + 8 * sa, pa);
-          ptx::mbar_wait_cluster(a_peer + 8 * sa, pa);
+          ptx::mbar_wait(a_peer + 8 * sa, pa);
           if (dbg) { t1 = clock64(); t_a += t1 - t0; }
           const uint32_t abase = a_stage0 + sa * C::A_STAGE;
           for (int t = 0; t < 9; ++t) {
             if (dbg) t0 = clock64();
             ptx::mbar_wait(w_full + 8 * sw, pw);
-            ptx::mbar_wait_cluster(w_peer + 8 * sw, pw);
+            if (dbg) { t1 = clock64(); t_a += t1 - t0; t0 = t1; }   // TEMP: t_a = local w wait, t_w = peer w wait
+            ptx::mbar_wait(w_peer + 8 * sw, pw);
             if (dbg) { t1 = clock64(); t_w += t1 - t0; }
             ptx::tc_fence_after();
             const uint32_t wbase = w_stage0 + sw * C::W_STAGE;
             const uint32_t tap_off = ((t / 3) * PITCH + (t % 3)) * 128;
+const uint64_t ad0 = ptx::smem_desc_sw128(abase + tap_off, p.desc_base_offset);
+            const uint64_t bd0 = ptx::smem_desc_sw128(wbase, 0);
 #pragma unroll
             for (int a = 0; a < C::APS; ++a) {
 #pragma unroll
               for (int k = 0; k < KC / 16; ++k) {
-                const uint64_t ad = ptx::smem_desc_sw128(abase + tap_off + a * (128 * 128) + k * 32,
-                                                         p.desc_base_offset);
-                const uint64_t bd = ptx::smem_desc_sw128(wbase + k * 32, 0);
-                ptx::mma2_bf16_ss(tmem + (slot * C::APS + a) * BN, ad, bd, idesc, 1u);  // both CTAs' TMEM were pre-loaded with the bias
+                const uint64_t ad = ptx::desc_advance(ad0, a * (128 * 128) + k * 32);
+                const uint64_t bd = ptx::desc_advance(bd0, k * 32);
+                ptx::mma2_bf16_ss(tmem + (slot * C::APS + a) * BN, ad, bd, idesc, 1u);   // TMEM was pre-loaded with the bias
               }
             }
             ptx::tc_commit2_mc(w_empty + 8 * sw, (uint16_t)3);  // frees the stage in both CTAs

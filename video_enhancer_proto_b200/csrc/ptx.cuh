@@ -15,6 +15,14 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// one lane of a fully converged warp (the form the compiler recognises as "exactly one thread", which lets it issue
+// tcgen05.mma / commit without wrapping each one in an elect-and-loop sequence)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+
 // ---------------------------------------------------------------------------------------- mbarrier
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
@@ -166,6 +174,10 @@ __device__ __forceinline__ uint32_t mapa(uint32_t saddr, uint32_t rank) {
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// relaxed flavour for pure signal relays (the relaying thread has written nothing itself)
+__device__ __forceinline__ void mbar_arrive_remote_relaxed(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 // wait with cluster-scope acquire (the arrive came from the peer CTA)
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
   const long long t0 = clock64();
@@ -230,6 +242,11 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t use
   if (use_base_offset) hi |= ((saddr >> 7) & 7u) << 17;
   return (static_cast<uint64_t>(hi) << 32) | lo;
 }
+// Advance a descriptor's start address by `bytes` (multiple of 16, staying inside the 256 KB window): the address
+// field is the low 14 bits of the low word, so this is one 32-bit add instead of re-encoding the descriptor.  The MMA
+// issue loop is a single thread on the uniform datapath; re-encoding both descriptors per MMA cost ~19 instructions
+// per tcgen05.mma and made the issue thread, not the tensor pipe, the bottleneck (measured: ~105 cycles per MMA).
+__device__ __forceinline__ uint64_t desc_advance(uint64_t d, uint32_t bytes) { return d + (bytes >> 4); }
 // Instruction descriptor for kind::f16: D fp32, A/B bf16, both K-major, dense, no negate.
 __host__ __device__ constexpr uint32_t idesc_bf16_f32(int m, int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n >> 3) << 17) |

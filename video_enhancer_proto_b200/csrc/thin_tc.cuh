@@ -144,7 +144,7 @@ im2col27_kernel(const I27Params p) {
     }
   } else if (warp == I27_MMA_WARP) {
     // ================================ weights once, then 2 MMAs per item
-    if (lane == 0) {
+    if (ptx::elect_one()) {
       ptx::mbar_expect_tx(w_bar, C::W_BYTES);
       ptx::bulk_load(sbase + C::W_OFF, p.wpack, C::W_BYTES, w_bar);
       ptx::mbar_wait(w_bar, 0);
@@ -321,7 +321,7 @@ gemm27_kernel(const __grid_constant__ CUtensorMap amap, const G27Params p) {
   const uint32_t tmem = *tmem_slot_p;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (ptx::elect_one()) {
       ptx::mbar_expect_tx(w_bar, p.NC * 4096);
       ptx::bulk_load(sbase + C::W_OFF, p.wpack, p.NC * 4096, w_bar);
       uint32_t sa = 0, pa = 0;
@@ -338,7 +338,7 @@ gemm27_kernel(const __grid_constant__ CUtensorMap amap, const G27Params p) {
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (ptx::elect_one()) {
       ptx::mbar_wait(w_bar, 0);
       constexpr uint32_t idesc = ptx::idesc_bf16_f32(128, 32);
       uint32_t sa = 0, pa = 0, b = 0, pb = 0;

@@ -282,9 +282,31 @@ int launch_tc3(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfl
   return VEX_OK;
 }
 
+#ifndef VEX_CONV_DEFAULT_VARIANT
+#define VEX_CONV_DEFAULT_VARIANT 3
+#endif
+
 int run_tc(vex_ctx* ctx, const TcLayer& L, const __nv_bfloat16* in, __nv_bfloat16* out,
            const __nv_bfloat16* skip, int n, int H, int W, cudaStream_t s) {
-  const bool v2 = ctx->opt_conv_variant == 2;
+  // conv_variant: 1 = v1 single-CTA kernel; 2 = v2 cluster pairs with multicast weights (cta_group::1);
+  // 3 = v3 cta_group::2 pairs; 0 = auto (see below)
+  const int variant = ctx->opt_conv_variant == 0 ? VEX_CONV_DEFAULT_VARIANT : ctx->opt_conv_variant;
+  if (variant == 3) {
+    const bool direct = (ctx->opt_epi_variant & 8) != 0;
+    if (direct) {
+      if (skip)
+        return L.bn == 256 ? launch_tc3<256, true, true>(ctx, L, in, out, skip, n, H, W, s)
+                           : launch_tc3<128, true, true>(ctx, L, in, out, skip, n, H, W, s);
+      return L.bn == 256 ? launch_tc3<256, false, true>(ctx, L, in, out, skip, n, H, W, s)
+                         : launch_tc3<128, false, true>(ctx, L, in, out, skip, n, H, W, s);
+    }
+    if (skip)
+      return L.bn == 256 ? launch_tc3<256, true, false>(ctx, L, in, out, skip, n, H, W, s)
+                         : launch_tc3<128, true, false>(ctx, L, in, out, skip, n, H, W, s);
+    return L.bn == 256 ? launch_tc3<256, false, false>(ctx, L, in, out, skip, n, H, W, s)
+                       : launch_tc3<128, false, false>(ctx, L, in, out, skip, n, H, W, s);
+  }
+  const bool v2 = variant == 2;
   if (v2) {
     const bool direct = (ctx->opt_epi_variant & 8) != 0;
     if (direct) {

@@ -248,9 +248,9 @@ def gpu_workload(workload, enh, args, world, rank, local, warmup, peaks, torch, 
         peak = peaks["bf16_tflops_sustained"]
         roof = {"bound": "tensor", "kernel": "conv3x3_tc_kernel (conv2+conv3+conv4, 3 launches/step)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                # DRAM bytes per launch (mean of the 3 launches), ncu --set full on batch 8 (profiles/r1_v4_ncu_full_cnn.csv:
-                # conv2 4.26+4.21, conv3 5.28+8.45, conv4 9.05+4.22 GB), scaled to this step's frame count
-                "traffic": int(11.82e9 * fps_step / 8), "traffic_source": "profiles/r1_v4_ncu_full_cnn.csv",
+                # DRAM bytes per launch (mean of the 3 launches), ncu --set full on batch 8 (profiles/r1_v5_ncu_full_cnn.csv:
+                # conv2 4.58+4.21, conv3 5.10+8.45, conv4 9.29+4.22 GB), scaled to this step's frame count
+                "traffic": int(11.95e9 * fps_step / 8), "traffic_source": "profiles/r1_v5_ncu_full_cnn.csv",
                 "peak_source": peaks["source"] + " (sustained cuBLAS bf16)",
                 "algorithmic_flop_per_step": tc_flop, "kernel_ms_per_step": tc_ms,
                 "kernel_share_of_step": tc_ms / float(np.mean(step_ms)), "layer_ms": prof,

@@ -33,7 +33,8 @@ constexpr int I27_THREADS = 544;       // warps 0-3 / 4-7 two A-builder groups, 
 constexpr int I27_SA = 4;              // A stages (128 rows x 128 B each); item sequence k uses stage k & 3
 constexpr int I27_MMA_WARP = 8;
 constexpr int I27_EPI_WARP0 = 9;
-constexpr int I27_STG = 8192;          // per drain warp: 32 pixels x 256 B staged for coalesced stores
+constexpr int I27_STG_PITCH = 272;     // staged row pitch: 256 B + 16 B so that 16-byte stores of 32 lanes do not conflict
+constexpr int I27_STG = 32 * I27_STG_PITCH;   // per drain warp: 32 pixels x 256 B
 
 template <int BN>
 struct I27Cfg {
@@ -167,34 +168,42 @@ im2col27_kernel(const I27Params p) {
       }
     }
   } else {
-    // ================================ drain: TMEM -> bias, relu, bf16 -> shared stage -> coalesced global stores.
-    // Two groups of 4 warps take alternate items.  A warp owns 32 pixels (TMEM lane quarter q); per 128 output
-    // columns it stages [32 px][256 B] (16-byte chunk c of pixel r at c ^ (r & 7): conflict-free both ways) and
-    // writes it back as 16 instructions of 32 x 16 B = 512 contiguous bytes:
-    //   CONV1: the 32 pixels x 128 channels are 8 KB contiguous in x1;
-    //   UP1:   columns [128*py, 128*py+128) are the 64 hi-res pixels of row 2y+py (PixelShuffle), 8 KB contiguous.
+    // ================================ drain: TMEM -> bias, relu, bf16 -> shared stage -> bulk (TMA) stores.
+    // Two groups of 4 warps take alternate items.  A lane owns one pixel (TMEM lane); per 128 output columns it
+    // stages ITS OWN 256-byte row (pitch 272 B: conflict-free 16-byte stores) and sends it to global with one
+    // cp.async.bulk of 256 contiguous bytes:
+    //   CONV1: channels [128*hf, 128*hf+128) of the pixel;
+    //   UP1:   columns [128*py, 128*py+128) = hi-res pixels (2y+py, 2x) and (2y+py, 2x+1), 64 channels each (PixelShuffle).
+    // No lane touches another lane's row, so there is no warp synchronisation and no address shuffling in the loop.
     const int ew = warp - I27_EPI_WARP0;
     const int ge = ew >> 2, q = warp & 3;
-    uint8_t* stg = sm + C::STG_OFF + ew * I27_STG;
+    uint8_t* stg = sm + C::STG_OFF + ew * I27_STG + lane * I27_STG_PITCH;
+    const uint32_t stg_s = ptx::smem_u32(stg);
     constexpr int HALVES = BN / 128;
     long long k = ge;
     for (long long it = blockIdx.x + (long long)ge * gridDim.x; it < items; it += 2LL * gridDim.x, k += 2) {
       const uint32_t b = (uint32_t)(k % C::NACC), pb = (uint32_t)((k / C::NACC) & 1);
-      const long long pix0 = it * 128 + q * 32;      // first pixel of this warp
-      const long long pix = pix0 + lane;
+      const long long pix = it * 128 + q * 32 + lane;
       const bool valid = pix < p.npix;
-      unsigned long long obase = 0;                  // UP1: address of hi-res pixel (2y, 2x) of this lane's pixel
-      if (MODE == MODE_UP1 && valid) {
-        const int x = (int)(pix % p.W);
-        const long long t = pix / p.W;
-        const int y = (int)(t % p.H);
-        const long long img = t / p.H;
-        obase = reinterpret_cast<unsigned long long>(p.out + ((img * 2 * p.H + 2 * y) * (2LL * p.W) + 2 * x) * (BN / 4));
+      uint8_t* obase = nullptr;                      // first of this pixel's HALVES 256-byte destinations
+      size_t half_stride = 256;                      // CONV1: next 128 channels of the same pixel
+      if (valid) {
+        if (MODE == MODE_CONV1) {
+          obase = reinterpret_cast<uint8_t*>(p.out + pix * BN);
+        } else {
+          const int x = (int)(pix % p.W);
+          const long long t = pix / p.W;
+          const int y = (int)(t % p.H);
+          const long long img = t / p.H;
+          obase = reinterpret_cast<uint8_t*>(p.out + ((img * 2 * p.H + 2 * y) * (2LL * p.W) + 2 * x) * (BN / 4));
+          half_stride = (size_t)(2LL * p.W) * (BN / 4) * 2;     // hi-res row 2y+1
+        }
       }
       ptx::mbar_wait(acc_full + 8 * b, pb);
       ptx::tc_fence_after();
 #pragma unroll 1
       for (int hf = 0; hf < HALVES; ++hf) {
+        ptx::bulk_wait_read0();                      // this lane's previous bulk store has finished reading its row
 #pragma unroll 1
         for (int g = 0; g < 4; ++g) {
           uint32_t v[32];
@@ -206,8 +215,7 @@ im2col27_kernel(const I27Params p) {
             float f[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[j4 * 8 + e]) + bias_s[col + j4 * 8 + e];
-            const int c = g * 4 + j4;
-            *reinterpret_cast<uint4*>(stg + lane * 256 + ((c ^ (lane & 7)) << 4)) =
+            *reinterpret_cast<uint4*>(stg + (g * 4 + j4) * 16) =
                 make_uint4(ptx::pack_relu_bf16x2(f[0], f[1]), ptx::pack_relu_bf16x2(f[2], f[3]),
                            ptx::pack_relu_bf16x2(f[4], f[5]), ptx::pack_relu_bf16x2(f[6], f[7]));
           }
@@ -216,33 +224,13 @@ im2col27_kernel(const I27Params p) {
           ptx::tc_fence_before();
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive(acc_empty + 8 * b);
-        } else {
-          __syncwarp();
         }
-        if (MODE == MODE_CONV1) {
-          // pixel px, channels [128*hf, 128*hf+128): 256 contiguous bytes (the whole pixel when BN == 128)
-          uint8_t* gbase = reinterpret_cast<uint8_t*>(p.out + pix0 * BN + hf * 128);
-#pragma unroll 4
-          for (int i = 0; i < 16; ++i) {
-            const int px = 2 * i + (lane >> 4), c = lane & 15;
-            const uint4 o = *reinterpret_cast<const uint4*>(stg + px * 256 + ((c ^ (px & 7)) << 4));
-            if (pix0 + px < p.npix) *reinterpret_cast<uint4*>(gbase + (size_t)px * (BN * 2) + c * 16) = o;
-          }
-        } else {
-          const unsigned long long rowoff = (unsigned long long)hf * (2ULL * p.W) * (BN / 4) * 2;   // hi-res row 2y+py
-#pragma unroll 4
-          for (int i = 0; i < 16; ++i) {
-            const int h = 4 * i + (lane >> 3), cc = lane & 7;     // hi-res pixel within the warp's 64, chunk
-            const int xl = h >> 1, pxp = h & 1;
-            const unsigned long long ob = __shfl_sync(0xffffffffu, obase, xl);
-            const int c = pxp * 8 + cc;
-            const uint4 o = *reinterpret_cast<const uint4*>(stg + xl * 256 + ((c ^ (xl & 7)) << 4));
-            if (ob) *reinterpret_cast<uint4*>(ob + rowoff + pxp * (BN / 4) * 2 + cc * 16) = o;
-          }
-        }
-        __syncwarp();
+        ptx::fence_proxy_async_smem();               // the row was written through the generic proxy
+        if (valid) ptx::bulk_store(obase + hf * half_stride, stg_s, 256);
+        ptx::bulk_commit();
       }
     }
+    ptx::bulk_wait_all0();                           // global writes complete before the CTA exits
   }
   ptx::tc_fence_before();
   __syncthreads();

@@ -351,7 +351,7 @@ int launch_i27(vex_ctx* ctx, unsigned abit, const void* in, const uint8_t* w, co
   }
   thin::I27Params p;
   p.in = in; p.wpack = w; p.bias = bias; p.out = out; p.H = H; p.W = W;
-  p.npix = (long long)n * H * W; p.in_bgr = in_bgr;
+  p.npix = (long long)n * H * W; p.in_bgr = in_bgr; p.probe = ctx->opt_thin_probe;
   const long long items = (p.npix + 127) / 128;
   thin::im2col27_kernel<MODE, BN><<<(unsigned)std::min<long long>(items, ctx->sm_count), thin::I27_THREADS, C::SMEM, s>>>(p);
   ctx->launches++;

@@ -56,6 +56,7 @@ struct I27Params {
   int H, W;
   long long npix;          // n*H*W
   int in_bgr;
+  int probe;               // bring-up timing probes (WRONG RESULTS): 1 = no global stores, 2 = no TMEM drain, 4 = no gather loads
 };
 
 template <int MODE, int BN>
@@ -103,7 +104,7 @@ im2col27_kernel(const I27Params p) {
       uint32_t w[16];
 #pragma unroll
       for (int j = 0; j < 16; ++j) w[j] = 0u;
-      if (pix < p.npix) {
+      if (pix < p.npix && !(p.probe & 4)) {
         const int x = (int)(pix % p.W);
         const long long t = pix / p.W;
         const int y = (int)(t % p.H);
@@ -205,7 +206,7 @@ im2col27_kernel(const I27Params p) {
       for (int hf = 0; hf < HALVES; ++hf) {
         ptx::bulk_wait_read0();                      // this lane's previous bulk store has finished reading its row
 #pragma unroll 1
-        for (int g = 0; g < 4; ++g) {
+        for (int g = (p.probe & 2) ? 4 : 0; g < 4; ++g) {
           uint32_t v[32];
           const int col = hf * 128 + g * 32;
           ptx::tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + b * BN + col, v);
@@ -226,7 +227,9 @@ im2col27_kernel(const I27Params p) {
           if (lane == 0) ptx::mbar_arrive(acc_empty + 8 * b);
         }
         ptx::fence_proxy_async_smem();               // the row was written through the generic proxy
-        if (valid) ptx::bulk_store(obase + hf * half_stride, stg_s, 256);
+        if (p.probe & 8) {                           // probe: half as many ops, 512 B each (garbage payload)
+          if (valid && !(lane & 1)) ptx::bulk_store(obase + hf * half_stride, stg_s, 512);
+        } else if (valid && !(p.probe & 1)) ptx::bulk_store(obase + hf * half_stride, stg_s, 256);
         ptx::bulk_commit();
       }
     }

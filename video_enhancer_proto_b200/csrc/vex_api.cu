@@ -216,6 +216,7 @@ int vex_set_option(vex_ctx* ctx, const char* name, int value) {
   else if (!strcmp(name, "force_generic_bicubic")) slot = &ctx->opt_force_generic_bicubic;
   else if (!strcmp(name, "bicubic_rows")) slot = &ctx->opt_bicubic_rows;
   else if (!strcmp(name, "conv_variant")) slot = &ctx->opt_conv_variant;
+  else if (!strcmp(name, "thin_probe")) slot = &ctx->opt_thin_probe;
   else if (!strcmp(name, "conv3_bn")) slot = &ctx->opt_conv3_bn;
   else if (!strcmp(name, "ws_budget_mb")) slot = &ctx->opt_ws_budget_mb;
   else if (!strcmp(name, "profile")) slot = &ctx->opt_profile;

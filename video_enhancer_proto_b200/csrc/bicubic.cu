@@ -93,12 +93,12 @@ __device__ __forceinline__ uint32_t magic_f(const uint32_t (&raw)[7]) {
   return prmt(raw[IDX >> 2], 0x47000000u, 0x7000u | (ZSEL << 8) | ((IDX & 3) << 4) | ZSEL);
 }
 
-// this lane's three 16-byte destinations of an output row pair (2 rows x 48 vectors per warp)
+// this lane's destinations of an output row pair (2 rows x 48 vectors of 16 B per warp): vector `lane` of each row,
+// and lanes 0..15 also vector 32 + lane.  Two running pointers and immediate offsets - no per-lane offset registers.
 struct LaneOut {
-  uint8_t* p1;          // running: output row 2i, vector `lane`
-  uint32_t d2, d3;      // byte distance from p1 to the second / third destination
-  int s2;               // staging vector of the second destination (first = lane, third = 64 + lane)
-  bool ok1, ok2, ok3;
+  uint8_t* pa;          // running: output row 2i, vector `lane`
+  uint8_t* pb;          // running: output row 2i + 1, vector `lane`
+  bool ok1, ok2;        // vector `lane` / vector 32 + lane (lanes 0..15) lies inside the row
 };
 __device__ __forceinline__ void stg_v4_if(void* p, const uint4& v, bool pred) {
   asm volatile(
@@ -188,12 +188,13 @@ __device__ __forceinline__ void strip_step(u64 (&S)[4][12], uint32_t (&raw)[7], 
       so[2] = make_uint2(b1, b2);
     }
     __syncwarp();
-    // 96 x 16 B (2 rows x 48) leave in three fully coalesced passes; o1/o2/o3 are this lane's three
-    // destinations, sidx* the matching staging vectors, pr* the (row-in-image && column-in-image) predicates
+    // 96 x 16 B (2 rows x 48) leave in four coalesced passes (two of them half warps)
     const uint4* sv = reinterpret_cast<const uint4*>(stage);
-    stg_v4_if(o.p1, sv[lane], o.ok1 && store_ok);
-    stg_v4_if(o.p1 + o.d2, sv[o.s2], o.ok2 && store_ok);
-    stg_v4_if(o.p1 + o.d3, sv[64 + lane], o.ok3 && store_ok);
+    const bool k1 = o.ok1 && store_ok, k2 = o.ok2 && store_ok;
+    stg_v4_if(o.pa, sv[lane], k1);
+    stg_v4_if(o.pb, sv[48 + lane], k1);
+    stg_v4_if(o.pa + 512, sv[32 + lane], k2);
+    stg_v4_if(o.pb + 512, sv[80 + lane], k2);
   }
 }
 
@@ -238,6 +239,15 @@ bicubic2x_strip_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out
                    : "memory");
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
+  const uint8_t* nsrc;                                        // source of the next row to issue (clamped in y)
+  auto issue_next = [&](int y, int slot) {                    // y = unclamped row of nsrc
+    if (chunk_lane)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(ring_dst + slot * RING_ROW),
+                   "l"(nsrc), "r"(chunk_bytes)
+                   : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    if ((unsigned)y < (unsigned)(H - 1)) nsrc += in_row;
+  };
   auto fetch_row = [&](int slot, uint32_t(&r)[7]) {          // the row issued RING_D steps ago has landed
     asm volatile("cp.async.wait_group %0;" ::"n"(RING_D - 1) : "memory");
     __syncwarp();
@@ -251,25 +261,22 @@ bicubic2x_strip_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out
   LaneOut o;
   {
     uint8_t* orow = out + (size_t)f * 2 * H * out_row + (size_t)xw * STAGE_ROW + (size_t)(2 * r0) * out_row;
-    const int row = lane >> 4, vv = row ? lane - 16 : lane + 32;
-    o.p1 = orow + 16 * lane;
+    o.pa = orow + 16 * lane;
+    o.pb = o.pa + out_row;
     o.ok1 = lane < valid_vecs;
-    o.d2 = (uint32_t)(row * out_row + 16 * vv - 16 * lane);
-    o.s2 = row * 48 + vv;
-    o.ok2 = vv < valid_vecs;
-    o.d3 = (uint32_t)(out_row + 256);
-    o.ok3 = lane + 16 < valid_vecs;
+    o.ok2 = lane < 16 && lane + 32 < valid_vecs;
   }
   const size_t adv = 2 * out_row;
   // step s handles input row q = r0 - 2 + s from ring slot s % RING_SLOTS and issues row q + RING_D
   int q = r0 - 2;
 #pragma unroll
   for (int d = 0; d < RING_D; ++d) issue_row(q + d, d);
+  nsrc = fsrc + (size_t)((uint32_t)min(max(q + RING_D, 0), H - 1) * in_row);
 #define VEX_STEP(K, EMIT, SLOT, OK)                                   \
   {                                                                   \
   const bool ok_ = OK;                                                \
   fetch_row((SLOT) & (RING_SLOTS - 1), raw);                          \
-  issue_row(q + RING_D, ((SLOT) + RING_D) & (RING_SLOTS - 1));        \
+  issue_next(q + RING_D, ((SLOT) + RING_D) & (RING_SLOTS - 1));       \
   ++q;                                                                \
   strip_step<ROUND, K, EMIT>(S, raw, left, right, stage, o, ok_, lane); \
   }
@@ -279,17 +286,32 @@ bicubic2x_strip_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out
   VEX_STEP(3, false, 3, false)
   // main loop: the step that consumes input row q emits output rows 2(q-2), 2(q-2)+1
   const int qend = min(r0 + R, H) + 2;
-  int sl = 4;
 #pragma unroll 1
-  for (; q < qend; sl += 4) {
-    VEX_STEP(0, true, sl, true)
-    o.p1 += adv;
-    VEX_STEP(1, true, sl + 1, q < qend)
-    o.p1 += adv;
-    VEX_STEP(2, true, sl + 2, q < qend)
-    o.p1 += adv;
-    VEX_STEP(3, true, sl + 3, q < qend)
-    o.p1 += adv;
+  for (; q < qend;) {
+    VEX_STEP(0, true, 4, true)
+    o.pa += adv;
+    o.pb += adv;
+    VEX_STEP(1, true, 5, q < qend)
+    o.pa += adv;
+    o.pb += adv;
+    VEX_STEP(2, true, 6, q < qend)
+    o.pa += adv;
+    o.pb += adv;
+    VEX_STEP(3, true, 7, q < qend)
+    o.pa += adv;
+    o.pb += adv;
+    VEX_STEP(0, true, 0, q < qend)
+    o.pa += adv;
+    o.pb += adv;
+    VEX_STEP(1, true, 1, q < qend)
+    o.pa += adv;
+    o.pb += adv;
+    VEX_STEP(2, true, 2, q < qend)
+    o.pa += adv;
+    o.pb += adv;
+    VEX_STEP(3, true, 3, q < qend)
+    o.pa += adv;
+    o.pb += adv;
   }
 #undef VEX_STEP
   asm volatile("cp.async.wait_group 0;" ::: "memory");

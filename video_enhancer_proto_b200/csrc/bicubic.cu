@@ -71,7 +71,9 @@ __device__ __forceinline__ uint32_t pack4(float b0, float b1, float b2, float b3
   return r;
 }
 
-constexpr int STRIP_WARPS = 4;            // warps per block, each fully independent
+constexpr int STRIP_WARPS = 1;            // warps per block: one, so that every loop bound and ring slot is provably
+                                          // warp-uniform (uniform datapath, no divergence check around __syncwarp)
+constexpr int RESIDENT_WARPS = 12;        // per SM at 168 registers
 constexpr int WARP_PX = 128;              // input pixels per warp row segment: lane = 4 px = 2 strips x 2 px
 constexpr int STAGE_ROW = WARP_PX * 6;    // 768 output bytes per warp per output row
 constexpr int RING_D = 6;                 // input rows in flight per warp (cp.async groups)
@@ -203,7 +205,7 @@ __device__ __forceinline__ void strip_step(u64 (&S)[4][12], uint32_t (&raw)[7], 
 // registers held while they fly): 26 lanes copy the warp's 416-byte row segment [S-16, S+400) as 16-byte chunks,
 // chunks outside the row are zero-filled (src-size 0) and rebuilt by the border replicate.
 template <int ROUND>
-__global__ void __launch_bounds__(STRIP_WARPS * 32, 3)
+__global__ void __launch_bounds__(STRIP_WARPS * 32, RESIDENT_WARPS / STRIP_WARPS)
 bicubic2x_strip_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int H, int W, int R,
                        int wpr, int nstrips, int total_warps) {
   __shared__ __align__(16) uint8_t s_stage[STRIP_WARPS][2 * STAGE_ROW];
@@ -375,9 +377,9 @@ int launch_bicubic2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h
   if (w % 16 == 0 && aligned && !ctx->opt_force_generic_bicubic) {
     const int wpr = (w + WARP_PX - 1) / WARP_PX;
     // rows per strip: tall strips amortise the 4-row window warm-up (measured: 120 rows +3 % over 40); take the
-    // tallest strip that still gives every resident warp slot (3 blocks x 4 warps per SM) one strip
+    // tallest strip that still gives every resident warp slot (12 per SM) one strip
     int R = 8;
-    const long long want = (long long)ctx->sm_count * 3 * STRIP_WARPS;
+    const long long want = (long long)ctx->sm_count * RESIDENT_WARPS;
     for (int cand : {120, 60, 40, 24, 16}) {
       if ((long long)n * ((h + cand - 1) / cand) * wpr >= want) { R = cand; break; }
     }

@@ -1,0 +1,98 @@
+"""Host-side video pipeline: ordering, slot rotation, back-pressure and error propagation of
+the reader -> GPU -> writer threads.  No CUDA here; the GPU stage is a stand-in callback."""
+import threading
+import time
+
+import numpy as np
+import pytest
+
+from video_enhancer_proto_b200 import pipeline
+
+
+def make_reader(n_batches, delay=0.0):
+    it = iter(range(n_batches))
+
+    def read():
+        if delay:
+            time.sleep(delay)
+        return next(it, None)
+    return read
+
+
+def test_order_count_and_threads():
+    seen, threads = [], set()
+
+    def process(b, slot):
+        threads.add(("p", threading.current_thread().name))
+        return b * 10
+
+    def write(r):
+        threads.add(("w", threading.current_thread().name))
+        seen.append(r)
+
+    n = pipeline.run_ordered_pipeline(make_reader(37), process, write, depth=2)
+    assert n == 37 and seen == [10 * i for i in range(37)]
+    assert ("w", "vex-writer") in threads and ("p", threading.current_thread().name) in threads
+
+
+def test_empty_stream():
+    assert pipeline.run_ordered_pipeline(lambda: None, lambda b, s: b, lambda r: None) == 0
+
+
+@pytest.mark.parametrize("depth", [1, 2, 4])
+def test_slot_not_reused_while_writer_holds_it(depth):
+    """Results alias per-slot buffers (the pinned output buffers of the real path): with a slow writer the producer
+    must block instead of overwriting a slot that is still queued or being written."""
+    bufs = [np.zeros(4, np.int64) for _ in range(pipeline.n_slots(depth))]
+    got = []
+
+    def process(b, slot):
+        bufs[slot][:] = b
+        return bufs[slot]
+
+    def write(r):
+        time.sleep(0.003)
+        got.append(int(r[0]))
+        assert (r == r[0]).all()
+
+    pipeline.run_ordered_pipeline(make_reader(40), process, write, depth=depth)
+    assert got == list(range(40))
+
+
+def test_slow_reader_and_fast_writer():
+    got = []
+    pipeline.run_ordered_pipeline(make_reader(12, delay=0.002), lambda b, s: b, got.append, depth=2)
+    assert got == list(range(12))
+
+
+@pytest.mark.parametrize("stage", ["read", "process", "write"])
+def test_errors_propagate_and_nothing_hangs(stage):
+    it = iter(range(1000))
+
+    def read():
+        v = next(it)
+        if stage == "read" and v == 5:
+            raise OSError("decode failed")
+        return v
+
+    def process(b, slot):
+        if stage == "process" and b == 5:
+            raise RuntimeError("vex_upscale_host failed")
+        return b
+
+    def write(r):
+        if stage == "write" and r == 5:
+            raise IOError("encode failed")
+
+    t0 = time.time()
+    with pytest.raises((OSError, RuntimeError, IOError)) as ei:
+        pipeline.run_ordered_pipeline(read, process, write, depth=2)
+    assert "failed" in str(ei.value)
+    assert time.time() - t0 < 5.0
+    time.sleep(0.2)
+    assert not [t for t in threading.enumerate() if t.name in ("vex-reader", "vex-writer")]
+
+
+def test_bad_depth():
+    with pytest.raises(ValueError):
+        pipeline.run_ordered_pipeline(lambda: None, lambda b, s: b, lambda r: None, depth=0)

@@ -26,7 +26,7 @@ from typing import Dict, List, Mapping, Optional, Sequence
 import numpy as np
 import torch
 
-from . import _lib, weights as W
+from . import _lib, pipeline, weights as W
 
 logger = logging.getLogger(__name__)
 
@@ -43,6 +43,7 @@ class B200VideoEnhancer:
         self.model_name = model_name
         self.scale = scale
         self.batch_size = batch_size                      # app.py:453
+        self.pipeline_depth = 2                           # batches queued either side of the GPU in the video loop
         self.models_loaded = False
         self.processing_stats = {"total_processed": 0, "total_time": 0.0}   # app.py:236-240
         self.job_history: List[Dict] = []
@@ -141,8 +142,9 @@ class B200VideoEnhancer:
                 raise ValueError("frames must be uint8 HWC with 3 channels and one common size")
         return h, w
 
-    def _run_host(self, mode: int, frames: Sequence[np.ndarray], flags: int) -> np.ndarray:
-        """frames (host) -> [n, 2h, 2w, 3] uint8 (host) through vex_upscale_host."""
+    def _run_host(self, mode: int, frames: Sequence[np.ndarray], flags: int, slot: int = 0) -> np.ndarray:
+        """frames (host) -> [n, 2h, 2w, 3] uint8 (host) through vex_upscale_host.  The result is a view of the
+        pinned output buffer of `slot`; it stays valid until the next call with the same slot."""
         self._ensure_ctx()
         if mode == _lib.VEX_MODE_CNN:
             self._ensure_weights()
@@ -150,7 +152,7 @@ class B200VideoEnhancer:
         n = len(frames)
         fin = h * w * 3
         pin_in = self._pinned_buf("in", n * fin)
-        pin_out = self._pinned_buf("out", n * fin * 4)
+        pin_out = self._pinned_buf(f"out{slot}", n * fin * 4)
         vin = pin_in.numpy()[: n * fin].reshape(n, h, w, 3)
         for i, f in enumerate(frames):
             vin[i] = f
@@ -310,32 +312,32 @@ class B200VideoEnhancer:
             out = cv2.VideoWriter(output_path, fourcc, out_fps, (width * 2, height * 2))
             if not out.isOpened():
                 raise ValueError(f"Could not create output video: {output_path}")
+            mode = _lib.VEX_MODE_BICUBIC if self._use_bicubic() else _lib.VEX_MODE_CNN
+            # cv2 frames are BGR.  bicubic is channel-agnostic (basic_upscaler_fallback.py:142); for the CNN the
+            # frames stay BGR on the host and in_bgr|out_bgr do app.py:469 and :550 inside the kernels
+            flags = 1 if mode == _lib.VEX_MODE_BICUBIC else 0b11
             n_done = 0
-            batch: List[np.ndarray] = []
 
-            def flush():
+            def read_batch():
+                batch: List[np.ndarray] = []
+                while len(batch) < self.batch_size:
+                    ret, frame = cap.read()
+                    if not ret:
+                        break
+                    batch.append(frame)
+                return batch or None
+
+            def process(batch, slot):
+                return self._run_host(mode, batch, flags, slot=slot)
+
+            def write(res):
                 nonlocal n_done
-                if not batch:
-                    return
-                if self._use_bicubic():
-                    # cv2 frames are BGR; bicubic is channel-agnostic (basic_upscaler_fallback.py:142)
-                    res = self._run_host(_lib.VEX_MODE_BICUBIC, batch, flags=1)
-                else:
-                    # frames stay BGR on the host: in_bgr|out_bgr do app.py:469 and :550 inside the kernels
-                    res = self._run_host(_lib.VEX_MODE_CNN, batch, flags=0b11)
                 for i in range(res.shape[0]):
                     out.write(res[i])
-                n_done += len(batch)
-                batch.clear()
+                n_done += res.shape[0]
 
-            while True:
-                ret, frame = cap.read()
-                if not ret:
-                    break
-                batch.append(frame)
-                if len(batch) >= self.batch_size:
-                    flush()
-            flush()
+            # decode and encode on their own threads, the GPU call on this one
+            pipeline.run_ordered_pipeline(read_batch, process, write, depth=self.pipeline_depth)
         finally:
             cap.release()
             if out is not None:

@@ -63,16 +63,23 @@ int vex_bicubic2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc,
 /* Channel plan of the AdvancedUpscaler family (app.py:269-301):
  *   conv1 3->c1, conv2 c1->c2 (+skip, needs c1==c2), conv3 c2->c3, conv4 c3->c4, conv5 c4->3,
  *   upconv1 ConvT 3->up_ch k4 s2 p1, upconv2 ConvT up_ch->3 k3 s1 p1.
- * The reference is {128,128,256,128,64}.  Widths must be multiples of 128 in [128, 512]; up_ch 64. */
+ * The reference is {128,128,256,128,64}.  Widths must be multiples of 128 in [128, 512]; up_ch 64.
+ * n_extra (0 for the reference, at most VEX_CNN_MAX_EXTRA) deepens the plan for BASELINE.json configs[4]:
+ * after conv3, n_extra more blocks conv3x3 c3->c3 + BatchNorm + ReLU of the same kind as app.py:293. */
 typedef struct vex_cnn_desc {
   int c1, c2, c3, c4, up_ch;
   float bn_eps;              /* 1e-5 (nn.BatchNorm2d default, app.py:284-287) */
+  int n_extra;
 } vex_cnn_desc;
 
 #define VEX_CNN_NUM_TENSORS 30
+#define VEX_CNN_MAX_EXTRA 4
+#define VEX_CNN_TENSORS_PER_EXTRA 6
 /* tensors[i]: fp32 host arrays in the reference module's state_dict order (app.py:273-287):
  *   conv1..conv5 {weight,bias}, upconv1 {weight,bias}, upconv2 {weight,bias},
- *   bn1..bn4 {weight,bias,running_mean,running_var}     (num_batches_tracked is skipped).
+ *   bn1..bn4 {weight,bias,running_mean,running_var}     (num_batches_tracked is skipped),
+ *   then per extra block k = 1..n_extra: conv3x<k> {weight,bias}, bn3x<k> {weight,bias,running_mean,running_var};
+ *   n_tensors = VEX_CNN_NUM_TENSORS + VEX_CNN_TENSORS_PER_EXTRA * n_extra.
  * Folds eval-mode BN into per-channel scale/shift, converts weights to bf16 in the kernels'
  * layouts, uploads.  Copies; the caller keeps ownership.  Replaces _create_gpu_upscaler
  * (app.py:265-311) minus the random init (the caller supplies the values). */
@@ -89,13 +96,14 @@ int vex_cnn2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc,
 
 /* Parity hook: same network, pre-quantisation fp32 output, NCHW [n][3][2h][2w] (device).
  * `tap` selects what is written: 0 = final clamp(upconv2) (app.py:299); 1..5 = x1..x5
- * (NCHW fp32, [n][C][h][w]); 6 = relu(upconv1) ([n][up_ch][2h][2w]). */
+ * (NCHW fp32, [n][C][h][w]; with n_extra > 0, x3 is the output of conv3 itself); 6 = relu(upconv1)
+ * ([n][up_ch][2h][2w]); 7 + k = output of extra block k + 1 ([n][c3][h][w]). */
 int vex_cnn2x_f32_debug(vex_ctx* ctx, const uint8_t* in_hwc, float* out_nchw,
                         int n, int h, int w, int in_bgr, int tap, void* stream);
 
 /* Per-layer device time (ms, CUDA events on the caller's stream) of the most recent vex_cnn2x_u8 /
  * vex_cnn2x_f32_debug(tap 0) call made while option "profile" is 1:
- * ms7 = {conv1, conv2, conv3, conv4, conv5, upconv1, upconv2}; sub-batches are summed.  Synchronises on
+ * ms7 = {conv1, conv2, conv3 (+ extra blocks), conv4, conv5, upconv1, upconv2}; sub-batches are summed.  Synchronises on
  * the last event.  (The reference has no per-layer timing; its PerformanceTracker,
  * utils/performance_monitor.py:178, only wraps whole videos.) */
 int vex_cnn_profile_ms(vex_ctx* ctx, float* ms7);

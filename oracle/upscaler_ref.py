@@ -38,13 +38,15 @@ STATE_DICT_KEYS = (
 class AdvancedUpscalerRef(nn.Module):
     """Restatement of ``AdvancedUpscaler`` (app.py:269-301), generalised to a channel plan.
 
-    ``widths=(128, 128, 256, 128)`` and ``up_ch=64`` reproduce the reference exactly.  Other
-    plans give the "widened/deepened variant" of BASELINE.json configs[4] (same layer kinds).
+    ``widths=(128, 128, 256, 128)``, ``up_ch=64`` and ``extra=0`` reproduce the reference exactly.  Other
+    plans give the "widened/deepened variant" of BASELINE.json configs[4] (same layer kinds): ``extra`` more
+    conv3x3 + BatchNorm + ReLU blocks of width c3 after conv3, named conv3x<k> / bn3x<k>.
     """
 
-    def __init__(self, widths: Sequence[int] = (128, 128, 256, 128), up_ch: int = 64):
+    def __init__(self, widths: Sequence[int] = (128, 128, 256, 128), up_ch: int = 64, extra: int = 0):
         super().__init__()
         c1, c2, c3, c4 = widths
+        self.extra = extra
         assert c1 == c2, "skip connection x2 = relu(bn2(conv2(x1))) + x1 needs equal widths"
         self.conv1 = nn.Conv2d(3, c1, 3, padding=1)        # app.py:273
         self.conv2 = nn.Conv2d(c1, c2, 3, padding=1)       # app.py:274
@@ -57,17 +59,24 @@ class AdvancedUpscalerRef(nn.Module):
         self.bn2 = nn.BatchNorm2d(c2)                      # app.py:285
         self.bn3 = nn.BatchNorm2d(c3)                      # app.py:286
         self.bn4 = nn.BatchNorm2d(c4)                      # app.py:287
+        for k in range(1, extra + 1):                      # not in the reference: configs[4] only
+            setattr(self, f"conv3x{k}", nn.Conv2d(c3, c3, 3, padding=1))
+            setattr(self, f"bn3x{k}", nn.BatchNorm2d(c3))
 
     def forward(self, x, taps: Dict[str, torch.Tensor] | None = None):
         x1 = F.relu(self.bn1(self.conv1(x)))               # app.py:291
         x2 = F.relu(self.bn2(self.conv2(x1))) + x1         # app.py:292 (skip AFTER relu)
         x3 = F.relu(self.bn3(self.conv3(x2)))              # app.py:293
-        x4 = F.relu(self.bn4(self.conv4(x3)))              # app.py:294
+        xe, mids = x3, {}
+        for k in range(1, self.extra + 1):                 # same block kind as app.py:293
+            xe = F.relu(getattr(self, f"bn3x{k}")(getattr(self, f"conv3x{k}")(xe)))
+            mids[f"x3e{k}"] = xe
+        x4 = F.relu(self.bn4(self.conv4(xe)))              # app.py:294
         x5 = self.conv5(x4)                                # app.py:295
         up = F.relu(self.upconv1(x5))                      # app.py:298
         out = torch.clamp(self.upconv2(up), 0, 1)          # app.py:299
         if taps is not None:
-            taps.update(x1=x1, x2=x2, x3=x3, x4=x4, x5=x5, up=up, out=out)
+            taps.update(x1=x1, x2=x2, x3=x3, x4=x4, x5=x5, up=up, out=out, **mids)
         return out
 
 
@@ -82,12 +91,12 @@ def init_reference_weights(model: nn.Module) -> nn.Module:
     return model
 
 
-def make_model(seed: int = 0, widths=(128, 128, 256, 128), up_ch: int = 64) -> AdvancedUpscalerRef:
+def make_model(seed: int = 0, widths=(128, 128, 256, 128), up_ch: int = 64, extra: int = 0) -> AdvancedUpscalerRef:
     # The reference never seeds (app.py:303-311); parity runs seed once, then construct and
     # run the init loop exactly as ``_create_gpu_upscaler`` does, so that the AST-extracted
     # reference class under the same seed yields bit-identical tensors (oracle/make_golden.py).
     torch.manual_seed(seed)
-    m = AdvancedUpscalerRef(widths, up_ch)
+    m = AdvancedUpscalerRef(widths, up_ch, extra)
     init_reference_weights(m)
     return m.eval()                                        # app.py:331, 428
 
@@ -118,7 +127,11 @@ def make_stress_model(seed: int = 7, gain: float = 1.0) -> AdvancedUpscalerRef:
 
 def export_state(model: nn.Module) -> "collections.OrderedDict[str, np.ndarray]":
     sd = model.state_dict()
-    return collections.OrderedDict((k, sd[k].detach().cpu().float().contiguous().numpy()) for k in STATE_DICT_KEYS)
+    keys = list(STATE_DICT_KEYS)
+    for k in range(1, getattr(model, "extra", 0) + 1):
+        keys += [f"conv3x{k}.weight", f"conv3x{k}.bias"]
+        keys += [f"bn3x{k}.{p}" for p in ("weight", "bias", "running_mean", "running_var")]
+    return collections.OrderedDict((k, sd[k].detach().cpu().float().contiguous().numpy()) for k in keys)
 
 
 # ----------------------------------------------------------------------------- CNN path

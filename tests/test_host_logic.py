@@ -31,7 +31,21 @@ def test_normalize_state_rejects_bad_shapes():
     del bad["conv3.weight"]
     with pytest.raises(KeyError):
         W.normalize_state(bad)
-    assert W.infer_plan(st) == ((128, 128, 256, 128), 64)
+    assert W.infer_plan(st) == ((128, 128, 256, 128), 64, 0)
+
+
+def test_deepened_plan_state_matches_oracle_order_and_values():
+    """configs[4]: extra conv3x<k>/bn3x<k> blocks are appended after the reference's 30 tensors, and the init
+    procedure draws them in module order exactly like the oracle's model."""
+    from oracle import upscaler_ref as O
+    a = W.init_state(3, widths=(128, 128, 256, 128), n_extra=2)
+    b = O.export_state(O.make_model(3, widths=(128, 128, 256, 128), extra=2))
+    assert list(a) == list(b) and len(a) == 30 + 6 * 2
+    assert list(a)[:30] == list(W.STATE_DICT_KEYS) and list(a)[30:32] == ["conv3x1.weight", "conv3x1.bias"]
+    for k in a:
+        assert np.array_equal(a[k], b[k]), k
+    assert W.infer_plan(a) == ((128, 128, 256, 128), 64, 2)
+    assert a["conv3x2.weight"].shape == (256, 256, 3, 3)
 
 
 @pytest.mark.parametrize("world,n", [(1, 5), (2, 5), (4, 3000), (8, 3000), (8, 3), (3, 0)])

@@ -14,4 +14,4 @@ for probe in ([int(a) for a in sys.argv[1:]] or (0, 1, 2, 4, 3, 5, 6, 7, 0)):
     for rep in range(4):
         enh.upscale_device(f, mode="cnn", out=out); torch.cuda.synchronize()
         if rep: acc.append(enh.cnn_profile_ms())
-    print("probe", probe, {k: round(float(np.mean([a[k] for a in acc])), 3) for k in ("conv1", "upconv1")}, flush=True)
+    print("probe", probe, {k: round(float(np.mean([a[k] for a in acc])), 3) for k in ("conv1", "upconv1", "upconv2")}, flush=True)

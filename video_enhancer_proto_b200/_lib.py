@@ -10,11 +10,13 @@ LIB_PATH = os.path.join(HERE, "libvex.so")
 VEX_MODE_BICUBIC = 0
 VEX_MODE_CNN = 1
 VEX_CNN_NUM_TENSORS = 30
+VEX_CNN_MAX_EXTRA = 4
+VEX_CNN_TENSORS_PER_EXTRA = 6
 
 
 class VexCnnDesc(C.Structure):
     _fields_ = [("c1", C.c_int), ("c2", C.c_int), ("c3", C.c_int), ("c4", C.c_int), ("up_ch", C.c_int),
-                ("bn_eps", C.c_float)]
+                ("bn_eps", C.c_float), ("n_extra", C.c_int)]
 
 
 # name -> (restype, argtypes); must list every symbol include/vex.h declares (tests check this)

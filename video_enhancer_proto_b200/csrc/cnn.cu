@@ -16,6 +16,7 @@
 #include "conv_tc2.cuh"
 #include "conv_tc3.cuh"
 #include "thin_tc.cuh"
+#include "tail_tc.cuh"
 #include "vex_internal.cuh"
 
 namespace vex {
@@ -35,8 +36,10 @@ struct CnnPlan {
   float *wu1 = nullptr, *bu1 = nullptr;      // upconv1: [4][12][up], [up]
   float *wu2 = nullptr, *bu2 = nullptr;      // upconv2: [up/64][9][64][4], [3]
   TcLayer tc[3];                             // conv2, conv3, conv4
+  TcLayer extra[VEX_CNN_MAX_EXTRA];          // deepened plans: c3 -> c3 blocks after conv3
   // thin layers on the tensor cores (thin_tc.cuh): SWIZZLE_128B operand images, bf16
   uint8_t *t1w = nullptr, *tu1w = nullptr, *t5w = nullptr, *tu2w = nullptr;
+  uint8_t* tu1wb = nullptr;                  // tu1w with the bias in k = 27, 28 (fused tail, tail_tc.cuh)
   float* tu1b = nullptr;                     // upconv1 bias replicated per PixelShuffle phase [4*up]
   // workspace
   uint8_t* ws = nullptr;
@@ -385,10 +388,32 @@ int launch_g27(vex_ctx* ctx, unsigned abit, const __nv_bfloat16* in, int C, cons
   return VEX_OK;
 }
 
+// x5 [n][H][W] -> uint8 [n][2H][2W][3]: upconv1 + relu + upconv2 + clamp + quantise in one kernel (tail_tc.cuh)
+int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_t* w2, const float* b2,
+                  uint8_t* out_u8, float* out_nchw, int n, int H, int W, int out_bgr, cudaStream_t s) {
+  if (!(ctx->attr_mask & 0x400u)) {
+    VEX_CUDA(ctx, cudaFuncSetAttribute(thin::uptail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       thin::UTCfg::SMEM));
+    ctx->attr_mask |= 0x400u;
+  }
+  thin::UTParams p;
+  p.x5 = reinterpret_cast<const float4*>(x5); p.w1pack = w1; p.w2pack = w2; p.bias2 = b2;
+  p.out_u8 = out_u8; p.out_nchw = out_nchw; p.H = H; p.W = W;
+  p.tiles_x = (2 * W + thin::G27_TW - 1) / thin::G27_TW;
+  p.tiles_y = (2 * H + thin::G27_ROWS - 1) / thin::G27_ROWS;
+  p.n_img = n; p.out_bgr = out_bgr; p.probe = ctx->opt_thin_probe;
+  const long long total = (long long)p.tiles_x * p.tiles_y * n;
+  if (total > 0x7fffffffLL) return fail(ctx, VEX_ERR_INVALID, "uptail: too many tiles");
+  thin::uptail_kernel<<<(unsigned)std::min<long long>(total, ctx->sm_count), thin::UT_THREADS, thin::UTCfg::SMEM, s>>>(p);
+  ctx->launches++;
+  VEX_CUDA(ctx, cudaGetLastError());
+  return VEX_OK;
+}
+
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct Layout {
-  size_t a, b, c, x5, total;     // offsets: bufA (x1/x4), bufB (x2), bufC (x3/up), x5
+  size_t a, b, c, d, x5, total;  // offsets: bufA (x1/x4), bufB (x2), bufC (x3/up), bufD (extra blocks), x5
 };
 Layout ws_layout(const vex_cnn_desc& d, size_t npix) {
   Layout L;
@@ -396,6 +421,7 @@ Layout ws_layout(const vex_cnn_desc& d, size_t npix) {
   L.a = off; off += align_up(npix * std::max(d.c1, d.c4) * 2, 1024);
   L.b = off; off += align_up(npix * d.c2 * 2, 1024);
   L.c = off; off += align_up(npix * std::max(d.c3, 4 * d.up_ch) * 2, 1024);
+  L.d = off; off += d.n_extra > 0 ? align_up(npix * d.c3 * 2, 1024) : 0;
   L.x5 = off; off += align_up(npix * 16, 1024);
   L.total = off;
   return L;
@@ -406,8 +432,10 @@ Layout ws_layout(const vex_cnn_desc& d, size_t npix) {
 // ------------------------------------------------------------------------------------------- weights
 
 int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const* t, int n_tensors) {
-  if (!arch || !t || n_tensors != VEX_CNN_NUM_TENSORS)
-    return fail(ctx, VEX_ERR_INVALID, "vex_cnn_load_weights: need 30 tensors in state_dict order");
+  if (!arch || !t || arch->n_extra < 0 || arch->n_extra > VEX_CNN_MAX_EXTRA ||
+      n_tensors != VEX_CNN_NUM_TENSORS + VEX_CNN_TENSORS_PER_EXTRA * arch->n_extra)
+    return fail(ctx, VEX_ERR_INVALID,
+                "vex_cnn_load_weights: need 30 + 6 * n_extra tensors in state_dict order, n_extra in [0,4]");
   for (int i = 0; i < n_tensors; ++i)
     if (!t[i]) return fail(ctx, VEX_ERR_INVALID, "vex_cnn_load_weights: null tensor");
   const int c1 = arch->c1, c2 = arch->c2, c3 = arch->c3, c4 = arch->c4, up = arch->up_ch;
@@ -463,6 +491,23 @@ int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const*
         L.w_folded[(size_t)co * L.cin * 9 + j] = cw[l + 1][(size_t)co * L.cin * 9 + j] * scale[l + 1][co];
     if ((rc = pack_tc(ctx, L))) return rc;
     if ((rc = upload(ctx, &L.bias, shift[l + 1].data(), (size_t)L.cout * 4))) return rc;
+  }
+  for (int e = 0; e < arch->n_extra; ++e) {  // deepened plans: conv3x<e+1> c3 -> c3, BN folded like conv2..conv4
+    const float* const* x = t + VEX_CNN_NUM_TENSORS + VEX_CNN_TENSORS_PER_EXTRA * e;
+    const float *w = x[0], *b = x[1], *g = x[2], *be = x[3], *mu = x[4], *var = x[5];
+    TcLayer& L = P->extra[e];
+    L.cin = c3; L.cout = c3;
+    L.bn = (ctx->opt_conv3_bn == 256 && c3 % 256 == 0) ? 256 : 128;
+    L.w_folded.resize((size_t)c3 * c3 * 9);
+    std::vector<float> sh(c3);
+    for (int co = 0; co < c3; ++co) {
+      const float sc = g[co] / sqrtf(var[co] + arch->bn_eps);
+      sh[co] = (b[co] - mu[co]) * sc + be[co];
+      for (size_t j = 0; j < (size_t)c3 * 9; ++j)
+        L.w_folded[(size_t)co * c3 * 9 + j] = w[(size_t)co * c3 * 9 + j] * sc;
+    }
+    if ((rc = pack_tc(ctx, L))) return rc;
+    if ((rc = upload(ctx, &L.bias, sh.data(), (size_t)c3 * 4))) return rc;
   }
   {  // conv5: [c4/64][9][64][4]
     std::vector<float> w((size_t)c4 * 9 * 4, 0.f);
@@ -520,6 +565,22 @@ int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const*
       return u1w[(((size_t)ci * up + co) * 4 + ky) * 4 + kx];
     });
     if (rc) return rc;
+    // same image with the bias folded in as two bf16 terms (hi + lo) at k = 27, 28; the fused tail's builder puts 1.0 there
+    rc = pack_rows_sw128(ctx, &P->tu1wb, 4 * up, 1, [&](int r, int k) -> float {
+      const int ph = r / up, co = r % up;
+      if (k == 27 || k == 28) {
+        const uint32_t hb = (uint32_t)f32_to_bf16_rne(u1b[co]) << 16;
+        float hi;
+        memcpy(&hi, &hb, 4);
+        return k == 27 ? hi : u1b[co] - hi;
+      }
+      if (k > 28) return 0.f;
+      const int ci = k % 3, tap = k / 3;
+      const int ky = kmap[ph >> 1][tap / 3], kx = kmap[ph & 1][tap % 3];
+      if (ky < 0 || kx < 0) return 0.f;
+      return u1w[(((size_t)ci * up + co) * 4 + ky) * 4 + kx];
+    });
+    if (rc) return rc;
     std::vector<float> b4((size_t)4 * up);
     for (int i = 0; i < 4 * up; ++i) b4[i] = u1b[i % up];
     if ((rc = upload(ctx, &P->tu1b, b4.data(), b4.size() * 4))) return rc;
@@ -563,7 +624,7 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
   __nv_bfloat16* x2 = reinterpret_cast<__nv_bfloat16*>(P->ws + L.b);
   __nv_bfloat16* x3 = reinterpret_cast<__nv_bfloat16*>(P->ws + L.c);
   __nv_bfloat16* x4 = x1;
-  __nv_bfloat16* up = x3;
+  __nv_bfloat16* up = x3;                     // bufC; free again once conv4 has run
   float* x5 = reinterpret_cast<float*>(P->ws + L.x5);
   const int HW = H * W;
   auto tap_bf16 = [&](const __nv_bfloat16* x, int C) -> int {
@@ -601,8 +662,14 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
   mark();
   if (out_f32 && tap == 2) return tap_bf16(x2, d.c2);
   if ((rc = run_tc(ctx, P->tc[1], x2, x3, nullptr, n, H, W, s))) return rc;
-  mark();
   if (out_f32 && tap == 3) return tap_bf16(x3, d.c3);
+  for (int e = 0; e < d.n_extra; ++e) {                                        // ping-pong bufC <-> bufD
+    __nv_bfloat16* nxt = reinterpret_cast<__nv_bfloat16*>(P->ws + ((e & 1) ? L.c : L.d));
+    if ((rc = run_tc(ctx, P->extra[e], x3, nxt, nullptr, n, H, W, s))) return rc;
+    x3 = nxt;
+    if (out_f32 && tap == 7 + e) return tap_bf16(x3, d.c3);
+  }
+  mark();                                                                      // conv3's slot includes the extra blocks
   if ((rc = run_tc(ctx, P->tc[2], x3, x4, nullptr, n, H, W, s))) return rc;
   mark();
   if (out_f32 && tap == 4) return tap_bf16(x4, d.c4);
@@ -628,6 +695,13 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
     small::nhw4_f32_to_nchw_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, s>>>(x5, out_f32, npix, HW);
     ctx->launches++;
     VEX_CUDA(ctx, cudaGetLastError());
+    return VEX_OK;
+  }
+  if (thin_tc && ctx->opt_fuse_tail && d.up_ch == 64 && !(out_f32 && tap == 6)) {
+    // upconv1 + relu + upconv2 + clamp + uint8 in one kernel: `up` never reaches HBM
+    if ((rc = launch_uptail(ctx, x5, P->tu1wb, P->tu2w, P->bu2, out_u8, out_f32, n, H, W, out_bgr, s))) return rc;
+    mark();                                  // the fused time is reported in upconv1's slot, upconv2's reads 0
+    mark();
     return VEX_OK;
   }
   if (thin_tc) {
@@ -675,7 +749,9 @@ int cnn_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f32
   const size_t budget = (size_t)ctx->opt_ws_budget_mb << 20;
   int sub = (int)std::max<size_t>(1, std::min<size_t>((size_t)n, budget / std::max<size_t>(per_frame, 1)));
   const vex_cnn_desc& d = ctx->cnn->arch;
-  const size_t out_ch[7] = {3, (size_t)d.c1, (size_t)d.c2, (size_t)d.c3, (size_t)d.c4, 3, (size_t)d.up_ch};
+  if (tap > 6 + d.n_extra) return fail(ctx, VEX_ERR_INVALID, "vex_cnn2x_f32_debug: tap beyond the last extra block");
+  const size_t out_ch[7 + VEX_CNN_MAX_EXTRA] = {3, (size_t)d.c1, (size_t)d.c2, (size_t)d.c3, (size_t)d.c4, 3, (size_t)d.up_ch,
+                                                (size_t)d.c3, (size_t)d.c3, (size_t)d.c3, (size_t)d.c3};
   const size_t out_px = (tap == 0 || tap == 6) ? (size_t)4 * h * w : (size_t)h * w;
   for (int f0 = 0; f0 < n; f0 += sub) {
     const int nf = std::min(sub, n - f0);
@@ -705,24 +781,33 @@ int cnn_profile_ms(vex_ctx* ctx, float* ms7) {
 int cnn_repack(vex_ctx* ctx) {
   CnnPlan* P = ctx->cnn;
   if (!P || !P->w1g) return VEX_OK;
-  TcLayer& L = P->tc[1];
-  const int bn = (ctx->opt_conv3_bn == 256 && L.cout % 256 == 0) ? 256 : 128;
-  if (bn == L.bn) return VEX_OK;
-  VEX_CUDA(ctx, cudaDeviceSynchronize());
-  L.bn = bn;
-  return pack_tc(ctx, L);
+  TcLayer* layers[1 + VEX_CNN_MAX_EXTRA] = {&P->tc[1], &P->extra[0], &P->extra[1], &P->extra[2], &P->extra[3]};
+  for (int i = 0; i < 1 + P->arch.n_extra; ++i) {
+    TcLayer& L = *layers[i];
+    const int bn = (ctx->opt_conv3_bn == 256 && L.cout % 256 == 0) ? 256 : 128;
+    if (bn == L.bn) continue;
+    VEX_CUDA(ctx, cudaDeviceSynchronize());
+    L.bn = bn;
+    int rc = pack_tc(ctx, L);
+    if (rc) return rc;
+  }
+  return VEX_OK;
 }
 
 void cnn_destroy(vex_ctx* ctx) {
   CnnPlan* P = ctx->cnn;
   if (!P) return;
   float* fs[] = {P->w1g, P->b1, P->w5g, P->b5, P->wu1, P->bu1, P->wu2, P->bu2, P->tu1b};
-  uint8_t* us[] = {P->t1w, P->tu1w, P->t5w, P->tu2w};
+  uint8_t* us[] = {P->t1w, P->tu1w, P->tu1wb, P->t5w, P->tu2w};
   for (uint8_t* u : us)
     if (u) cudaFree(u);
   for (float* f : fs)
     if (f) cudaFree(f);
   for (TcLayer& L : P->tc) {
+    if (L.wpack) cudaFree(L.wpack);
+    if (L.bias) cudaFree(L.bias);
+  }
+  for (TcLayer& L : P->extra) {
     if (L.wpack) cudaFree(L.wpack);
     if (L.bias) cudaFree(L.bias);
   }

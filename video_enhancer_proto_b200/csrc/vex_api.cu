@@ -127,7 +127,7 @@ int vex_cnn2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, i
 int vex_cnn2x_f32_debug(vex_ctx* ctx, const uint8_t* in_hwc, float* out_nchw, int n, int h, int w,
                         int in_bgr, int tap, void* stream) {
   if (!ctx) return VEX_ERR_INVALID;
-  if (!in_hwc || !out_nchw || n <= 0 || h <= 0 || w <= 0 || tap < 0 || tap > 6)
+  if (!in_hwc || !out_nchw || n <= 0 || h <= 0 || w <= 0 || tap < 0 || tap > 6 + VEX_CNN_MAX_EXTRA)
     return vex::fail(ctx, VEX_ERR_INVALID, "vex_cnn2x_f32_debug: bad argument");
   VEX_CUDA(ctx, cudaSetDevice(ctx->device));
   return vex::cnn_forward(ctx, in_hwc, nullptr, out_nchw, tap, n, h, w, in_bgr != 0, 0,
@@ -221,6 +221,7 @@ int vex_set_option(vex_ctx* ctx, const char* name, int value) {
   else if (!strcmp(name, "ws_budget_mb")) slot = &ctx->opt_ws_budget_mb;
   else if (!strcmp(name, "profile")) slot = &ctx->opt_profile;
   else if (!strcmp(name, "thin_tc")) slot = &ctx->opt_thin_tc;
+  else if (!strcmp(name, "fuse_tail")) slot = &ctx->opt_fuse_tail;
   else if (!strcmp(name, "conv_dbg")) slot = &ctx->opt_conv_dbg;
   else if (!strcmp(name, "epi_variant")) slot = &ctx->opt_epi_variant;
   if (!slot) return vex::fail(ctx, VEX_ERR_INVALID, std::string("vex_set_option: unknown ") + name);

@@ -51,7 +51,7 @@ class B200VideoEnhancer:
         self._lib = None
         self._state = None
         self._pending_state = (state_dict, seed)
-        self._widths, self._up_ch = W.REFERENCE_WIDTHS, W.REFERENCE_UP_CH
+        self._widths, self._up_ch, self._n_extra = W.REFERENCE_WIDTHS, W.REFERENCE_UP_CH, 0
         self._pinned = {}                                  # (tag, nbytes) -> pinned tensors
         self._dev = {}
 
@@ -86,13 +86,13 @@ class B200VideoEnhancer:
     def load_state_dict(self, state_dict: Mapping[str, object]) -> None:
         """Upload a checkpoint with the reference module's key names."""
         self._ensure_ctx()
-        widths, up_ch = W.infer_plan(state_dict)
-        st = W.normalize_state(state_dict, widths, up_ch)
-        desc = _lib.VexCnnDesc(widths[0], widths[1], widths[2], widths[3], up_ch, 1e-5)
+        widths, up_ch, n_extra = W.infer_plan(state_dict)
+        st = W.normalize_state(state_dict, widths, up_ch, n_extra)
+        desc = _lib.VexCnnDesc(widths[0], widths[1], widths[2], widths[3], up_ch, 1e-5, n_extra)
         ptrs = (C.c_void_p * len(st))(*[a.ctypes.data for a in st.values()])
         rc = self._lib.vex_cnn_load_weights(self._ctx, C.byref(desc), ptrs, len(st))
         _lib.check(self._ctx, rc, "vex_cnn_load_weights")
-        self._state, self._widths, self._up_ch = st, widths, up_ch
+        self._state, self._widths, self._up_ch, self._n_extra = st, widths, up_ch, n_extra
 
     def state_dict(self):
         self._ensure_weights()
@@ -194,7 +194,9 @@ class B200VideoEnhancer:
         n, h, w, _ = frames_u8.shape
         c1, c2, c3, c4 = self._widths
         shape = {0: (n, 3, 2 * h, 2 * w), 1: (n, c1, h, w), 2: (n, c2, h, w), 3: (n, c3, h, w),
-                 4: (n, c4, h, w), 5: (n, 3, h, w), 6: (n, self._up_ch, 2 * h, 2 * w)}[tap]
+                 4: (n, c4, h, w), 5: (n, 3, h, w), 6: (n, self._up_ch, 2 * h, 2 * w)}.get(tap, (n, c3, h, w))
+        if tap > 6 + self._n_extra:
+            raise ValueError(f"tap {tap}: the plan has {self._n_extra} extra block(s)")
         out = torch.empty(shape, dtype=torch.float32, device=frames_u8.device)
         rc = self._lib.vex_cnn2x_f32_debug(self._ctx, frames_u8.data_ptr(), out.data_ptr(), n, h, w,
                                            int(in_bgr), tap, torch.cuda.current_stream(frames_u8.device).cuda_stream)
@@ -284,8 +286,10 @@ class B200VideoEnhancer:
             "scale": self.scale,
             "device": self.device,
             "model": self.model_name,
-            "architecture": f"conv3x3 3-{c1}-{c2}(+skip)-{c3}-{c4}-3, ConvT k4s2 3-{self._up_ch}, ConvT k3 {self._up_ch}-3",
-            "parameters": int(sum(int(np.prod(s)) for k, s in W.expected_shapes(self._widths, self._up_ch).items()
+            "architecture": f"conv3x3 3-{c1}-{c2}(+skip)-{c3}" + f"-{c3}" * self._n_extra +
+                            f"-{c4}-3, ConvT k4s2 3-{self._up_ch}, ConvT k3 {self._up_ch}-3",
+            "parameters": int(sum(int(np.prod(s)) for k, s in
+                                  W.expected_shapes(self._widths, self._up_ch, self._n_extra).items()
                                   if "running" not in k)),
             "capabilities": ["upscaling", "bicubic_fallback"],
             "precision": "bf16 operands, fp32 accumulate",

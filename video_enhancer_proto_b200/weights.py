@@ -29,9 +29,20 @@ STATE_DICT_KEYS = (
 
 REFERENCE_WIDTHS = (128, 128, 256, 128)
 REFERENCE_UP_CH = 64
+EXTRA_PARAMS = ("weight", "bias")
+BN_PARAMS = ("weight", "bias", "running_mean", "running_var")
 
 
-def expected_shapes(widths: Sequence[int] = REFERENCE_WIDTHS, up_ch: int = REFERENCE_UP_CH):
+def extra_keys(n_extra: int):
+    """Keys of the deepened plans (BASELINE.json configs[4]): block k = conv3x<k> + bn3x<k>, appended after the
+    reference's 30 tensors in this order (include/vex.h)."""
+    keys = []
+    for k in range(1, n_extra + 1):
+        keys += [f"conv3x{k}.{p}" for p in EXTRA_PARAMS] + [f"bn3x{k}.{p}" for p in BN_PARAMS]
+    return tuple(keys)
+
+
+def expected_shapes(widths: Sequence[int] = REFERENCE_WIDTHS, up_ch: int = REFERENCE_UP_CH, n_extra: int = 0):
     c1, c2, c3, c4 = widths
     s = collections.OrderedDict()
     for name, (co, ci) in (("conv1", (c1, 3)), ("conv2", (c2, c1)), ("conv3", (c3, c2)),
@@ -45,11 +56,16 @@ def expected_shapes(widths: Sequence[int] = REFERENCE_WIDTHS, up_ch: int = REFER
     for i, c in enumerate((c1, c2, c3, c4), start=1):
         for p in ("weight", "bias", "running_mean", "running_var"):
             s[f"bn{i}.{p}"] = (c,)
-    return collections.OrderedDict((k, s[k]) for k in STATE_DICT_KEYS)
+    for k in range(1, n_extra + 1):
+        s[f"conv3x{k}.weight"] = (c3, c3, 3, 3)
+        s[f"conv3x{k}.bias"] = (c3,)
+        for p in BN_PARAMS:
+            s[f"bn3x{k}.{p}"] = (c3,)
+    return collections.OrderedDict((k, s[k]) for k in STATE_DICT_KEYS + extra_keys(n_extra))
 
 
 def init_state(seed: Optional[int] = None, widths: Sequence[int] = REFERENCE_WIDTHS,
-               up_ch: int = REFERENCE_UP_CH) -> "collections.OrderedDict[str, np.ndarray]":
+               up_ch: int = REFERENCE_UP_CH, n_extra: int = 0) -> "collections.OrderedDict[str, np.ndarray]":
     """Fresh weights by the reference's procedure (app.py:273-287 construction order, then the
     init loop app.py:305-309).  ``seed=None`` draws from the global RNG like the reference."""
     if seed is not None:
@@ -65,6 +81,9 @@ def init_state(seed: Optional[int] = None, widths: Sequence[int] = REFERENCE_WID
     layers["upconv2"] = nn.ConvTranspose2d(up_ch, 3, 3, padding=1)
     for i, c in enumerate((c1, c2, c3, c4), start=1):
         layers[f"bn{i}"] = nn.BatchNorm2d(c)
+    for k in range(1, n_extra + 1):                 # deepened plans only; the reference has none
+        layers[f"conv3x{k}"] = nn.Conv2d(c3, c3, 3, padding=1)
+        layers[f"bn3x{k}"] = nn.BatchNorm2d(c3)
     for m in layers.values():                       # same traversal order as model.modules()
         if isinstance(m, (nn.Conv2d, nn.ConvTranspose2d)):
             nn.init.xavier_uniform_(m.weight)
@@ -73,13 +92,13 @@ def init_state(seed: Optional[int] = None, widths: Sequence[int] = REFERENCE_WID
     for name, m in layers.items():
         for k, v in m.state_dict().items():
             sd[f"{name}.{k}"] = v
-    return normalize_state(sd, widths, up_ch)
+    return normalize_state(sd, widths, up_ch, n_extra)
 
 
 def normalize_state(sd: Mapping[str, object], widths: Sequence[int] = REFERENCE_WIDTHS,
-                    up_ch: int = REFERENCE_UP_CH) -> "collections.OrderedDict[str, np.ndarray]":
+                    up_ch: int = REFERENCE_UP_CH, n_extra: int = 0) -> "collections.OrderedDict[str, np.ndarray]":
     """Validate names/shapes and return contiguous fp32 numpy arrays in ABI order."""
-    shapes = expected_shapes(widths, up_ch)
+    shapes = expected_shapes(widths, up_ch, n_extra)
     out = collections.OrderedDict()
     for k, shp in shapes.items():
         if k not in sd:
@@ -95,7 +114,10 @@ def normalize_state(sd: Mapping[str, object], widths: Sequence[int] = REFERENCE_
 
 
 def infer_plan(sd: Mapping[str, object]):
-    """(widths, up_ch) from a state_dict's tensor shapes."""
+    """(widths, up_ch, n_extra) from a state_dict's tensor shapes and keys."""
     g = lambda k: tuple(sd[k].shape)
     widths = (g("conv1.weight")[0], g("conv2.weight")[0], g("conv3.weight")[0], g("conv4.weight")[0])
-    return widths, g("upconv1.weight")[1]
+    n_extra = 0
+    while f"conv3x{n_extra + 1}.weight" in sd:
+        n_extra += 1
+    return widths, g("upconv1.weight")[1], n_extra

@@ -17,8 +17,9 @@
 namespace vex {
 namespace thin {
 
-constexpr int UT_THREADS = 640;        // warps 0-3 builders; 4-6 / 8-10 mid-drain groups (phases 0-1 / 2-3; TMEM lanes 0-95);
-                                       // 7 MMA; 11 idle; 12-15 / 16-19 epilogue groups (even / odd items)
+constexpr int UT_EPI_GROUPS = 3;       // the epilogue is the longest role: three groups of 4 warps take items k % 3
+constexpr int UT_THREADS = 384 + 128 * UT_EPI_GROUPS;   // warps 0-3 builders; 4-6 / 8-10 mid-drain groups (phases 0-1 / 2-3;
+                                       // TMEM lanes 0-95); 7 MMA; 11 idle; 12-15 / 16-19 / 20-23 epilogue groups
 constexpr int UT_MMA_WARP = 7;
 constexpr int UT_EPI_WARP0 = 12;
 constexpr int UT_LR = 5, UT_LC = 17;   // low-res pixels under the 8 x 32 hi-res halo tile
@@ -33,9 +34,9 @@ struct UTCfg {
   static constexpr int W2_OFF = A2_OFF + 2 * A2_STAGE;              // 32 rows x 128 B
   static constexpr int YS_OFF = W2_OFF + 4096;
   static constexpr int YS_BYTES = 27 * G27_YS_PITCH * 4;
-  static constexpr int OB_OFF = YS_OFF + 2 * YS_BYTES;
+  static constexpr int OB_OFF = YS_OFF + UT_EPI_GROUPS * YS_BYTES;
   static constexpr int OB_BYTES = G27_ROWS * G27_OB_PITCH + 16;
-  static constexpr int BAR_OFF = (OB_OFF + 2 * OB_BYTES + 15) / 16 * 16;
+  static constexpr int BAR_OFF = (OB_OFF + UT_EPI_GROUPS * OB_BYTES + 15) / 16 * 16;
   static constexpr int BIAS_OFF = BAR_OFF + 256;
   static constexpr int SMEM = BIAS_OFF + 1024;
 };
@@ -63,11 +64,11 @@ uptail_kernel(const UTParams p) {
   uint8_t* sm = smem_raw + (sbase - raw);
   const uint32_t bar0 = sbase + C::BAR_OFF;
   const uint32_t a1_full = bar0, a1_empty = bar0 + 16;
-  const uint32_t acc1_full = bar0 + 32, acc1_empty = bar0 + 56;      // ring of three 128-column half accumulators
-  const uint32_t a2_full = bar0 + 80, a2_empty = bar0 + 96;
-  const uint32_t acc2_full = bar0 + 112, acc2_empty = bar0 + 128;
-  const uint32_t w_bar = bar0 + 144, tmem_slot = bar0 + 152;
-  volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(sm + C::BAR_OFF + 152);
+  const uint32_t acc1_full = bar0 + 32, acc1_empty = bar0 + 48;      // per half of the first accumulator (phases 0-1 / 2-3)
+  const uint32_t a2_full = bar0 + 64, a2_empty = bar0 + 80;
+  const uint32_t acc2_full = bar0 + 96, acc2_empty = bar0 + 128;     // per epilogue group (up to 4)
+  const uint32_t w_bar = bar0 + 160, tmem_slot = bar0 + 168;
+  volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(sm + C::BAR_OFF + 168);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total = p.tiles_x * p.tiles_y * p.n_img;
   const int H2 = 2 * p.H, W2 = 2 * p.W;
@@ -76,14 +77,14 @@ uptail_kernel(const UTParams p) {
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(a1_full + 8 * i, 128); ptx::mbar_init(a1_empty + 8 * i, 1);
       ptx::mbar_init(a2_full + 8 * i, 192); ptx::mbar_init(a2_empty + 8 * i, 1);
-      ptx::mbar_init(acc2_full + 8 * i, 1); ptx::mbar_init(acc2_empty + 8 * i, 4);
+      ptx::mbar_init(acc1_full + 8 * i, 1); ptx::mbar_init(acc1_empty + 8 * i, 3);
     }
-    for (int i = 0; i < 3; ++i) { ptx::mbar_init(acc1_full + 8 * i, 1); ptx::mbar_init(acc1_empty + 8 * i, 3); }
+    for (int i = 0; i < UT_EPI_GROUPS; ++i) { ptx::mbar_init(acc2_full + 8 * i, 1); ptx::mbar_init(acc2_empty + 8 * i, 4); }
     ptx::mbar_init(w_bar, 1);
     ptx::fence_mbar_init();
   }
   if (warp == UT_MMA_WARP) {
-    ptx::tmem_alloc(tmem_slot, 512);                 // 3 x 128 columns: first GEMM (half-job ring); 384 + b*64 + g*32: second GEMM
+    ptx::tmem_alloc(tmem_slot, 512);                 // [0,256): first GEMM, two halves; 256 + grp*64 + g*32: second GEMM
     ptx::tmem_relinquish();
   }
   ptx::tc_fence_before();
@@ -141,7 +142,8 @@ uptail_kernel(const UTParams p) {
       constexpr uint32_t idesc2 = ptx::idesc_bf16_f32(128, 32);
       auto gemm2 = [&](uint32_t j) {
         const uint32_t s = j & 1, ph = (j >> 1) & 1;
-        ptx::mbar_wait(acc2_empty + 8 * s, ph ^ 1);
+        const uint32_t eg = j % UT_EPI_GROUPS, eu = j / UT_EPI_GROUPS;    // epilogue group and its use count
+        ptx::mbar_wait(acc2_empty + 8 * eg, (eu & 1) ^ 1);
         ptx::mbar_wait(a2_full + 8 * s, ph);
         ptx::tc_fence_after();
 #pragma unroll
@@ -150,27 +152,26 @@ uptail_kernel(const UTParams p) {
           for (int kk = 0; kk < 4; ++kk) {
             const uint64_t ad = ptx::smem_desc_sw128(sbase + C::A2_OFF + s * C::A2_STAGE + g * 16384 + kk * 32, 0);
             const uint64_t bd = ptx::smem_desc_sw128(sbase + C::W2_OFF + kk * 32, 0);
-            ptx::mma_bf16_ss(tmem + 384 + s * 64 + g * 32, ad, bd, idesc2, kk != 0);
+            ptx::mma_bf16_ss(tmem + 256 + eg * 64 + g * 32, ad, bd, idesc2, kk != 0);
           }
         ptx::tc_commit(a2_empty + 8 * s);
-        ptx::tc_commit(acc2_full + 8 * s);
+        ptx::tc_commit(acc2_full + 8 * eg);
       };
-      uint32_t k = 0, buf = 0, use = 0;              // half-job j = 2k + h uses ring buffer j % 3 for the (j / 3)-th time
+      uint32_t k = 0;
       for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
         const uint32_t sa = k & 1, pa = (k >> 1) & 1;
         ptx::mbar_wait(a1_full + 8 * sa, pa);
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {                // phases 0-1, then 2-3; the ring lets the MMA run two half-jobs ahead
-          ptx::mbar_wait(acc1_empty + 8 * buf, (use & 1) ^ 1);
+        for (int h = 0; h < 2; ++h) {                // phases 0-1, then 2-3: the mid-drain of one half overlaps the other
+          ptx::mbar_wait(acc1_empty + 8 * h, (k & 1) ^ 1);
           ptx::tc_fence_after();
 #pragma unroll
           for (int kk = 0; kk < 2; ++kk) {
             const uint64_t ad = ptx::smem_desc_sw128(sbase + C::A1_OFF + sa * C::A1_STAGE + kk * 32, 0);
             const uint64_t bd = ptx::smem_desc_sw128(sbase + C::W1_OFF + h * 16384 + kk * 32, 0);
-            ptx::mma_bf16_ss(tmem + buf * 128, ad, bd, idesc1, kk);
+            ptx::mma_bf16_ss(tmem + h * 128, ad, bd, idesc1, kk);
           }
-          ptx::tc_commit(acc1_full + 8 * buf);
-          if (++buf == 3) { buf = 0; ++use; }
+          ptx::tc_commit(acc1_full + 8 * h);
         }
         ptx::tc_commit(a1_empty + 8 * sa);
         if (k > 0) gemm2(k - 1);
@@ -189,9 +190,8 @@ uptail_kernel(const UTParams p) {
       const int txi = it % p.tiles_x, t = it / p.tiles_x;
       const int tyi = t % p.tiles_y;
       const uint32_t s = k & 1;
-      const uint32_t j = 2 * k + h, buf = j % 3, use = j / 3;
       ptx::mbar_wait(a2_empty + 8 * s, ((k >> 1) & 1) ^ 1);
-      ptx::mbar_wait(acc1_full + 8 * buf, use & 1);
+      ptx::mbar_wait(acc1_full + 8 * h, k & 1);
       ptx::tc_fence_after();
       uint8_t* a2 = sm + C::A2_OFF + s * C::A2_STAGE;
 #pragma unroll
@@ -206,7 +206,7 @@ uptail_kernel(const UTParams p) {
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint32_t v[32];
-          ptx::tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + buf * 128 + pp * 64 + half * 32, v);
+          ptx::tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + h * 128 + pp * 64 + half * 32, v);
           ptx::tmem_ld_wait();
           if (in_tile && !(p.probe & 2)) {
 #pragma unroll
@@ -224,7 +224,7 @@ uptail_kernel(const UTParams p) {
       }
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(acc1_empty + 8 * buf); // this half accumulator is free
+      if (lane == 0) ptx::mbar_arrive(acc1_empty + 8 * h);   // this half of the first accumulator is free
       ptx::fence_proxy_async_smem();
       ptx::mbar_arrive(a2_full + 8 * s);
     }
@@ -238,7 +238,7 @@ uptail_kernel(const UTParams p) {
     const float b0 = p.bias2[0], b1 = p.bias2[1], b2 = p.bias2[2];
     const uint32_t b = grp;
     uint32_t pb = 0;
-    for (int it = blockIdx.x + grp * gridDim.x; it < total; it += 2 * gridDim.x) {
+    for (int it = blockIdx.x + grp * gridDim.x; it < total; it += UT_EPI_GROUPS * gridDim.x) {
       const int txi = it % p.tiles_x, t = it / p.tiles_x;
       const int tyi = t % p.tiles_y, n = t / p.tiles_y;
       const int x0 = txi * G27_TW, y0 = tyi * G27_ROWS;
@@ -247,7 +247,7 @@ uptail_kernel(const UTParams p) {
 #pragma unroll
       for (int g = 0; g < 2; ++g) {
         uint32_t v[32];
-        ptx::tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + 384 + b * 64 + g * 32, v);
+        ptx::tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + 256 + b * 64 + g * 32, v);
         ptx::tmem_ld_wait();
         const int m = g * 128 + q * 32 + lane;
 #pragma unroll

@@ -201,7 +201,9 @@ uptail_kernel(const UTParams p) {
         const bool in_tile = r < UT_ROWS1 && hr >= 0 && hr < 8 && hc >= 0 && hc < 32;
         const int hy = 6 * tyi - 1 + hr, hx = 30 * txi - 1 + hc;
         const bool in_img = hy >= 0 && hy < H2 && hx >= 0 && hx < W2;
-        const int m = hr * 32 + hc;
+        // A2 row order: within a hi-res row the even columns come first, then the odd ones.  One PixelShuffle phase has
+        // one column parity, so a warp's 16-byte stores then cover all 8 swizzle positions (4 wavefronts instead of 8).
+        const int m = hr * 32 + (hc >> 1) + 16 * (hc & 1);
         uint8_t* row = a2 + (m >> 7) * 16384 + (m & 127) * 128;
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
@@ -266,7 +268,8 @@ uptail_kernel(const UTParams p) {
         float s0 = b0, s1 = b1, s2 = b2;
 #pragma unroll
         for (int tp = 0; tp < 9; ++tp) {
-          const int m = (ty + tp / 3) * 32 + tx + tp % 3;
+          const int c = tx + tp % 3;                                  // halo-tile column; rows are stored even | odd
+          const int m = (ty + tp / 3) * 32 + (c >> 1) + 16 * (c & 1);
           s0 += Ys[(tp * 3 + 0) * G27_YS_PITCH + m];
           s1 += Ys[(tp * 3 + 1) * G27_YS_PITCH + m];
           s2 += Ys[(tp * 3 + 2) * G27_YS_PITCH + m];

@@ -58,6 +58,27 @@ int vex_abi_version(void);
 int vex_bicubic2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc,
                      int n, int h, int w, int round_mode, void* stream);
 
+/* ---- the other per-frame stages of BasicUpscalerFallback --------------------
+ * models/enhancement/frame/basic_upscaler_fallback.py:113-128 runs, per frame,
+ *   LANCZOS mode:  cv2.bilateralFilter(frame, 5, 50, 50) -> cv2.resize(INTER_LANCZOS4) -> cv2.filter2D(sharpen) -> clip
+ *   CUBIC mode:    cv2.resize(INTER_CUBIC) (= vex_bicubic2x_u8 round_mode 1)           -> cv2.filter2D(sharpen) -> clip
+ * All three take and return packed u8 HWC device buffers, n frames, any channel order (they are channel-symmetric). */
+
+/* cv2.resize(frame, (2w, 2h), interpolation=cv2.INTER_LANCZOS4) (basic_upscaler_fallback.py:52,120) for 8-bit images:
+ * OpenCV's 11-bit fixed-point 8-tap separable path, replicate border.  Bit-exact.  out: n*[2h][2w][3]. */
+int vex_lanczos4_2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w, void* stream);
+
+/* cv2.bilateralFilter(frame, 5, sigma_color, sigma_space) (basic_upscaler_fallback.py:117; the reference passes 50, 50):
+ * diameter 5 -> the 13 taps within radius 2, BORDER_REFLECT_101.  in != out.  out: n*[h][w][3]. */
+int vex_bilateral5_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w, float sigma_color,
+                      float sigma_space, void* stream);
+
+/* cv2.filter2D(img, -1, kernel) for a 3x3 fp32 kernel given row-major (basic_upscaler_fallback.py:123-127: the reference's
+ * kernel is 0.1 * [[-1,-1,-1],[-1,9,-1],[-1,-1,-1]]), BORDER_REFLECT_101, rounded and saturated to u8 (which is also what
+ * the reference's np.clip(...).astype(np.uint8) leaves).  in != out.  out: n*[h][w][3]. */
+int vex_filter3x3_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w, const float* kernel9,
+                     void* stream);
+
 /* ---- CNN upscaler ------------------------------------------------------------------------ */
 
 /* Channel plan of the AdvancedUpscaler family (app.py:269-301):

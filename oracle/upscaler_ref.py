@@ -240,3 +240,65 @@ def psnr(a: np.ndarray, b: np.ndarray, peak: float = 1.0) -> float:
     if mse == 0:
         return float("inf")
     return 10.0 * np.log10(peak * peak / mse)
+
+
+# ----------------------------------------------------------------------------- BasicUpscalerFallback stages
+
+def ref_basic_upscaler_frame(frame: np.ndarray, model_name: str = "LANCZOS", scale: int = 2, stages: bool = False):
+    """The per-frame body of BasicUpscalerFallback.enhance_video (basic_upscaler_fallback.py:113-128), verbatim calls:
+    bilateral pre-filter for LANCZOS (:115-117), cv2.resize with the mode's interpolation (:120), the 0.1-scaled
+    sharpening filter2D and clip (:123-128).  ``stages=True`` also returns the intermediate images."""
+    import cv2
+    interpolation = {"LANCZOS": cv2.INTER_LANCZOS4, "CUBIC": cv2.INTER_CUBIC}[model_name.upper()]
+    out_h, out_w = frame.shape[0] * scale, frame.shape[1] * scale
+    den = frame
+    if model_name.upper() == "LANCZOS":
+        den = cv2.bilateralFilter(frame, 5, 50, 50)
+    upscaled0 = cv2.resize(den, (out_w, out_h), interpolation=interpolation)
+    kernel = np.array([[-1, -1, -1], [-1, 9, -1], [-1, -1, -1]], dtype=np.float32)
+    kernel = kernel * 0.1
+    upscaled = cv2.filter2D(upscaled0, -1, kernel)
+    upscaled = np.clip(upscaled, 0, 255).astype(np.uint8)
+    return (upscaled, den, upscaled0) if stages else upscaled
+
+
+LANCZOS4_TAPS_Q11 = {0.25: (-31, 114, -312, 1830, 579, -188, 64, -8), 0.75: (-8, 64, -188, 579, 1830, -312, 114, -31)}
+
+
+def lanczos4_taps_q11(t: float):
+    """OpenCV imgproc ``interpolateLanczos4`` (fp32 coefficients from the sin/cos recurrence table, normalised) followed by
+    resize's fixed-point conversion ``saturate_cast<short>(c * 2048)``; the exact 2x ratio only needs t = 0.25, 0.75."""
+    x = np.float32(t)
+    s45 = 0.70710678118654752440084436210485
+    cs = [[1, 0], [-s45, -s45], [0, 1], [s45, -s45], [-1, 0], [s45, s45], [0, -1], [-s45, s45]]
+    y0 = -(x + 3) * np.pi * 0.25
+    s0, c0 = np.sin(y0), np.cos(y0)
+    co = np.zeros(8, np.float32)
+    total = np.float32(0)
+    for i in range(8):
+        y = -(x + 3 - i) * np.pi * 0.25
+        co[i] = np.float32((cs[i][0] * s0 + cs[i][1] * c0) / (y * y))
+        total = np.float32(total + co[i])
+    co = (co * (np.float32(1.0) / total)).astype(np.float32)
+    return tuple(int(np.clip(np.rint(np.float32(v) * np.float32(2048)), -32768, 32767)) for v in co)
+
+
+def np_lanczos4_2x_u8(frame: np.ndarray) -> np.ndarray:
+    """Exact restatement of cv2.resize(frame, (2w, 2h), INTER_LANCZOS4) for uint8: horizontal then vertical pass in
+    integers with the Q11 taps, replicate border, (v + 2^21) >> 22, saturate.  Small cases only (pure numpy loops)."""
+    h, w, _ = frame.shape
+    src = frame.astype(np.int64)
+
+    def pass1d(a, n):                       # a: [n, ...] -> [2n, ...] along axis 0
+        out = np.zeros((2 * n,) + a.shape[1:], np.int64)
+        for d in range(2 * n):
+            s = (d + 0.5) * 0.5 - 0.5
+            i = int(np.floor(s))
+            taps = LANCZOS4_TAPS_Q11[round(s - i, 2)]
+            for k in range(8):
+                out[d] += taps[k] * a[min(max(i + k - 3, 0), n - 1)]
+        return out
+
+    hpass = pass1d(src.transpose(1, 0, 2), w).transpose(1, 0, 2)       # [h, 2w, 3]
+    v = pass1d(hpass, h)
+    return np.clip((v + (1 << 21)) >> 22, 0, 255).astype(np.uint8)

@@ -82,3 +82,15 @@ def test_bicubic_weights_are_the_keys_kernel():
         return 0.0
     for t, wts in ((0.25, O.W_T025), (0.75, O.W_T075)):
         assert np.allclose([k(t + 1), k(t), k(1 - t), k(2 - t)], wts, atol=0, rtol=0)
+
+
+def test_lanczos4_restatement_matches_opencv():
+    """the Q11 tap table and the integer restatement of INTER_LANCZOS4 2x against cv2 itself."""
+    cv2 = pytest.importorskip("cv2")
+    for t, taps in O.LANCZOS4_TAPS_Q11.items():
+        assert O.lanczos4_taps_q11(t) == taps and sum(taps) == 2048
+    rng = np.random.default_rng(0)
+    for shape in ((1, 1, 3), (5, 7, 3), (20, 33, 3)):
+        img = rng.integers(0, 256, shape, dtype=np.uint8)
+        want = cv2.resize(img, (shape[1] * 2, shape[0] * 2), interpolation=cv2.INTER_LANCZOS4)
+        assert np.array_equal(O.np_lanczos4_2x_u8(img), want), shape

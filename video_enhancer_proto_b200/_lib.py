@@ -26,6 +26,9 @@ SIGNATURES = {
     "vex_destroy": (C.c_int, [C.c_void_p]),
     "vex_last_error": (C.c_char_p, [C.c_void_p]),
     "vex_bicubic2x_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "vex_lanczos4_2x_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "vex_bilateral5_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p]),
+    "vex_filter3x3_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float), C.c_void_p]),
     "vex_cnn_load_weights": (C.c_int, [C.c_void_p, C.POINTER(VexCnnDesc), C.POINTER(C.c_void_p), C.c_int]),
     "vex_cnn2x_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "vex_cnn2x_f32_debug": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),

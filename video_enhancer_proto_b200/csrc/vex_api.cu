@@ -82,6 +82,7 @@ int vex_destroy(vex_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
   vex::cnn_destroy(ctx);
+  if (ctx->bilateral_cw) cudaFree(ctx->bilateral_cw);
   for (int i = 0; i < 2; ++i) {
     if (ctx->slot_in[i]) cudaFree(ctx->slot_in[i]);
     if (ctx->slot_out[i]) cudaFree(ctx->slot_out[i]);
@@ -105,6 +106,26 @@ int vex_bicubic2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int 
   if (!ctx) return VEX_ERR_INVALID;
   VEX_CUDA(ctx, cudaSetDevice(ctx->device));
   return vex::launch_bicubic2x(ctx, in_hwc, out_hwc, n, h, w, round_mode, (cudaStream_t)stream);
+}
+
+int vex_lanczos4_2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w, void* stream) {
+  if (!ctx) return VEX_ERR_INVALID;
+  VEX_CUDA(ctx, cudaSetDevice(ctx->device));
+  return vex::launch_lanczos4_2x(ctx, in_hwc, out_hwc, n, h, w, (cudaStream_t)stream);
+}
+
+int vex_bilateral5_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w, float sigma_color,
+                      float sigma_space, void* stream) {
+  if (!ctx) return VEX_ERR_INVALID;
+  VEX_CUDA(ctx, cudaSetDevice(ctx->device));
+  return vex::launch_bilateral5(ctx, in_hwc, out_hwc, n, h, w, sigma_color, sigma_space, (cudaStream_t)stream);
+}
+
+int vex_filter3x3_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w, const float* kernel9,
+                     void* stream) {
+  if (!ctx) return VEX_ERR_INVALID;
+  VEX_CUDA(ctx, cudaSetDevice(ctx->device));
+  return vex::launch_filter3x3(ctx, in_hwc, out_hwc, n, h, w, kernel9, (cudaStream_t)stream);
 }
 
 int vex_cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const* tensors,

@@ -12,12 +12,19 @@
 
 namespace vex {
 
-struct CnnPlan;  // cnn.cu
+struct CnnPlan;  // filters.cu
+int launch_filter3x3(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, const float* k9, cudaStream_t s);
+int launch_bilateral5(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, float sigma_color,
+                      float sigma_space, cudaStream_t s);
+int launch_lanczos4_2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, cudaStream_t s);
+
+// cnn.cu
 
 }  // namespace vex
 
 struct vex_ctx {
   int device = 0;
+  float* bilateral_cw = nullptr;   // colour-weight table of vex_bilateral5_u8 (768 floats, device)
   int sm_count = 148;
   std::string err;
   unsigned long long launches = 0;

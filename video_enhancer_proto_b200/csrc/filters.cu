@@ -52,33 +52,102 @@ __global__ void filter3x3_kernel(const uint8_t* __restrict__ in, uint8_t* __rest
   o[0] = sat_u8_rn(s0); o[1] = sat_u8_rn(s1); o[2] = sat_u8_rn(s2);
 }
 
+// Fast path (row bytes % 16 == 0, 16-byte aligned buffers, W >= 2): the image is a matrix of bytes with neighbours at
+// +-3 bytes; a thread owns one 16-byte column of that matrix and walks down FILT_ROWS rows with a 3-row window of 22
+// floats (16 + 3 either side) in registers: per row one 16-byte load, two 4-byte halo loads, 16 x 9 FMAs in exactly the
+// row-major tap order of the generic kernel, one 16-byte store.
+constexpr int FILT_ROWS = 16;
+
+__device__ __forceinline__ void filt_load_row(const uint8_t* __restrict__ rowp, int col, int row_bytes, float (&f)[22]) {
+  const uint4 v = *reinterpret_cast<const uint4*>(rowp + col);
+  // halo: bytes col-3..col-1 and col+16..col+18; at the row ends REFLECT_101 in x: pixel -1 -> pixel 1, pixel W -> W-2
+  uint32_t lo, hi;
+  if (col > 0) lo = *reinterpret_cast<const uint32_t*>(rowp + col - 4) >> 8;            // bytes col-3, col-2, col-1
+  else lo = (v.x >> 24) | (v.y << 8);                                                    // bytes 3, 4, 5 (pixel 1)
+  if (col + 16 < row_bytes) hi = *reinterpret_cast<const uint32_t*>(rowp + col + 16);    // bytes col+16 .. col+18
+  else hi = (v.z >> 16) | (v.w << 16);                                                   // bytes 10, 11, 12 (pixel W-2)
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int i = 0; i < 3; ++i) f[i] = (float)((lo >> (8 * i)) & 0xffu);
+#pragma unroll
+  for (int i = 0; i < 16; ++i) f[3 + i] = (float)((w[i >> 2] >> (8 * (i & 3))) & 0xffu);
+#pragma unroll
+  for (int i = 0; i < 3; ++i) f[19 + i] = (float)((hi >> (8 * i)) & 0xffu);
+}
+
+__global__ void __launch_bounds__(128)
+filter3x3_rows_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int H, int row_bytes,
+                      float k0, float k1, float k2, float k3, float k4, float k5, float k6, float k7, float k8) {
+  const int col = (blockIdx.x * blockDim.x + threadIdx.x) * 16;
+  if (col >= row_bytes) return;
+  const int y0 = blockIdx.y * FILT_ROWS, y1 = min(y0 + FILT_ROWS, H);
+  const size_t fo = (size_t)blockIdx.z * H * row_bytes;
+  const uint8_t* base = in + fo;
+  const float kk[9] = {k0, k1, k2, k3, k4, k5, k6, k7, k8};
+  float r[3][22];                                  // window rows y-1, y, y+1 live in r[t % 3], r[(t+1) % 3], r[(t+2) % 3]
+  filt_load_row(base + (size_t)reflect101(y0 - 1, H) * row_bytes, col, row_bytes, r[0]);
+  filt_load_row(base + (size_t)y0 * row_bytes, col, row_bytes, r[1]);
+#pragma unroll
+  for (int t = 0; t < FILT_ROWS; ++t) {            // fully unrolled: the window rotates by renaming, not by moves
+    const int y = y0 + t;
+    if (y >= y1) break;
+    float (&ra)[22] = r[t % 3];
+    float (&rb)[22] = r[(t + 1) % 3];
+    float (&rc)[22] = r[(t + 2) % 3];
+    filt_load_row(base + (size_t)reflect101(y + 1, H) * row_bytes, col, row_bytes, rc);
+    uint32_t o[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      float a = 0.f;
+      a = fmaf(kk[0], ra[i], a); a = fmaf(kk[1], ra[i + 3], a); a = fmaf(kk[2], ra[i + 6], a);
+      a = fmaf(kk[3], rb[i], a); a = fmaf(kk[4], rb[i + 3], a); a = fmaf(kk[5], rb[i + 6], a);
+      a = fmaf(kk[6], rc[i], a); a = fmaf(kk[7], rc[i + 3], a); a = fmaf(kk[8], rc[i + 6], a);
+      o[i >> 2] |= (uint32_t)sat_u8_rn(a) << (8 * (i & 3));
+    }
+    *reinterpret_cast<uint4*>(out + fo + (size_t)y * row_bytes + col) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ bilateral 5x5
 struct BilateralTab {
   float space[13];
-  signed char di[13], dj[13];
 };
+// the 13 taps of a diameter-5 kernel (i^2 + j^2 <= 4) in OpenCV's row-major order
+__device__ constexpr int BL_DI[13] = {-2, -1, -1, -1, 0, 0, 0, 0, 0, 1, 1, 1, 2};
+__device__ constexpr int BL_DJ[13] = {0, -1, 0, 1, -2, -1, 0, 1, 2, -1, 0, 1, 0};
 
-__global__ void bilateral5_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int H, int W,
-                                  const float* __restrict__ color_w, const BilateralTab tab) {
+constexpr int BL_TW = 32, BL_TH = 16;            // pixels per block; the tile is staged with a 2-pixel REFLECT_101 halo
+
+// Pixels are staged as one 32-bit word each (b | g << 8 | r << 16), so a tap is one shared-memory load and the colour
+// distance |db| + |dg| + |dr| is one packed sum-of-absolute-differences instruction.
+__global__ void __launch_bounds__(BL_TW * BL_TH)
+bilateral5_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int H, int W,
+                  const float* __restrict__ color_w, const BilateralTab tab) {
   __shared__ float cw[768];
-  for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < 768; i += blockDim.x * blockDim.y) cw[i] = color_w[i];
-  __syncthreads();
-  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
-  if (x >= W || y >= H) return;
+  __shared__ uint32_t tile[BL_TH + 4][BL_TW + 4 + 1];
+  const int tid = threadIdx.y * BL_TW + threadIdx.x;
+  const int x0 = blockIdx.x * BL_TW, y0 = blockIdx.y * BL_TH;
   const size_t fo = (size_t)blockIdx.z * H * W * 3;
-  const uint8_t* c = in + fo + ((size_t)y * W + x) * 3;
-  const int b0 = c[0], g0 = c[1], r0 = c[2];
+  for (int i = tid; i < 768; i += BL_TW * BL_TH) cw[i] = color_w[i];
+  for (int i = tid; i < (BL_TH + 4) * (BL_TW + 4); i += BL_TW * BL_TH) {
+    const int r = i / (BL_TW + 4), c = i - r * (BL_TW + 4);
+    const int yy = reflect101(min(y0 + r - 2, H + 1), H), xx = reflect101(min(x0 + c - 2, W + 1), W);
+    const uint8_t* p = in + fo + ((size_t)yy * W + xx) * 3;
+    tile[r][c] = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16);
+  }
+  __syncthreads();
+  const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
+  if (x >= W || y >= H) return;
+  const uint32_t c0 = tile[threadIdx.y + 2][threadIdx.x + 2];
   float sb = 0.f, sg = 0.f, sr = 0.f, ws = 0.f;
 #pragma unroll
   for (int k = 0; k < 13; ++k) {
-    const int yy = reflect101(y + tab.di[k], H), xx = reflect101(x + tab.dj[k], W);
-    const uint8_t* p = in + fo + ((size_t)yy * W + xx) * 3;
-    const int b = p[0], g = p[1], r = p[2];
-    const float w = tab.space[k] * cw[abs(b - b0) + abs(g - g0) + abs(r - r0)];
+    const uint32_t p = tile[threadIdx.y + 2 + BL_DI[k]][threadIdx.x + 2 + BL_DJ[k]];
+    const float w = tab.space[k] * cw[__vsadu4(p, c0)];
     ws += w;
-    sb = fmaf((float)b, w, sb);
-    sg = fmaf((float)g, w, sg);
-    sr = fmaf((float)r, w, sr);
+    sb = fmaf((float)(p & 0xffu), w, sb);
+    sg = fmaf((float)((p >> 8) & 0xffu), w, sg);
+    sr = fmaf((float)(p >> 16), w, sr);
   }
   const float inv = 1.f / ws;
   uint8_t* o = out + fo + ((size_t)y * W + x) * 3;
@@ -97,7 +166,7 @@ __constant__ int c_lz[2][8] = {{-8, 64, -188, 579, 1830, -312, 114, -31},     //
 __global__ void __launch_bounds__(256)
 lanczos4_2x_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int H, int W) {
   __shared__ uint8_t s_in[LZ_IN_H][LZ_IN_W * 3];
-  __shared__ int s_h[LZ_IN_H][2 * LZ_TW * 3];
+  __shared__ __align__(16) int s_h[LZ_IN_H][2 * LZ_TW * 3];
   const int x0 = blockIdx.x * LZ_TW, y0 = blockIdx.y * LZ_TH;
   const size_t fi = (size_t)blockIdx.z * H * W * 3, fo = (size_t)blockIdx.z * H * W * 12;
   const int tid = threadIdx.x;
@@ -108,43 +177,58 @@ lanczos4_2x_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, in
     s_in[r][c * 3 + 0] = p[0]; s_in[r][c * 3 + 1] = p[1]; s_in[r][c * 3 + 2] = p[2];
   }
   __syncthreads();
-  // horizontal: out col d = 2j + e of the tile (j in [0,32)); e = 0 uses tile cols j .. j+7, e = 1 uses j+1 .. j+8
-  for (int i = tid; i < LZ_IN_H * 2 * LZ_TW * 3; i += 256) {
-    const int r = i / (2 * LZ_TW * 3), q = i - r * (2 * LZ_TW * 3);
-    const int d = q / 3, ch = q - d * 3;
-    const int j = d >> 1, e = d & 1;
-    unsigned acc = 0;
+  // horizontal: out col d = 2j + e of the tile (j in [0,32)); e = 0 uses tile cols j .. j+7, e = 1 uses j+1 .. j+8.
+  // One item = (row, channel, 4 input px): 12 bytes in registers feed 8 outputs.
+  for (int i = tid; i < LZ_IN_H * 3 * (LZ_TW / 4); i += 256) {
+    const int ch = i % 3, g = (i / 3) % (LZ_TW / 4), r = i / (3 * (LZ_TW / 4));
+    int v[12];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) acc += (unsigned)(c_lz[e][k] * (int)s_in[r][(j + e + k) * 3 + ch]);
-    s_h[r][q] = (int)acc;
+    for (int c = 0; c < 12; ++c) v[c] = s_in[r][(4 * g + c) * 3 + ch];
+#pragma unroll
+    for (int d = 0; d < 8; ++d) {
+      const int j = d >> 1, e = d & 1;
+      unsigned acc = 0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc += (unsigned)(c_lz[e][k] * v[j + e + k]);
+      s_h[r][(8 * g + d) * 3 + ch] = (int)acc;
+    }
   }
   __syncthreads();
-  // vertical: out row 2i + e of the tile; e = 0 uses tile rows i .. i+7, e = 1 uses i+1 .. i+8.  4 bytes per thread.
-  const int row_bytes = 2 * LZ_TW * 3;                       // 192
+  // vertical: out row 2i + e of the tile; e = 0 uses tile rows i .. i+7, e = 1 uses i+1 .. i+8.  One thread = 4 adjacent
+  // output bytes x 8 output rows: 12 rows of 4 ints in registers feed 32 outputs.
+  constexpr int row_bytes = 2 * LZ_TW * 3;                   // 192
   const int valid_bytes = min(row_bytes, (2 * W - 2 * x0) * 3);
   const size_t orow = (size_t)2 * W * 3;
   const bool word_ok = ((orow | (size_t)(2 * x0 * 3)) & 3) == 0 && ((reinterpret_cast<uintptr_t>(out) + fo) & 3) == 0;
-  for (int i = tid; i < 2 * LZ_TH * (row_bytes / 4); i += 256) {
-    const int orow_t = i / (row_bytes / 4), w4 = i - orow_t * (row_bytes / 4);
-    const int oy = 2 * y0 + orow_t;
-    if (oy >= 2 * H) continue;
-    const int ii = orow_t >> 1, e = orow_t & 1;
-    uint32_t packed = 0;
+  if (tid < 4 * (row_bytes / 4)) {
+    const int w4 = tid % (row_bytes / 4), rq = tid / (row_bytes / 4);
+    int4 hv[12];
 #pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      const int q = w4 * 4 + b;
-      unsigned acc = 0;
+    for (int r = 0; r < 12; ++r) hv[r] = *reinterpret_cast<const int4*>(&s_h[4 * rq + r][4 * w4]);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) acc += (unsigned)(c_lz[e][k] * s_h[ii + e + k][q]);
-      const int v = ((int)(acc + (1u << 21))) >> 22;
-      packed |= (uint32_t)min(max(v, 0), 255) << (8 * b);
-    }
-    uint8_t* o = out + fo + (size_t)oy * orow + (size_t)2 * x0 * 3 + w4 * 4;
-    if (word_ok && w4 * 4 + 4 <= valid_bytes) {
-      *reinterpret_cast<uint32_t*>(o) = packed;
-    } else {
-      for (int b = 0; b < 4; ++b)
-        if (w4 * 4 + b < valid_bytes) o[b] = (uint8_t)(packed >> (8 * b));
+    for (int t = 0; t < 8; ++t) {
+      const int orow_t = 8 * rq + t, oy = 2 * y0 + orow_t;
+      const int ii = t >> 1, e = t & 1;
+      unsigned a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int4 h4 = hv[ii + e + k];
+        a0 += (unsigned)(c_lz[e][k] * h4.x); a1 += (unsigned)(c_lz[e][k] * h4.y);
+        a2 += (unsigned)(c_lz[e][k] * h4.z); a3 += (unsigned)(c_lz[e][k] * h4.w);
+      }
+      const int v0 = ((int)(a0 + (1u << 21))) >> 22, v1 = ((int)(a1 + (1u << 21))) >> 22,
+                v2 = ((int)(a2 + (1u << 21))) >> 22, v3 = ((int)(a3 + (1u << 21))) >> 22;
+      const uint32_t packed = (uint32_t)min(max(v0, 0), 255) | ((uint32_t)min(max(v1, 0), 255) << 8) |
+                              ((uint32_t)min(max(v2, 0), 255) << 16) | ((uint32_t)min(max(v3, 0), 255) << 24);
+      if (oy < 2 * H) {
+        uint8_t* o = out + fo + (size_t)oy * orow + (size_t)2 * x0 * 3 + w4 * 4;
+        if (word_ok && w4 * 4 + 4 <= valid_bytes) {
+          *reinterpret_cast<uint32_t*>(o) = packed;
+        } else {
+          for (int bb = 0; bb < 4; ++bb)
+            if (w4 * 4 + bb < valid_bytes) o[bb] = (uint8_t)(packed >> (8 * bb));
+        }
+      }
     }
   }
 }
@@ -154,6 +238,17 @@ lanczos4_2x_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, in
 int launch_filter3x3(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, const float* k9, cudaStream_t s) {
   if (!in || !out || !k9 || n <= 0 || h <= 0 || w <= 0 || in == out)
     return fail(ctx, VEX_ERR_INVALID, "vex_filter3x3_u8: bad argument");
+  const int row_bytes = w * 3;
+  const bool aligned = ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  if (row_bytes % 16 == 0 && aligned && w >= 8 && !ctx->opt_force_generic_bicubic) {
+    dim3 grid((row_bytes / 16 + 127) / 128, (h + FILT_ROWS - 1) / FILT_ROWS, n);
+    if (grid.y > 65535 || grid.z > 65535) return fail(ctx, VEX_ERR_INVALID, "vex_filter3x3_u8: frame or batch too large");
+    filter3x3_rows_kernel<<<grid, 128, 0, s>>>(in, out, h, row_bytes, k9[0], k9[1], k9[2], k9[3], k9[4], k9[5], k9[6], k9[7],
+                                               k9[8]);
+    ctx->launches++;
+    VEX_CUDA(ctx, cudaGetLastError());
+    return VEX_OK;
+  }
   dim3 block(32, 8), grid((w + 31) / 32, (h + 7) / 8, n);
   if (grid.y > 65535 || grid.z > 65535) return fail(ctx, VEX_ERR_INVALID, "vex_filter3x3_u8: frame or batch too large");
   filter3x3_kernel<<<grid, block, 0, s>>>(in, out, h, w, k9[0], k9[1], k9[2], k9[3], k9[4], k9[5], k9[6], k9[7], k9[8]);
@@ -177,13 +272,12 @@ int launch_bilateral5(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int 
       const double r = sqrt((double)i * i + (double)j * j);
       if (r > 2) continue;
       tab.space[k] = (float)exp(r * r * gs);
-      tab.di[k] = (signed char)i; tab.dj[k] = (signed char)j;
       ++k;
     }
   if (!ctx->bilateral_cw) VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&ctx->bilateral_cw), sizeof(cw)));
   VEX_CUDA(ctx, cudaMemcpyAsync(ctx->bilateral_cw, cw, sizeof(cw), cudaMemcpyHostToDevice, s));
   VEX_CUDA(ctx, cudaStreamSynchronize(s));                   // cw lives on this stack frame
-  dim3 block(32, 8), grid((w + 31) / 32, (h + 7) / 8, n);
+  dim3 block(BL_TW, BL_TH), grid((w + BL_TW - 1) / BL_TW, (h + BL_TH - 1) / BL_TH, n);
   if (grid.y > 65535 || grid.z > 65535) return fail(ctx, VEX_ERR_INVALID, "vex_bilateral5_u8: frame or batch too large");
   bilateral5_kernel<<<grid, block, 0, s>>>(in, out, h, w, ctx->bilateral_cw, tab);
   ctx->launches++;

@@ -96,3 +96,24 @@ def test_errors_propagate_and_nothing_hangs(stage):
 def test_bad_depth():
     with pytest.raises(ValueError):
         pipeline.run_ordered_pipeline(lambda: None, lambda b, s: b, lambda r: None, depth=0)
+
+
+def test_video_metadata_keys_and_fallbacks(tmp_path):
+    """utils/video_utils.py:38-135 semantics: full key set, frame_count alias, zero record for an unreadable file."""
+    cv2 = pytest.importorskip("cv2")
+    from video_enhancer_proto_b200 import video_io
+    assert video_io.parse_rate("30000/1001") == pytest.approx(29.97, abs=1e-2)
+    assert video_io.parse_rate("25") == 25.0 and video_io.parse_rate("x/y") == 30.0 and video_io.parse_rate("1/0") == 30.0
+    p = tmp_path / "c.mp4"
+    wr = cv2.VideoWriter(str(p), cv2.VideoWriter_fourcc(*"mp4v"), 20.0, (64, 48))
+    if not wr.isOpened():
+        pytest.skip("OpenCV cannot write mp4v here")
+    for i in range(7):
+        wr.write(np.full((48, 64, 3), 30 * i, np.uint8))
+    wr.release()
+    m = video_io.video_metadata(str(p))
+    assert set(m) == set(video_io.KEYS)
+    assert (m["width"], m["height"]) == (64, 48) and m["frame_count"] == m["total_frames"] == 7
+    assert m["fps"] == pytest.approx(20.0, abs=0.5) and m["duration"] == pytest.approx(0.35, abs=0.06) and m["file_size"] > 0
+    z = video_io.video_metadata(str(tmp_path / "missing.mp4"))
+    assert set(z) == set(video_io.KEYS) and z["frame_count"] == 0 and z["width"] == 0

@@ -26,7 +26,7 @@ from typing import Dict, List, Mapping, Optional, Sequence
 import numpy as np
 import torch
 
-from . import _lib, pipeline, weights as W
+from . import _lib, pipeline, video_io, weights as W
 
 logger = logging.getLogger(__name__)
 
@@ -351,4 +351,5 @@ class B200VideoEnhancer:
             "scale": self.scale, "model": f"B200Upscaler-{self.model_name}",
             "input_resolution": f"{width}x{height}", "output_resolution": f"{width * 2}x{height * 2}",
             "fps": float(out_fps),
+            "input_metadata": video_io.video_metadata(input_path),       # utils/video_utils.py:38 key set
         }

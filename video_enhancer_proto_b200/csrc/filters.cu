@@ -157,40 +157,54 @@ bilateral5_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int
 // ------------------------------------------------------------------------------------------------ Lanczos4 2x
 constexpr int LZ_TH = 16, LZ_TW = 32;           // input tile; output tile 32 x 64
 constexpr int LZ_IN_H = LZ_TH + 8, LZ_IN_W = LZ_TW + 8;
+__constant__ float c_lzf[2][8] = {{-8.f, 64.f, -188.f, 579.f, 1830.f, -312.f, 114.f, -31.f},
+                                  {-31.f, 114.f, -312.f, 1830.f, 579.f, -188.f, 64.f, -8.f}};
 __constant__ int c_lz[2][8] = {{-8, 64, -188, 579, 1830, -312, 114, -31},     // even output (t = 0.75): src j-4 .. j+3
                                {-31, 114, -312, 1830, 579, -188, 64, -8}};    // odd output  (t = 0.25): src j-3 .. j+4
 
 // One block = 16 x 32 input pixels -> 32 x 64 output pixels.  Stage the input tile (+4 halo, replicate border) as bytes,
-// run the horizontal pass into int32 shared memory for the 24 rows the vertical pass needs, then the vertical pass.
-// int32 arithmetic wraps exactly like the C code it follows.
+// run the horizontal pass into int32 shared memory for the 24 rows the vertical pass needs (in fp32 FMAs: every partial sum
+// is an integer below 2^24, so it is exact and twice the integer-multiply rate), then the vertical pass in int32, which
+// wraps exactly like the C code it follows.
 __global__ void __launch_bounds__(256)
 lanczos4_2x_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int H, int W) {
-  __shared__ uint8_t s_in[LZ_IN_H][LZ_IN_W * 3];
+  __shared__ __align__(16) uint8_t s_in[LZ_IN_H][LZ_IN_W * 3];
   __shared__ __align__(16) int s_h[LZ_IN_H][2 * LZ_TW * 3];
   const int x0 = blockIdx.x * LZ_TW, y0 = blockIdx.y * LZ_TH;
   const size_t fi = (size_t)blockIdx.z * H * W * 3, fo = (size_t)blockIdx.z * H * W * 12;
   const int tid = threadIdx.x;
-  for (int i = tid; i < LZ_IN_H * LZ_IN_W; i += 256) {
-    const int r = i / LZ_IN_W, c = i - r * LZ_IN_W;
-    const int yy = min(max(y0 + r - 4, 0), H - 1), xx = min(max(x0 + c - 4, 0), W - 1);
-    const uint8_t* p = in + fi + ((size_t)yy * W + xx) * 3;
-    s_in[r][c * 3 + 0] = p[0]; s_in[r][c * 3 + 1] = p[1]; s_in[r][c * 3 + 2] = p[2];
+  // interior tiles (no clamping in x, 4-byte aligned rows): the 120-byte row segment arrives as 30 words per row
+  const bool interior_x = x0 >= 4 && x0 + LZ_TW + 4 <= W && (W & 3) == 0 && ((reinterpret_cast<uintptr_t>(in) + fi) & 3) == 0;
+  if (interior_x) {
+    for (int i = tid; i < LZ_IN_H * (LZ_IN_W * 3 / 4); i += 256) {
+      const int r = i / (LZ_IN_W * 3 / 4), c4 = i - r * (LZ_IN_W * 3 / 4);
+      const int yy = min(max(y0 + r - 4, 0), H - 1);
+      const uint32_t v = *reinterpret_cast<const uint32_t*>(in + fi + ((size_t)yy * W + (x0 - 4)) * 3 + 4 * c4);
+      *reinterpret_cast<uint32_t*>(&s_in[r][4 * c4]) = v;
+    }
+  } else {
+    for (int i = tid; i < LZ_IN_H * LZ_IN_W; i += 256) {
+      const int r = i / LZ_IN_W, c = i - r * LZ_IN_W;
+      const int yy = min(max(y0 + r - 4, 0), H - 1), xx = min(max(x0 + c - 4, 0), W - 1);
+      const uint8_t* p = in + fi + ((size_t)yy * W + xx) * 3;
+      s_in[r][c * 3 + 0] = p[0]; s_in[r][c * 3 + 1] = p[1]; s_in[r][c * 3 + 2] = p[2];
+    }
   }
   __syncthreads();
   // horizontal: out col d = 2j + e of the tile (j in [0,32)); e = 0 uses tile cols j .. j+7, e = 1 uses j+1 .. j+8.
   // One item = (row, channel, 4 input px): 12 bytes in registers feed 8 outputs.
   for (int i = tid; i < LZ_IN_H * 3 * (LZ_TW / 4); i += 256) {
     const int ch = i % 3, g = (i / 3) % (LZ_TW / 4), r = i / (3 * (LZ_TW / 4));
-    int v[12];
+    float v[12];
 #pragma unroll
-    for (int c = 0; c < 12; ++c) v[c] = s_in[r][(4 * g + c) * 3 + ch];
+    for (int c = 0; c < 12; ++c) v[c] = (float)s_in[r][(4 * g + c) * 3 + ch];
 #pragma unroll
     for (int d = 0; d < 8; ++d) {
       const int j = d >> 1, e = d & 1;
-      unsigned acc = 0;
+      float acc = 0.f;                                         // |partial sums| <= 255 * 3126 < 2^24: exact in fp32
 #pragma unroll
-      for (int k = 0; k < 8; ++k) acc += (unsigned)(c_lz[e][k] * v[j + e + k]);
-      s_h[r][(8 * g + d) * 3 + ch] = (int)acc;
+      for (int k = 0; k < 8; ++k) acc = fmaf(c_lzf[e][k], v[j + e + k], acc);
+      s_h[r][(8 * g + d) * 3 + ch] = __float2int_rn(acc);
     }
   }
   __syncthreads();
@@ -263,20 +277,22 @@ int launch_bilateral5(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int 
     return fail(ctx, VEX_ERR_INVALID, "vex_bilateral5_u8: bad argument");
   // tables exactly as cv::bilateralFilter builds them (double exp, cast to float)
   const double gc = -0.5 / ((double)sigma_color * sigma_color), gs = -0.5 / ((double)sigma_space * sigma_space);
-  float cw[768];
-  for (int i = 0; i < 768; ++i) cw[i] = (float)exp((double)i * i * gc);
   BilateralTab tab;
   int k = 0;
   for (int i = -2; i <= 2; ++i)
     for (int j = -2; j <= 2; ++j) {
       const double r = sqrt((double)i * i + (double)j * j);
       if (r > 2) continue;
-      tab.space[k] = (float)exp(r * r * gs);
-      ++k;
+      tab.space[k++] = (float)exp(r * r * gs);
     }
-  if (!ctx->bilateral_cw) VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&ctx->bilateral_cw), sizeof(cw)));
-  VEX_CUDA(ctx, cudaMemcpyAsync(ctx->bilateral_cw, cw, sizeof(cw), cudaMemcpyHostToDevice, s));
-  VEX_CUDA(ctx, cudaStreamSynchronize(s));                   // cw lives on this stack frame
+  if (!ctx->bilateral_cw || ctx->bilateral_sigma != sigma_color) {     // colour table: uploaded once per sigma
+    float cw[768];
+    for (int i = 0; i < 768; ++i) cw[i] = (float)exp((double)i * i * gc);
+    if (!ctx->bilateral_cw) VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&ctx->bilateral_cw), sizeof(cw)));
+    VEX_CUDA(ctx, cudaDeviceSynchronize());                            // no kernel may still be reading the old table
+    VEX_CUDA(ctx, cudaMemcpy(ctx->bilateral_cw, cw, sizeof(cw), cudaMemcpyHostToDevice));
+    ctx->bilateral_sigma = sigma_color;
+  }
   dim3 block(BL_TW, BL_TH), grid((w + BL_TW - 1) / BL_TW, (h + BL_TH - 1) / BL_TH, n);
   if (grid.y > 65535 || grid.z > 65535) return fail(ctx, VEX_ERR_INVALID, "vex_bilateral5_u8: frame or batch too large");
   bilateral5_kernel<<<grid, block, 0, s>>>(in, out, h, w, ctx->bilateral_cw, tab);

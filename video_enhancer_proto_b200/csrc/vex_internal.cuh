@@ -25,6 +25,7 @@ int launch_lanczos4_2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int
 struct vex_ctx {
   int device = 0;
   float* bilateral_cw = nullptr;   // colour-weight table of vex_bilateral5_u8 (768 floats, device)
+  float bilateral_sigma = -1.f;    // sigma_color the table was built for
   int sm_count = 148;
   std::string err;
   unsigned long long launches = 0;

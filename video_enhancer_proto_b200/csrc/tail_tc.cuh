@@ -262,8 +262,10 @@ uptail_kernel(const UTParams p) {
       named_bar_sync(1 + grp, 128);
       const int nvx = min(G27_TW, W2 - x0);
 #pragma unroll 1
-      for (int idx = (p.probe & 1) ? 1000 : et; idx < G27_ROWS * G27_TW; idx += 128) {
-        const int ty = idx / G27_TW, tx = idx - ty * G27_TW;
+      // one warp = one tile row (lanes 30, 31 idle): a warp's 32 loads then fall into one row of Ys, i.e. 32 banks
+      for (int idx = (p.probe & 1) ? 1000 : et; idx < G27_ROWS * 32; idx += 128) {
+        const int ty = idx >> 5, tx = idx & 31;
+        if (tx >= G27_TW) continue;
         const int y = y0 + ty, x = x0 + tx;
         float s0 = b0, s1 = b1, s2 = b2;
 #pragma unroll

@@ -383,8 +383,10 @@ gemm27_kernel(const __grid_constant__ CUtensorMap amap, const G27Params p) {
       // 9-tap gather-sum: out(ty,tx) = bias + sum_t Y[(ty+t/3)*32 + tx+t%3][t*3+co]
       const int nvx = min(G27_TW, p.W - x0);                    // valid pixels per row of this tile
 #pragma unroll 1
-      for (int idx = et; idx < G27_ROWS * G27_TW; idx += 128) {
-        const int ty = idx / G27_TW, tx = idx - ty * G27_TW;
+      // one warp = one tile row (lanes 30, 31 idle): a warp's 32 loads then fall into one row of Ys, i.e. 32 banks
+      for (int idx = et; idx < G27_ROWS * 32; idx += 128) {
+        const int ty = idx >> 5, tx = idx & 31;
+        if (tx >= G27_TW) continue;
         const int y = y0 + ty, x = x0 + tx;
         float s0 = b0, s1 = b1, s2 = b2;
 #pragma unroll

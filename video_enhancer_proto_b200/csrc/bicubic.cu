@@ -241,7 +241,7 @@ bicubic2x_strip_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out
                    : "memory");
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
-  const uint8_t* nsrc;                                        // source of the next row to issue (clamped in y)
+  const uint8_t* nsrc = nullptr;                              // source of the next row to issue (clamped in y)
   auto issue_next = [&](int y, int slot) {                    // y = unclamped row of nsrc
     if (chunk_lane)
       asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(ring_dst + slot * RING_ROW),

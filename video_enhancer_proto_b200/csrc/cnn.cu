@@ -353,7 +353,7 @@ int launch_i27(vex_ctx* ctx, unsigned abit, const void* in, const uint8_t* w, co
     ctx->attr_mask |= abit;
   }
   thin::I27Params p;
-  p.in = in; p.wpack = w; p.bias = bias; p.out = out; p.H = H; p.W = W;
+  p.in = in; p.wpack = w; p.out = out; p.H = H; p.W = W;   // the bias travels inside w (k = 27, 28)
   p.npix = (long long)n * H * W; p.in_bgr = in_bgr; p.probe = ctx->opt_thin_probe;
   const long long items = (p.npix + 127) / 128;
   thin::im2col27_kernel<MODE, BN><<<(unsigned)std::min<long long>(items, ctx->sm_count), thin::I27_THREADS, C::SMEM, s>>>(p);
@@ -548,7 +548,13 @@ int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const*
   // ---- tensor-core images of the thin layers (thin_tc.cuh); k = (ky*3+kx)*3+ci, rows = output columns
   if (c1 <= 256) {   // conv1: [c1 rows][k < 27], BN scale and 1/255 folded
     rc = pack_rows_sw128(ctx, &P->t1w, c1, 1, [&](int r, int k) -> float {
-      if (k >= 27) return 0.f;
+      if (k == 27 || k == 28) {                      // folded bias as hi + lo bf16 against the builders' constant-1 columns
+        const uint32_t hb = (uint32_t)f32_to_bf16_rne(shift[0][r]) << 16;
+        float hi;
+        memcpy(&hi, &hb, 4);
+        return k == 27 ? hi : shift[0][r] - hi;
+      }
+      if (k > 28) return 0.f;
       const int ci = k % 3, tap = k / 3;
       return cw[0][((size_t)r * 3 + ci) * 9 + tap] * scale[0][r] * (1.0f / 255.0f);
     });
@@ -705,7 +711,7 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
     return VEX_OK;
   }
   if (thin_tc) {
-    if ((rc = launch_i27<thin::MODE_UP1, 256>(ctx, 64u, x5, P->tu1w, P->tu1b, up, n, H, W, 0, s))) return rc;
+    if ((rc = launch_i27<thin::MODE_UP1, 256>(ctx, 64u, x5, P->tu1wb, P->tu1b, up, n, H, W, 0, s))) return rc;
   } else {
     dim3 grid((W + 31) / 32, H, n);
     small::upconv1_kernel<<<grid, 128, (size_t)49 * d.up_ch * 4, s>>>(x5, up, P->wu1, P->bu1, H, W, d.up_ch);

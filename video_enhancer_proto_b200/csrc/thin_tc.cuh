@@ -50,8 +50,7 @@ struct I27Cfg {
 
 struct I27Params {
   const void* in;          // MODE_CONV1: uint8 [n][H][W][3];  MODE_UP1: float4 [n][H][W]
-  const uint8_t* wpack;    // BN rows x 128 B, SWIZZLE_128B image, k = (ky*3+kx)*3+ci in the first 32 bf16
-  const float* bias;       // [BN]
+  const uint8_t* wpack;    // BN rows x 128 B, SWIZZLE_128B image, k = (ky*3+kx)*3+ci for k < 27; k = 27, 28 = bias as hi + lo bf16
   __nv_bfloat16* out;      // MODE_CONV1: [n][H][W][BN];  MODE_UP1: [n][2H][2W][BN/4]
   int H, W;
   long long npix;          // n*H*W
@@ -72,7 +71,6 @@ im2col27_kernel(const I27Params p) {
   const uint32_t acc_full = a_empty + 8 * I27_SA, acc_empty = acc_full + 8 * C::NACC;
   const uint32_t w_bar = acc_empty + 8 * C::NACC, tmem_slot = w_bar + 8;
   volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(sm + C::BAR_OFF + (tmem_slot - bar0));
-  float* bias_s = reinterpret_cast<float*>(sm + C::BIAS_OFF);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long items = (p.npix + 127) / 128;
 
@@ -82,7 +80,6 @@ im2col27_kernel(const I27Params p) {
     ptx::mbar_init(w_bar, 1);
     ptx::fence_mbar_init();
   }
-  for (int i = threadIdx.x; i < BN; i += I27_THREADS) bias_s[i] = p.bias[i];
   if (warp == I27_MMA_WARP) {
     ptx::tmem_alloc(tmem_slot, 512);
     ptx::tmem_relinquish();
@@ -132,7 +129,8 @@ im2col27_kernel(const I27Params p) {
         }
 #pragma unroll
         for (int j = 0; j < 13; ++j) w[j] = ptx::pack_bf16x2(v[2 * j], v[2 * j + 1]);
-        w[13] = ptx::pack_bf16x2(v[26], 0.f);
+        w[13] = ptx::pack_bf16x2(v[26], 1.0f);       // k = 27, 28: constant 1 against the bias rows (hi + lo bf16) of W, so the
+        w[14] = ptx::pack_bf16x2(1.0f, 0.f);         // drain needs no per-element bias load and add
       }
       ptx::mbar_wait(a_empty + 8 * sa, pa ^ 1);
       uint8_t* row = sm + sa * C::A_STAGE + r * 128;
@@ -215,7 +213,7 @@ im2col27_kernel(const I27Params p) {
           for (int j4 = 0; j4 < 4; ++j4) {
             float f[8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[j4 * 8 + e]) + bias_s[col + j4 * 8 + e];
+            for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[j4 * 8 + e]);   // bias already inside (k = 27, 28)
             *reinterpret_cast<uint4*>(stg + (g * 4 + j4) * 16) =
                 make_uint4(ptx::pack_relu_bf16x2(f[0], f[1]), ptx::pack_relu_bf16x2(f[2], f[3]),
                            ptx::pack_relu_bf16x2(f[4], f[5]), ptx::pack_relu_bf16x2(f[6], f[7]));

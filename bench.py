@@ -236,9 +236,9 @@ def gpu_workload(workload, enh, args, world, rank, local, warmup, peaks, torch, 
         achieved = BICUBIC_BYTES_PER_FRAME * fps_step / (kern_ms / 1e3) / 1e9
         roof = {"bound": "hbm", "kernel": "bicubic2x_strip_kernel", "achieved": achieved, "peak": peaks["hbm_gbs"],
                 "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
-                # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/r1_v6_ncu_full_bicubic.csv:
+                # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/r1_v7_ncu_full_bicubic.csv:
                 # 2.003 + 7.407 GB for 300 frames), scaled to this launch's frame count
-                "traffic": int(9.410e9 * fps_step / 300), "traffic_source": "profiles/r1_v6_ncu_full_bicubic.csv",
+                "traffic": int(9.410e9 * fps_step / 300), "traffic_source": "profiles/r1_v7_ncu_full_bicubic.csv",
                 "peak_source": peaks["source"],
                 "algorithmic_bytes_per_launch": BICUBIC_BYTES_PER_FRAME * fps_step, "launch_ms": kern_ms}
         dtype = "u8"
@@ -250,9 +250,9 @@ def gpu_workload(workload, enh, args, world, rank, local, warmup, peaks, torch, 
         peak = peaks["bf16_tflops_sustained"]
         roof = {"bound": "tensor", "kernel": "conv3x3_tc_kernel (conv2+conv3+conv4, 3 launches/step)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                # DRAM bytes per launch (mean of the 3 launches), ncu --set full on batch 8 (profiles/r1_v6_ncu_full_cnn.csv:
-                # conv2 4.76+4.21, conv3 5.44+8.45, conv4 9.54+4.22 GB), scaled to this step's frame count
-                "traffic": int(12.21e9 * fps_step / 8), "traffic_source": "profiles/r1_v6_ncu_full_cnn.csv",
+                # DRAM bytes per launch (mean of the 3 launches), ncu --set full on batch 8 (profiles/r1_v7_ncu_full_cnn.csv:
+                # conv2 4.55+4.21, conv3 5.10+8.45, conv4 9.33+4.22 GB), scaled to this step's frame count
+                "traffic": int(11.95e9 * fps_step / 8), "traffic_source": "profiles/r1_v7_ncu_full_cnn.csv",
                 "peak_source": peaks["source"] + " (sustained cuBLAS bf16: the kernel is timed inside a long power-capped step)",
                 # the same achieved figure against the burst cuBLAS number (a kernel timed alone) - above 1.0 of the sustained
                 # peak means only that these layers, between the lighter thin layers, hold higher clocks than a pure GEMM loop

@@ -128,3 +128,23 @@ def test_synth_generators_are_deterministic():
     assert all(f.shape == (48, 64, 3) and f.dtype == np.uint8 for f in a)
     t = synth.tag_frame(a[0], 0x01020304)
     assert synth.read_tag(t) == 0x01020304
+
+
+def test_basic_upscaler_twin_constructor_semantics():
+    """basic_upscaler_fallback.py:45-62: (device, model_name, scale) order, unknown names fall back to Lanczos; modes without
+    a kernel are refused instead of silently running on the CPU.  No CUDA is touched before the first frame."""
+    import inspect
+    from video_enhancer_proto_b200.basic_upscaler import B200BasicUpscaler, SHARPEN_KERNEL
+    assert list(inspect.signature(B200BasicUpscaler.__init__).parameters)[1:4] == ["device", "model_name", "scale"]
+    assert B200BasicUpscaler(model_name="cubic").method == "CUBIC"
+    assert B200BasicUpscaler(model_name="something-else").method == "LANCZOS"
+    for name in ("LINEAR", "area", "NEAREST"):
+        with pytest.raises(ValueError):
+            B200BasicUpscaler(model_name=name)
+    with pytest.raises(ValueError):
+        B200BasicUpscaler(scale=4)
+    info = B200BasicUpscaler(model_name="LANCZOS").get_model_info()
+    assert {"name", "description", "scale", "device", "interpolation_method", "capabilities"} <= set(info)
+    # basic_upscaler_fallback.py:123-124 in float32: the whole kernel is scaled, so it sums to 0.1
+    assert SHARPEN_KERNEL.dtype == np.float32 and abs(float(SHARPEN_KERNEL.sum()) - 0.1) < 1e-6
+    assert float(SHARPEN_KERNEL[1, 1]) == float(np.float32(9) * np.float32(0.1))

@@ -38,9 +38,7 @@ struct CnnPlan {
   TcLayer tc[3];                             // conv2, conv3, conv4
   TcLayer extra[VEX_CNN_MAX_EXTRA];          // deepened plans: c3 -> c3 blocks after conv3
   // thin layers on the tensor cores (thin_tc.cuh): SWIZZLE_128B operand images, bf16
-  uint8_t *t1w = nullptr, *tu1w = nullptr, *t5w = nullptr, *tu2w = nullptr;
-  uint8_t* tu1wb = nullptr;                  // tu1w with the bias in k = 27, 28 (fused tail, tail_tc.cuh)
-  float* tu1b = nullptr;                     // upconv1 bias replicated per PixelShuffle phase [4*up]
+  uint8_t *t1w = nullptr, *tu1wb = nullptr, *t5w = nullptr, *tu2w = nullptr;   // t1w / tu1wb carry their bias in k = 27, 28
   // workspace
   uint8_t* ws = nullptr;
   size_t ws_bytes = 0;
@@ -344,7 +342,7 @@ int pack_rows_sw128(vex_ctx* ctx, uint8_t** dst, int rows, int nchunk, F value) 
 }
 
 template <int MODE, int BN>
-int launch_i27(vex_ctx* ctx, unsigned abit, const void* in, const uint8_t* w, const float* bias, __nv_bfloat16* out,
+int launch_i27(vex_ctx* ctx, unsigned abit, const void* in, const uint8_t* w, __nv_bfloat16* out,
                int n, int H, int W, int in_bgr, cudaStream_t s) {
   using C = thin::I27Cfg<BN>;
   if (!(ctx->attr_mask & abit)) {
@@ -563,15 +561,7 @@ int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const*
   {  // upconv1 as conv3x3 3 -> 4*up + PixelShuffle(2): row = phase*up + co, phase = py*2+px.
      // 3x3 tap index ky' (input row y + ky' - 1) -> transposed-conv kernel row ky:  py=0: {1->1, 0->3}, py=1: {2->0, 1->2}
     const int kmap[2][3] = {{3, 1, -1}, {-1, 2, 0}};
-    rc = pack_rows_sw128(ctx, &P->tu1w, 4 * up, 1, [&](int r, int k) -> float {
-      if (k >= 27) return 0.f;
-      const int ph = r / up, co = r % up, ci = k % 3, tap = k / 3;
-      const int ky = kmap[ph >> 1][tap / 3], kx = kmap[ph & 1][tap % 3];
-      if (ky < 0 || kx < 0) return 0.f;
-      return u1w[(((size_t)ci * up + co) * 4 + ky) * 4 + kx];
-    });
-    if (rc) return rc;
-    // same image with the bias folded in as two bf16 terms (hi + lo) at k = 27, 28; the fused tail's builder puts 1.0 there
+    // the bias is folded in as two bf16 terms (hi + lo) at k = 27, 28; the builders put 1.0 there (thin_tc.cuh, tail_tc.cuh)
     rc = pack_rows_sw128(ctx, &P->tu1wb, 4 * up, 1, [&](int r, int k) -> float {
       const int ph = r / up, co = r % up;
       if (k == 27 || k == 28) {
@@ -587,9 +577,6 @@ int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const*
       return u1w[(((size_t)ci * up + co) * 4 + ky) * 4 + kx];
     });
     if (rc) return rc;
-    std::vector<float> b4((size_t)4 * up);
-    for (int i = 0; i < 4 * up; ++i) b4[i] = u1b[i % up];
-    if ((rc = upload(ctx, &P->tu1b, b4.data(), b4.size() * 4))) return rc;
   }
   // conv5 / upconv2 as 1x1 GEMMs: row n = tap*3+co (27 of 32), K = input channels
   rc = pack_rows_sw128(ctx, &P->t5w, 32, c4 / 64, [&](int r, int k) -> float {
@@ -652,9 +639,9 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
   const bool thin_tc = ctx->opt_thin_tc != 0;
   mark();
   if (thin_tc && d.c1 == 128) {
-    if ((rc = launch_i27<thin::MODE_CONV1, 128>(ctx, 8u, in, P->t1w, P->b1, x1, n, H, W, in_bgr, s))) return rc;
+    if ((rc = launch_i27<thin::MODE_CONV1, 128>(ctx, 8u, in, P->t1w, x1, n, H, W, in_bgr, s))) return rc;
   } else if (thin_tc && d.c1 == 256) {
-    if ((rc = launch_i27<thin::MODE_CONV1, 256>(ctx, 16u, in, P->t1w, P->b1, x1, n, H, W, in_bgr, s))) return rc;
+    if ((rc = launch_i27<thin::MODE_CONV1, 256>(ctx, 16u, in, P->t1w, x1, n, H, W, in_bgr, s))) return rc;
   } else {
     dim3 grid((W + 31) / 32, (H + 7) / 8, n);
     small::conv1_u8_kernel<<<grid, dim3(32, 8), small::conv1_smem(d.c1), s>>>(in, x1, P->w1g, P->b1, H, W, d.c1,
@@ -711,7 +698,7 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
     return VEX_OK;
   }
   if (thin_tc) {
-    if ((rc = launch_i27<thin::MODE_UP1, 256>(ctx, 64u, x5, P->tu1wb, P->tu1b, up, n, H, W, 0, s))) return rc;
+    if ((rc = launch_i27<thin::MODE_UP1, 256>(ctx, 64u, x5, P->tu1wb, up, n, H, W, 0, s))) return rc;
   } else {
     dim3 grid((W + 31) / 32, H, n);
     small::upconv1_kernel<<<grid, 128, (size_t)49 * d.up_ch * 4, s>>>(x5, up, P->wu1, P->bu1, H, W, d.up_ch);
@@ -803,8 +790,8 @@ int cnn_repack(vex_ctx* ctx) {
 void cnn_destroy(vex_ctx* ctx) {
   CnnPlan* P = ctx->cnn;
   if (!P) return;
-  float* fs[] = {P->w1g, P->b1, P->w5g, P->b5, P->wu1, P->bu1, P->wu2, P->bu2, P->tu1b};
-  uint8_t* us[] = {P->t1w, P->tu1w, P->tu1wb, P->t5w, P->tu2w};
+  float* fs[] = {P->w1g, P->b1, P->w5g, P->b5, P->wu1, P->bu1, P->wu2, P->bu2};
+  uint8_t* us[] = {P->t1w, P->tu1wb, P->t5w, P->tu2w};
   for (uint8_t* u : us)
     if (u) cudaFree(u);
   for (float* f : fs)

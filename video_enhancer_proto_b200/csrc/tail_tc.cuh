@@ -96,32 +96,44 @@ uptail_kernel(const UTParams p) {
     // ================================ builders: low-res pixel r of the 5 x 17 patch -> one operand row
     const int r = threadIdx.x;
     const int lr = r / UT_LC, lc = r - lr * UT_LC;
-    uint32_t k = 0;
-    for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
+    // The gather is pure latency (9 independent 16-byte loads, then a dependent pack), so the loads of item k+1 are
+    // issued as soon as item k is packed, before its hand-off (wait for a free stage, store, arrive).
+    auto gather = [&](int it, float4 (&f)[9]) -> bool {
       const int txi = it % p.tiles_x, t = it / p.tiles_x;
       const int tyi = t % p.tiles_y, n = t / p.tiles_y;
       const int y = 3 * tyi - 1 + lr, x = 15 * txi - 1 + lc;
+      const bool live = r < UT_ROWS1 && y >= 0 && y < p.H && x >= 0 && x < p.W && !(p.probe & 4);
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky) {
+        const int yy = y + ky - 1;
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+          const int xx = x + kx - 1;
+          f[ky * 3 + kx] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (live && yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) f[ky * 3 + kx] = __ldg(p.x5 + ((size_t)n * p.H + yy) * p.W + xx);
+        }
+      }
+      return live;
+    };
+    float4 f[9];
+    bool live = false;
+    if ((int)blockIdx.x < total) live = gather(blockIdx.x, f);
+    uint32_t k = 0;
+    for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
       uint32_t w[16];
 #pragma unroll
       for (int j = 0; j < 16; ++j) w[j] = 0u;
-      if (r < UT_ROWS1 && y >= 0 && y < p.H && x >= 0 && x < p.W && !(p.probe & 4)) {
+      if (live) {
         float v[27];
 #pragma unroll
-        for (int ky = 0; ky < 3; ++ky) {
-          const int yy = y + ky - 1;
-#pragma unroll
-          for (int kx = 0; kx < 3; ++kx) {
-            const int xx = x + kx - 1;
-            float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) f = __ldg(p.x5 + ((size_t)n * p.H + yy) * p.W + xx);
-            v[(ky * 3 + kx) * 3 + 0] = f.x; v[(ky * 3 + kx) * 3 + 1] = f.y; v[(ky * 3 + kx) * 3 + 2] = f.z;
-          }
-        }
+        for (int q9 = 0; q9 < 9; ++q9) { v[q9 * 3 + 0] = f[q9].x; v[q9 * 3 + 1] = f[q9].y; v[q9 * 3 + 2] = f[q9].z; }
 #pragma unroll
         for (int j = 0; j < 13; ++j) w[j] = ptx::pack_bf16x2(v[2 * j], v[2 * j + 1]);
         w[13] = ptx::pack_bf16x2(v[26], 1.0f);       // k = 27, 28: constant 1 against the bias rows of W1
         w[14] = ptx::pack_bf16x2(1.0f, 0.f);
       }
+      const int itn = it + gridDim.x;                // the packed row frees f: the next item's loads fly during the hand-off
+      if (itn < total) live = gather(itn, f);
       const uint32_t sa = k & 1, pa = (k >> 1) & 1;
       ptx::mbar_wait(a1_empty + 8 * sa, pa ^ 1);
       uint8_t* row = sm + C::A1_OFF + sa * C::A1_STAGE + r * 128;

@@ -469,10 +469,19 @@ def main():
         raise SystemExit("bench.py: no CUDA device; the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
-        # stdout carries exactly one JSON line: NCCL's own log (the "NCCL version ..." banner at NCCL_DEBUG >= VERSION) goes
-        # to stderr instead
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+        # stdout carries exactly one JSON line.  NCCL prints its "NCCL version ..." banner to stdout when the environment
+        # sets NCCL_DEBUG=VERSION (this image does), so file descriptor 1 points at stderr while the communicator comes up.
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
     warmup = max(args.warmup, 3)
     peaks = load_peaks()
     if workload == "wide":                                  # configs[4]; a reporting workload, not the driver's default

@@ -265,7 +265,7 @@ def gpu_workload(workload, enh, args, world, rank, local, warmup, peaks, torch, 
             "launches": int(launches), "roofline": roof, "dtype": dtype,
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": e2e_frames * fin,
                     "d2h_bytes_per_step": e2e_frames * fin * 4, "frames_per_step": e2e_frames, "steps": e2e_steps,
-                    "api": "vex_upscale_host (pinned host in/out, H2D/compute/D2H streams, 2 slots x 8-frame chunks; the call returns when every output frame is on the host)"}}
+                    "api": "vex_upscale_host (pinned host in/out, H2D/compute/D2H streams, 2 slots x 8-frame chunks with quarter-size first and last chunks; the call returns when every output frame is on the host)"}}
 
 
 def gpu_stream(enh, args, world, rank, torch, dist, synth, _lib):

@@ -1,6 +1,7 @@
 // C ABI of libvex.so (include/vex.h): context, argument checking, host-buffer streaming.
 #include <algorithm>
 #include <string.h>
+#include <vector>
 
 #include "vex_internal.cuh"
 
@@ -188,9 +189,19 @@ int vex_upscale_host(vex_ctx* ctx, int mode, const uint8_t* in_host, uint8_t* ou
   // Three-stage pipeline over two device slots: chunk k's H2D (copy-in stream), kernels (compute stream)
   // and D2H (copy-out stream) are chained by events, so H2D(k+1) and D2H(k-1) overlap compute(k), and the
   // CNN workspace is only ever touched from the compute stream.
-  int k = 0;
-  for (int f0 = 0; f0 < n; f0 += chunk, ++k) {
-    const int nf = std::min(chunk, n - f0), sl = k & 1;
+  // Chunk schedule: the first H2D and the last D2H are the only copies no kernel hides, so long calls start and end with
+  // a quarter-size chunk (48 frames at chunk 8: 2, 8, 8, 8, 8, 8, 4, 2).
+  std::vector<int> sizes;
+  {
+    const int edge = (n >= 3 * chunk && chunk >= 4) ? chunk / 4 : 0;
+    int mid = n - 2 * edge;
+    if (edge) sizes.push_back(edge);
+    while (mid > 0) { sizes.push_back(std::min(chunk, mid)); mid -= sizes.back(); }
+    if (edge) sizes.push_back(edge);
+  }
+  int k = 0, f0 = 0;
+  for (size_t ci = 0; ci < sizes.size(); f0 += sizes[ci], ++ci, ++k) {
+    const int nf = sizes[ci], sl = k & 1;
     if (k >= 2) VEX_CUDA(ctx, cudaStreamWaitEvent(ctx->st_h2d, ctx->ev_comp[sl], 0));   // input slot consumed
     VEX_CUDA(ctx, cudaMemcpyAsync(ctx->slot_in[sl], in_host + fin * f0, fin * nf, cudaMemcpyHostToDevice,
                                   ctx->st_h2d));

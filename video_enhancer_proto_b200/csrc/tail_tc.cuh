@@ -152,6 +152,10 @@ uptail_kernel(const UTParams p) {
       ptx::mbar_wait(w_bar, 0);
       constexpr uint32_t idesc1 = ptx::idesc_bf16_f32(128, 128);
       constexpr uint32_t idesc2 = ptx::idesc_bf16_f32(128, 32);
+      // descriptors are encoded once; inside the loop an operand is one add away (ptx::desc_advance) - this thread's
+      // serial instruction stream paces the whole kernel
+      const uint64_t a1d0 = ptx::smem_desc_sw128(sbase + C::A1_OFF, 0), w1d = ptx::smem_desc_sw128(sbase + C::W1_OFF, 0);
+      const uint64_t a2d0 = ptx::smem_desc_sw128(sbase + C::A2_OFF, 0), w2d = ptx::smem_desc_sw128(sbase + C::W2_OFF, 0);
       auto gemm2 = [&](uint32_t j) {
         const uint32_t s = j & 1, ph = (j >> 1) & 1;
         const uint32_t eg = j % UT_EPI_GROUPS, eu = j / UT_EPI_GROUPS;    // epilogue group and its use count
@@ -162,8 +166,8 @@ uptail_kernel(const UTParams p) {
         for (int g = 0; g < 2; ++g)
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
-            const uint64_t ad = ptx::smem_desc_sw128(sbase + C::A2_OFF + s * C::A2_STAGE + g * 16384 + kk * 32, 0);
-            const uint64_t bd = ptx::smem_desc_sw128(sbase + C::W2_OFF + kk * 32, 0);
+            const uint64_t ad = ptx::desc_advance(a2d0, s * C::A2_STAGE + g * 16384 + kk * 32);
+            const uint64_t bd = ptx::desc_advance(w2d, kk * 32);
             ptx::mma_bf16_ss(tmem + 256 + eg * 64 + g * 32, ad, bd, idesc2, kk != 0);
           }
         ptx::tc_commit(a2_empty + 8 * s);
@@ -179,8 +183,8 @@ uptail_kernel(const UTParams p) {
           ptx::tc_fence_after();
 #pragma unroll
           for (int kk = 0; kk < 2; ++kk) {
-            const uint64_t ad = ptx::smem_desc_sw128(sbase + C::A1_OFF + sa * C::A1_STAGE + kk * 32, 0);
-            const uint64_t bd = ptx::smem_desc_sw128(sbase + C::W1_OFF + h * 16384 + kk * 32, 0);
+            const uint64_t ad = ptx::desc_advance(a1d0, sa * C::A1_STAGE + kk * 32);
+            const uint64_t bd = ptx::desc_advance(w1d, h * 16384 + kk * 32);
             ptx::mma_bf16_ss(tmem + h * 128, ad, bd, idesc1, kk);
           }
           ptx::tc_commit(acc1_full + 8 * h);

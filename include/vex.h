@@ -68,6 +68,14 @@ int vex_bicubic2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc,
  * OpenCV's 11-bit fixed-point 8-tap separable path, replicate border.  Bit-exact.  out: n*[2h][2w][3]. */
 int vex_lanczos4_2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w, void* stream);
 
+/* cv2.resize(frame, (2w, 2h), interpolation=code) for every method BasicUpscalerFallback maps a model name to
+ * (basic_upscaler_fallback.py:51-57,120); `interpolation` takes OpenCV's own flag values: 0 INTER_NEAREST, 1 INTER_LINEAR
+ * (11-bit fixed-point bilinear, replicate border), 2 INTER_CUBIC (= vex_bicubic2x_u8 round_mode 1), 3 INTER_AREA (enlarging
+ * by 2 replicates pixels, like NEAREST), 4 INTER_LANCZOS4 (= vex_lanczos4_2x_u8).  NEAREST / LINEAR / AREA / LANCZOS4 are
+ * bit-exact, CUBIC within 1 LSB.  out: n*[2h][2w][3]. */
+int vex_resize2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w, int interpolation,
+                    void* stream);
+
 /* cv2.bilateralFilter(frame, 5, sigma_color, sigma_space) (basic_upscaler_fallback.py:117; the reference passes 50, 50):
  * diameter 5 -> the 13 taps within radius 2, BORDER_REFLECT_101.  in != out.  out: n*[h][w][3]. */
 int vex_bilateral5_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w, float sigma_color,

@@ -249,7 +249,8 @@ def ref_basic_upscaler_frame(frame: np.ndarray, model_name: str = "LANCZOS", sca
     bilateral pre-filter for LANCZOS (:115-117), cv2.resize with the mode's interpolation (:120), the 0.1-scaled
     sharpening filter2D and clip (:123-128).  ``stages=True`` also returns the intermediate images."""
     import cv2
-    interpolation = {"LANCZOS": cv2.INTER_LANCZOS4, "CUBIC": cv2.INTER_CUBIC}[model_name.upper()]
+    interpolation = {"LANCZOS": cv2.INTER_LANCZOS4, "CUBIC": cv2.INTER_CUBIC, "LINEAR": cv2.INTER_LINEAR,
+                     "AREA": cv2.INTER_AREA, "NEAREST": cv2.INTER_NEAREST}[model_name.upper()]   # :51-57
     out_h, out_w = frame.shape[0] * scale, frame.shape[1] * scale
     den = frame
     if model_name.upper() == "LANCZOS":
@@ -260,6 +261,29 @@ def ref_basic_upscaler_frame(frame: np.ndarray, model_name: str = "LANCZOS", sca
     upscaled = cv2.filter2D(upscaled0, -1, kernel)
     upscaled = np.clip(upscaled, 0, 255).astype(np.uint8)
     return (upscaled, den, upscaled0) if stages else upscaled
+
+
+def np_linear2x_u8(frame: np.ndarray) -> np.ndarray:
+    """Exact restatement of cv2.resize(frame, (2w, 2h), INTER_LINEAR) for uint8 (basic_upscaler_fallback.py:54,120).
+    OpenCV's 8-bit bilinear path is 11-bit fixed point: H pass S = 512*far + 1536*near (phases 0.25 / 0.75, replicate
+    border), V pass ((b0 * (S0 >> 4)) >> 16) + ((b1 * (S1 >> 4)) >> 16), then (x + 2) >> 2.  With g = far + 3*near
+    (S >> 4 = 32 g) that is ((3 g_near >> 2) + (g_far >> 2) + 2) >> 2: both truncating shifts are OpenCV's."""
+    s = frame.astype(np.int64)
+    h, w = s.shape[:2]
+    dx = np.arange(2 * w)
+    k = dx // 2
+    far = np.clip(np.where(dx % 2 == 0, k - 1, k + 1), 0, w - 1)
+    g = s[:, far] + 3 * s[:, k]
+    dy = np.arange(2 * h)
+    ky = dy // 2
+    fary = np.clip(np.where(dy % 2 == 0, ky - 1, ky + 1), 0, h - 1)
+    return (((3 * g[ky]) // 4 + g[fary] // 4 + 2) >> 2).astype(np.uint8)
+
+
+def np_nearest2x_u8(frame: np.ndarray) -> np.ndarray:
+    """cv2.resize INTER_NEAREST (source index floor(d / 2)) and INTER_AREA (enlarging by an integer ratio: OpenCV's
+    area-mode bilinear has every fraction 0) at the exact 2x ratio: pixel replication (basic_upscaler_fallback.py:55-56)."""
+    return np.repeat(np.repeat(frame, 2, axis=0), 2, axis=1)
 
 
 LANCZOS4_TAPS_Q11 = {0.25: (-31, 114, -312, 1830, 579, -188, 64, -8), 0.75: (-8, 64, -188, 579, 1830, -312, 114, -31)}

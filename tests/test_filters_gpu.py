@@ -107,6 +107,76 @@ def test_whole_frame_pipeline_matches_reference_body(lanczos, cubic, name):
         assert g.shape == (128, 192, 3)
 
 
+CV_FLAGS = {"NEAREST": cv2.INTER_NEAREST, "LINEAR": cv2.INTER_LINEAR, "CUBIC": cv2.INTER_CUBIC, "AREA": cv2.INTER_AREA,
+            "LANCZOS": cv2.INTER_LANCZOS4}
+
+
+@pytest.mark.parametrize("h,w", SHAPES + [(5, 1), (1, 7), (33, 64)])
+def test_resize2x_linear_nearest_area_bit_exact(cubic, h, w):
+    """vex_resize2x_u8 with OpenCV's own flag values against cv2.resize (basic_upscaler_fallback.py:51-57,120) and the
+    integer restatements: NEAREST / LINEAR / AREA / LANCZOS4 bit-exact, CUBIC within 1 LSB; odd widths take the
+    byte-store kernel, even widths the word-store one."""
+    fr = frames_for(h, w, seed=h * 131 + w) + [(np.indices((h, w)).sum(0) % 2 * 255).astype(np.uint8)[..., None].repeat(3, 2)]
+    x = torch.from_numpy(np.stack(fr)).cuda()
+    for name, flag in CV_FLAGS.items():
+        assert int(flag) == B200BasicUpscaler.CV_INTERPOLATION[name]
+        got = call(cubic, "vex_resize2x_u8", x, int(flag), out_scale=2)
+        for g, f in zip(got, fr):
+            want = cv2.resize(f, (2 * w, 2 * h), interpolation=flag)
+            if name == "CUBIC":
+                assert np.abs(g.astype(int) - want.astype(int)).max() <= 1, (name, h, w)
+            else:
+                assert np.array_equal(g, want), (name, h, w)
+            if name == "LINEAR":
+                assert np.array_equal(g, O.np_linear2x_u8(f))
+            if name in ("NEAREST", "AREA"):
+                assert np.array_equal(g, O.np_nearest2x_u8(f))
+
+
+def test_resize2x_rejects_unknown_flag_and_unaligned_output_is_correct(cubic):
+    e = cubic._enh
+    e._ensure_ctx()
+    x = torch.zeros((1, 4, 4, 3), dtype=torch.uint8, device="cuda")
+    y = torch.empty((1, 8, 8, 3), dtype=torch.uint8, device="cuda")
+    rc = e._lib.vex_resize2x_u8(e._ctx, x.data_ptr(), y.data_ptr(), 1, 4, 4, 7, torch.cuda.current_stream().cuda_stream)
+    assert rc < 0 and "interpolation" in e._lib.vex_last_error(e._ctx).decode()
+    # an output buffer that is not word-aligned (a view one byte into an allocation) must take the byte-store path
+    rng = np.random.default_rng(3)
+    f = synth.random_frame(6, 8, rng)
+    xin = torch.from_numpy(f[None]).cuda()
+    buf = torch.zeros(12 * 16 * 3 + 8, dtype=torch.uint8, device="cuda")
+    rc = e._lib.vex_resize2x_u8(e._ctx, xin.data_ptr(), buf.data_ptr() + 1, 1, 6, 8, 1, torch.cuda.current_stream().cuda_stream)
+    _lib.check(e._ctx, rc, "vex_resize2x_u8")
+    got = buf[1:1 + 12 * 16 * 3].cpu().numpy().reshape(12, 16, 3)
+    assert np.array_equal(got, cv2.resize(f, (16, 12), interpolation=cv2.INTER_LINEAR))
+    assert int(buf[0]) == 0 and int(buf[1 + 12 * 16 * 3:].max()) == 0
+
+
+@pytest.mark.parametrize("name", ["LINEAR", "AREA", "NEAREST"])
+def test_remaining_modes_pipeline_matches_reference_body(name):
+    """The whole per-frame body of the reference for the three modes added last (resize -> 0.1-scaled sharpen -> clip)."""
+    u = B200BasicUpscaler(device="cuda:0", model_name=name)
+    try:
+        rng = np.random.default_rng(11)
+        fr = [synth.demo_frame(3, size=(96, 64), rng=rng, bgr=True), synth.random_frame(64, 96, rng), synth.edges_frame(64, 96, rng)]
+        for g, f in zip(u.enhance_frames(fr), fr):
+            want = O.ref_basic_upscaler_frame(f, name)
+            d = np.abs(g.astype(int) - want.astype(int))
+            assert g.shape == (128, 192, 3) and d.max() <= 1 and (d > 0).mean() <= 0.01, (name, int(d.max()))
+    finally:
+        u.close()
+
+
+def test_resize2x_1080p_full_size(cubic):
+    rng = np.random.default_rng(9)
+    f = synth.edges_frame(1080, 1920, rng)
+    x = torch.from_numpy(np.stack([f, synth.random_frame(1080, 1920, rng)])).cuda()
+    for flag in (cv2.INTER_LINEAR, cv2.INTER_NEAREST, cv2.INTER_AREA):
+        got = call(cubic, "vex_resize2x_u8", x, int(flag), out_scale=2)
+        for i in range(2):
+            assert np.array_equal(got[i], cv2.resize(x[i].cpu().numpy(), (3840, 2160), interpolation=flag))
+
+
 def test_1080p_full_size(lanczos):
     rng = np.random.default_rng(7)
     f = synth.edges_frame(1080, 1920, rng)
@@ -138,4 +208,4 @@ def test_video_and_info(tmp_path, cubic):
     with pytest.raises(ValueError, match="Could not open video"):
         cubic.enhance_video(str(tmp_path / "missing.mp4"), str(tmp_path / "x.mp4"))
     with pytest.raises(ValueError):
-        B200BasicUpscaler(model_name="NEAREST")
+        B200BasicUpscaler(model_name="NEAREST", scale=4)

@@ -131,16 +131,16 @@ def test_synth_generators_are_deterministic():
 
 
 def test_basic_upscaler_twin_constructor_semantics():
-    """basic_upscaler_fallback.py:45-62: (device, model_name, scale) order, unknown names fall back to Lanczos; modes without
-    a kernel are refused instead of silently running on the CPU.  No CUDA is touched before the first frame."""
+    """basic_upscaler_fallback.py:45-62: (device, model_name, scale) order, unknown names fall back to Lanczos; all five
+    interpolation names of the reference's table (:51-57) map to a kernel.  No CUDA is touched before the first frame."""
     import inspect
     from video_enhancer_proto_b200.basic_upscaler import B200BasicUpscaler, SHARPEN_KERNEL
     assert list(inspect.signature(B200BasicUpscaler.__init__).parameters)[1:4] == ["device", "model_name", "scale"]
     assert B200BasicUpscaler(model_name="cubic").method == "CUBIC"
     assert B200BasicUpscaler(model_name="something-else").method == "LANCZOS"
     for name in ("LINEAR", "area", "NEAREST"):
-        with pytest.raises(ValueError):
-            B200BasicUpscaler(model_name=name)
+        assert B200BasicUpscaler(model_name=name).method == name.upper()
+    assert B200BasicUpscaler.CV_INTERPOLATION == {"NEAREST": 0, "LINEAR": 1, "CUBIC": 2, "AREA": 3, "LANCZOS": 4}
     with pytest.raises(ValueError):
         B200BasicUpscaler(scale=4)
     info = B200BasicUpscaler(model_name="LANCZOS").get_model_info()

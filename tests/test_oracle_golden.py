@@ -94,3 +94,17 @@ def test_lanczos4_restatement_matches_opencv():
         img = rng.integers(0, 256, shape, dtype=np.uint8)
         want = cv2.resize(img, (shape[1] * 2, shape[0] * 2), interpolation=cv2.INTER_LANCZOS4)
         assert np.array_equal(O.np_lanczos4_2x_u8(img), want), shape
+
+
+def test_linear_nearest_area_restatements_match_opencv():
+    """the remaining BasicUpscalerFallback modes (basic_upscaler_fallback.py:54-56) - the integer
+    restatements the CUDA kernel follows against cv2 itself, bit-exact, incl. 1-px-wide / 1-px-high and odd shapes."""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(0)
+    for h, w in ((1, 1), (1, 7), (5, 1), (2, 2), (37, 53), (64, 96), (360, 480)):
+        for img in (rng.integers(0, 256, (h, w, 3), dtype=np.uint8), np.full((h, w, 3), 255, np.uint8),
+                    (np.indices((h, w)).sum(0) % 2 * 255).astype(np.uint8)[..., None].repeat(3, 2)):
+            size = (2 * w, 2 * h)
+            assert np.array_equal(O.np_linear2x_u8(img), cv2.resize(img, size, interpolation=cv2.INTER_LINEAR)), (h, w)
+            assert np.array_equal(O.np_nearest2x_u8(img), cv2.resize(img, size, interpolation=cv2.INTER_NEAREST)), (h, w)
+            assert np.array_equal(O.np_nearest2x_u8(img), cv2.resize(img, size, interpolation=cv2.INTER_AREA)), (h, w)

@@ -23,6 +23,10 @@ stages = {
                            lambda f: cv2.bilateralFilter(f, 5, 50, 50), lambda: y1[0], pool[0]),
     "lanczos4 2x (1080p->2160p)": (lambda: e._lib.vex_lanczos4_2x_u8(e._ctx, x.data_ptr(), x2.data_ptr(), N, H, W, st), 15 * H * W,
                                    lambda f: cv2.resize(f, (2 * W, 2 * H), interpolation=cv2.INTER_LANCZOS4), lambda: x2[0], pool[0]),
+    "linear 2x (1080p->2160p)": (lambda: e._lib.vex_resize2x_u8(e._ctx, x.data_ptr(), x2.data_ptr(), N, H, W, 1, st), 15 * H * W,
+                                 lambda f: cv2.resize(f, (2 * W, 2 * H), interpolation=cv2.INTER_LINEAR), lambda: x2[0], pool[0]),
+    "nearest/area 2x (1080p->2160p)": (lambda: e._lib.vex_resize2x_u8(e._ctx, x.data_ptr(), x2.data_ptr(), N, H, W, 0, st), 15 * H * W,
+                                       lambda f: cv2.resize(f, (2 * W, 2 * H), interpolation=cv2.INTER_NEAREST), lambda: x2[0], pool[0]),
 }
 out = {}
 for name, (fn, bytes_per_frame, cpu, result, src) in stages.items():

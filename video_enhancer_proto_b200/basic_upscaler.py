@@ -8,7 +8,7 @@ Same constructor order, ``enhance_video`` contract and ``get_model_info`` keys; 
 
 The reference's sharpening kernel sums to 0.1, not 1 (``kernel * 0.1`` scales the centre tap too), so its output is the
 sharpened image at a tenth of the brightness; that is what the reference writes and what is reproduced here.
-LINEAR / AREA / NEAREST have no kernel in this build and are refused (no CPU fallback).
+    LINEAR / AREA / NEAREST:  cv2.resize(INTER_*) = vex_resize2x_u8 (bit-exact)       -> cv2.filter2D(0.1 * sharpen) -> clip
 """
 from __future__ import annotations
 
@@ -31,14 +31,13 @@ BILATERAL_ARGS = (5, 50.0, 50.0)            # basic_upscaler_fallback.py:117
 
 
 class B200BasicUpscaler:
-    SUPPORTED = ("LANCZOS", "CUBIC")
+    SUPPORTED = ("LANCZOS", "CUBIC", "LINEAR", "AREA", "NEAREST")          # basic_upscaler_fallback.py:51-57
+    CV_INTERPOLATION = {"NEAREST": 0, "LINEAR": 1, "CUBIC": 2, "AREA": 3, "LANCZOS": 4}   # cv2.INTER_* values
 
     def __init__(self, device: str = "cuda", model_name: str = "LANCZOS", scale: int = 2, batch_size: int = 8):
         if scale != 2:
             raise ValueError("B200BasicUpscaler implements the 2x ratio the application uses")
         name = model_name.upper()
-        if name in ("LINEAR", "AREA", "NEAREST"):
-            raise ValueError(f"{model_name}: no B200 kernel in this build (LANCZOS and CUBIC only)")
         # unknown names fall back to Lanczos like the reference's dict.get default (basic_upscaler_fallback.py:59-62)
         self.method = name if name in self.SUPPORTED else "LANCZOS"
         self.device = device
@@ -67,8 +66,12 @@ class B200BasicUpscaler:
                                                   BILATERAL_ARGS[2], st), "vex_bilateral5_u8")
             up = torch.empty((n, 2 * h, 2 * w, 3), dtype=torch.uint8, device=x.device)
             _lib.check(ctx, lib.vex_lanczos4_2x_u8(ctx, den.data_ptr(), up.data_ptr(), n, h, w, st), "vex_lanczos4_2x_u8")
-        else:
+        elif self.method == "CUBIC":
             up = e.upscale_device(x, mode="bicubic", round_mode=1)          # cv2.resize INTER_CUBIC rounds to nearest
+        else:                                                               # LINEAR / AREA / NEAREST (:54-56)
+            up = torch.empty((n, 2 * h, 2 * w, 3), dtype=torch.uint8, device=x.device)
+            _lib.check(ctx, lib.vex_resize2x_u8(ctx, x.data_ptr(), up.data_ptr(), n, h, w,
+                                                self.CV_INTERPOLATION[self.method], st), "vex_resize2x_u8")
         if not sharpen:
             return up
         out = torch.empty_like(up)

@@ -311,4 +311,100 @@ int launch_lanczos4_2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int
   return VEX_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// cv2.resize(frame, (2w, 2h), INTER_LINEAR / INTER_NEAREST / INTER_AREA) for 8-bit images
+// (basic_upscaler_fallback.py:52-57,120).  At the exact ratio 2 OpenCV's 11-bit fixed-point bilinear path reduces to
+//   g(r, dx)  = src[r][far(dx)] + 3 * src[r][near(dx)]            (H pass: (512*far + 1536*near) >> 4 = 32 g)
+//   out(dy,dx) = ((3 * g(near(dy)) >> 2) + (g(far(dy)) >> 2) + 2) >> 2   (V pass: mul-high by 1536 / 512, rounding shift)
+// with near(d) = d >> 1, far(d) = near -+ 1 (d even / odd) clamped to the image (replicate border); the two truncating
+// shifts are OpenCV's.  INTER_AREA enlarging by an integer ratio has all fractions 0 and INTER_NEAREST takes floor(d / 2):
+// both replicate pixels.  One thread = one 4-byte output word column of RZ_ROWS source rows (a sliding window of g).
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int RZ_ROWS = 8;
+constexpr int RZ_THREADS = 128;
+
+template <bool LINEAR, bool WORDS>
+__global__ void __launch_bounds__(RZ_THREADS) resize2x_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out,
+                                                              int h, int w) {
+  const int row_in = 3 * w, row_out = 6 * w;
+  const int j = blockIdx.x * RZ_THREADS + threadIdx.x;            // output word column
+  if (4 * j >= row_out) return;
+  const int y0 = blockIdx.y * RZ_ROWS, y1 = min(h, y0 + RZ_ROWS);
+  const uint8_t* src = in + (size_t)blockIdx.z * h * row_in;
+  uint8_t* dst = out + (size_t)blockIdx.z * 2 * h * row_out;
+
+  int near_b[4], far_b[4], nvalid = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int ob = min(4 * j + i, row_out - 1);
+    nvalid += (4 * j + i < row_out);
+    const int dx = ob / 3, c = ob - 3 * dx, k = dx >> 1;
+    const int kf = (dx & 1) ? min(k + 1, w - 1) : max(k - 1, 0);
+    near_b[i] = 3 * k + c;
+    far_b[i] = 3 * kf + c;
+  }
+  auto emit = [&](int dy, const int (&v)[4]) {
+    uint8_t* d = dst + (size_t)dy * row_out + 4 * j;
+    if (WORDS) {
+      *reinterpret_cast<uint32_t*>(d) = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) | ((uint32_t)v[3] << 24);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if (i < nvalid) d[i] = (uint8_t)v[i];
+    }
+  };
+  if (!LINEAR) {
+    for (int y = y0; y < y1; ++y) {
+      const uint8_t* r = src + (size_t)y * row_in;
+      int v[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) v[i] = __ldg(r + near_b[i]);
+      emit(2 * y, v);
+      emit(2 * y + 1, v);
+    }
+    return;
+  }
+  auto grow = [&](int y, int (&g)[4]) {
+    const uint8_t* r = src + (size_t)y * row_in;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) g[i] = (int)__ldg(r + far_b[i]) + 3 * (int)__ldg(r + near_b[i]);
+  };
+  int gp[4], gc[4], gn[4];
+  grow(max(y0 - 1, 0), gp);
+  grow(y0, gc);
+  for (int y = y0; y < y1; ++y) {
+    grow(min(y + 1, h - 1), gn);
+    int top[4], bot[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int m = (3 * gc[i]) >> 2;
+      top[i] = (m + (gp[i] >> 2) + 2) >> 2;
+      bot[i] = (m + (gn[i] >> 2) + 2) >> 2;
+      gp[i] = gc[i];
+      gc[i] = gn[i];
+    }
+    emit(2 * y, top);
+    emit(2 * y + 1, bot);
+  }
+}
+
+int launch_resize2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, int linear, cudaStream_t s) {
+  if (!in || !out || n <= 0 || h <= 0 || w <= 0) return fail(ctx, VEX_ERR_INVALID, "vex_resize2x_u8: bad argument");
+  const int words = (6 * w + 3) / 4;
+  dim3 grid((words + RZ_THREADS - 1) / RZ_THREADS, (h + RZ_ROWS - 1) / RZ_ROWS, n);
+  if (grid.y > 65535 || grid.z > 65535) return fail(ctx, VEX_ERR_INVALID, "vex_resize2x_u8: frame or batch too large");
+  // 6w bytes per output row: rows stay word-aligned iff w is even (cudaMalloc'd frames; checked for sub-buffers)
+  const bool word_ok = (w % 2 == 0) && (reinterpret_cast<uintptr_t>(out) % 4 == 0);
+  if (linear) {
+    if (word_ok) resize2x_kernel<true, true><<<grid, RZ_THREADS, 0, s>>>(in, out, h, w);
+    else resize2x_kernel<true, false><<<grid, RZ_THREADS, 0, s>>>(in, out, h, w);
+  } else {
+    if (word_ok) resize2x_kernel<false, true><<<grid, RZ_THREADS, 0, s>>>(in, out, h, w);
+    else resize2x_kernel<false, false><<<grid, RZ_THREADS, 0, s>>>(in, out, h, w);
+  }
+  ctx->launches++;
+  VEX_CUDA(ctx, cudaGetLastError());
+  return VEX_OK;
+}
+
 }  // namespace vex

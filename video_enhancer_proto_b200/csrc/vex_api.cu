@@ -115,6 +115,21 @@ int vex_lanczos4_2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, in
   return vex::launch_lanczos4_2x(ctx, in_hwc, out_hwc, n, h, w, (cudaStream_t)stream);
 }
 
+int vex_resize2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w, int interpolation,
+                    void* stream) {
+  if (!ctx) return VEX_ERR_INVALID;
+  VEX_CUDA(ctx, cudaSetDevice(ctx->device));
+  switch (interpolation) {                     // OpenCV's InterpolationFlags values
+    case 0: case 3: return vex::launch_resize2x(ctx, in_hwc, out_hwc, n, h, w, 0, (cudaStream_t)stream);
+    case 1: return vex::launch_resize2x(ctx, in_hwc, out_hwc, n, h, w, 1, (cudaStream_t)stream);
+    case 2: return vex::launch_bicubic2x(ctx, in_hwc, out_hwc, n, h, w, 1, (cudaStream_t)stream);
+    case 4: return vex::launch_lanczos4_2x(ctx, in_hwc, out_hwc, n, h, w, (cudaStream_t)stream);
+    default: break;
+  }
+  return vex::fail(ctx, VEX_ERR_INVALID,
+                   "vex_resize2x_u8: interpolation must be 0 (NEAREST), 1 (LINEAR), 2 (CUBIC), 3 (AREA) or 4 (LANCZOS4)");
+}
+
 int vex_bilateral5_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w, float sigma_color,
                       float sigma_space, void* stream) {
   if (!ctx) return VEX_ERR_INVALID;

@@ -17,6 +17,7 @@ int launch_filter3x3(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h
 int launch_bilateral5(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, float sigma_color,
                       float sigma_space, cudaStream_t s);
 int launch_lanczos4_2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, cudaStream_t s);
+int launch_resize2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, int linear, cudaStream_t s);
 
 // cnn.cu
 

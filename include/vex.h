@@ -163,7 +163,7 @@ int vex_upscale_host(vex_ctx* ctx, int mode, const uint8_t* in_host, uint8_t* ou
 int vex_kernel_launches(const vex_ctx* ctx, unsigned long long* out);
 
 /* Knobs: "profile" (0/1), "conv3_bn" (128/256: Cout block of conv3), "ws_budget_mb" (activation
- * workspace cap; larger batches run as sub-batches), "desc_base_offset", "force_generic_bicubic"
+ * workspace cap; larger batches run as sub-batches), "desc_base_offset", "force_generic_bicubic", "force_generic_resize"
  * (bring-up).  Returns the previous value, or a negative vex_status. */
 int vex_set_option(vex_ctx* ctx, const char* name, int value);
 

@@ -167,6 +167,27 @@ def test_remaining_modes_pipeline_matches_reference_body(name):
         u.close()
 
 
+@pytest.mark.parametrize("h,w", [(1, 4), (2, 8), (17, 12), (9, 516), (64, 96)])
+def test_resize2x_word_kernel_matches_byte_kernel(cubic, h, w):
+    """w % 4 == 0 takes the packed 4-pixel kernel (one unit = first and last at w = 4); option force_generic_resize runs
+    the byte-indexed kernel on the same input: identical, and both equal cv2."""
+    e = cubic._enh
+    e._ensure_ctx()
+    rng = np.random.default_rng(h * 1000 + w)
+    fr = [synth.random_frame(h, w, rng), synth.edges_frame(h, w, rng), np.full((h, w, 3), 255, np.uint8)]
+    x = torch.from_numpy(np.stack(fr)).cuda()
+    for flag in (cv2.INTER_LINEAR, cv2.INTER_NEAREST, cv2.INTER_AREA):
+        fast = call(cubic, "vex_resize2x_u8", x, int(flag), out_scale=2)
+        prev = e._lib.vex_set_option(e._ctx, b"force_generic_resize", 1)
+        try:
+            slow = call(cubic, "vex_resize2x_u8", x, int(flag), out_scale=2)
+        finally:
+            e._lib.vex_set_option(e._ctx, b"force_generic_resize", max(prev, 0))
+        assert np.array_equal(fast, slow), (h, w, flag)
+        for g, f in zip(fast, fr):
+            assert np.array_equal(g, cv2.resize(f, (2 * w, 2 * h), interpolation=flag)), (h, w, flag)
+
+
 def test_resize2x_1080p_full_size(cubic):
     rng = np.random.default_rng(9)
     f = synth.edges_frame(1080, 1920, rng)

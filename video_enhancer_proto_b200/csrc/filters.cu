@@ -388,6 +388,127 @@ __global__ void __launch_bounds__(RZ_THREADS) resize2x_kernel(const uint8_t* __r
   }
 }
 
+// Fast path (w % 4 == 0, word-aligned frames): one thread = 4 source pixels (3 words + one halo word each side) x RZ_ROWS
+// source rows -> 8 output pixels (24 bytes = three 8-byte stores) x 2*RZ_ROWS rows.  All arithmetic runs on two 16-bit
+// lanes per register (g <= 1020, 3g <= 3060: no carries between lanes), bytes are moved with PRMT only:
+//   e[-4..15] = the 5 words; A/B = byte pairs (e[i], e[i+1]) at even / odd i; gE = 3A + B(i-3), gO = 3A + B(i+3)
+//   G[j] = the g pair of output bytes (2j, 2j+1); vertical pass per G register; one PRMT packs four results.
+__host__ __device__ constexpr int rz_src(int ob) { return 3 * ((ob / 3) >> 1) + ob % 3; }   // near source byte of output byte
+__host__ __device__ constexpr int rz_odd(int ob) { return (ob / 3) & 1; }                    // output pixel parity
+
+__device__ __forceinline__ uint32_t rz_pair16(const uint32_t (&X)[5], int i) {               // e[i] | e[i+1] << 16
+  const int p = i + 4, wa = p >> 2, ba = p & 3;
+  if (ba < 3) return __byte_perm(X[wa], 0u, (uint32_t)(ba | 0x40 | ((ba + 1) << 8) | 0x4000));
+  return __byte_perm(X[wa], X[wa + 1], 0x0403u) & 0x00FF00FFu;
+}
+
+template <bool LINEAR>
+__global__ void __launch_bounds__(RZ_THREADS) resize2x_px4_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out,
+                                                                  int h, int w) {
+  const int units = w >> 2;
+  const int u = blockIdx.x * RZ_THREADS + threadIdx.x;
+  if (u >= units) return;
+  const int row_in = 3 * w, row_out = 6 * w;
+  const int y0 = blockIdx.y * RZ_ROWS, y1 = min(h, y0 + RZ_ROWS);
+  const uint8_t* src = in + (size_t)blockIdx.z * h * row_in + 12 * u;
+  uint8_t* dst = out + (size_t)blockIdx.z * 2 * h * row_out + 24 * u;
+  const bool first = (u == 0), last = (u == units - 1);
+
+  auto load_words = [&](int y, uint32_t (&X)[5]) {
+    const uint32_t* r = reinterpret_cast<const uint32_t*>(src + (size_t)y * row_in);
+    X[1] = __ldg(r);
+    X[2] = __ldg(r + 1);
+    X[3] = __ldg(r + 2);
+    if (LINEAR) {
+      X[0] = first ? (X[1] << 8) : __ldg(r - 1);      // e[-3..-1]: left neighbour pixel, replicated at the border
+      X[4] = last ? (X[3] >> 8) : __ldg(r + 3);       // e[12..14]: right neighbour pixel
+    } else {
+      X[0] = 0u;
+      X[4] = 0u;
+    }
+  };
+  auto store_row = [&](int dy, const uint32_t (&o)[6]) {
+    uint2* d = reinterpret_cast<uint2*>(dst + (size_t)dy * row_out);
+    d[0] = make_uint2(o[0], o[1]);
+    d[1] = make_uint2(o[2], o[3]);
+    d[2] = make_uint2(o[4], o[5]);
+  };
+
+  if (!LINEAR) {
+    for (int y = y0; y < y1; ++y) {
+      uint32_t X[5], o[6];
+      load_words(y, X);
+#pragma unroll
+      for (int q = 0; q < 6; ++q) {
+        int wb = 5;                                     // lowest word any of the four source bytes lies in (they span <= 2)
+#pragma unroll
+        for (int t = 0; t < 4; ++t) wb = min(wb, (rz_src(4 * q + t) + 4) >> 2);
+        uint32_t sel = 0;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const int p = rz_src(4 * q + t) + 4;
+          sel |= (uint32_t)(((p >> 2) - wb) * 4 + (p & 3)) << (4 * t);
+        }
+        o[q] = __byte_perm(X[wb], X[wb + 1], sel);
+      }
+      store_row(2 * y, o);
+      store_row(2 * y + 1, o);
+    }
+    return;
+  }
+
+  auto load_g = [&](int y, uint32_t (&G)[12]) {
+    uint32_t X[5], A[6], B[9], gE[6], gO[6];
+    load_words(y, X);
+#pragma unroll
+    for (int p = 0; p < 6; ++p) A[p] = rz_pair16(X, 2 * p);
+#pragma unroll
+    for (int m = 0; m < 9; ++m) B[m] = rz_pair16(X, 2 * m - 3);
+#pragma unroll
+    for (int p = 0; p < 6; ++p) {
+      gE[p] = 3u * A[p] + B[p];
+      gO[p] = 3u * A[p] + B[p + 3];
+    }
+#pragma unroll
+    for (int j = 0; j < 12; ++j) {
+      const int i0 = rz_src(2 * j), i1 = rz_src(2 * j + 1);
+      const uint32_t ra = rz_odd(2 * j) ? gO[i0 >> 1] : gE[i0 >> 1];
+      const uint32_t rb = rz_odd(2 * j + 1) ? gO[i1 >> 1] : gE[i1 >> 1];
+      const uint32_t la = 2 * (i0 & 1), lb = 4 + 2 * (i1 & 1);
+      G[j] = __byte_perm(ra, rb, la | ((la + 1) << 4) | (lb << 8) | ((lb + 1) << 12));
+    }
+  };
+
+  constexpr uint32_t MASK = 0x3FFF3FFFu, HALF = 0x00020002u;
+  uint32_t Qp[12], Gc[12], Gn[12];
+  load_g(max(y0 - 1, 0), Qp);
+#pragma unroll
+  for (int j = 0; j < 12; ++j) Qp[j] = (Qp[j] >> 2) & MASK;
+  load_g(y0, Gc);
+  for (int y = y0; y < y1; ++y) {
+    load_g(min(y + 1, h - 1), Gn);
+    uint32_t top[12], bot[12];
+#pragma unroll
+    for (int j = 0; j < 12; ++j) {
+      // the low lane of m carries two stray bits (14, 15) from the high lane; with the masked q they cannot carry out,
+      // and PRMT below only takes bits 0..7 of each lane
+      const uint32_t m = (3u * Gc[j]) >> 2;
+      const uint32_t qn = (Gn[j] >> 2) & MASK;
+      top[j] = (m + Qp[j] + HALF) >> 2;
+      bot[j] = (m + qn + HALF) >> 2;
+      Qp[j] = (Gc[j] >> 2) & MASK;
+      Gc[j] = Gn[j];
+    }
+    uint32_t o[6];
+#pragma unroll
+    for (int q = 0; q < 6; ++q) o[q] = __byte_perm(top[2 * q], top[2 * q + 1], 0x6420u);
+    store_row(2 * y, o);
+#pragma unroll
+    for (int q = 0; q < 6; ++q) o[q] = __byte_perm(bot[2 * q], bot[2 * q + 1], 0x6420u);
+    store_row(2 * y + 1, o);
+  }
+}
+
 int launch_resize2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, int linear, cudaStream_t s) {
   if (!in || !out || n <= 0 || h <= 0 || w <= 0) return fail(ctx, VEX_ERR_INVALID, "vex_resize2x_u8: bad argument");
   const int words = (6 * w + 3) / 4;
@@ -395,6 +516,15 @@ int launch_resize2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h,
   if (grid.y > 65535 || grid.z > 65535) return fail(ctx, VEX_ERR_INVALID, "vex_resize2x_u8: frame or batch too large");
   // 6w bytes per output row: rows stay word-aligned iff w is even (cudaMalloc'd frames; checked for sub-buffers)
   const bool word_ok = (w % 2 == 0) && (reinterpret_cast<uintptr_t>(out) % 4 == 0);
+  if (w % 4 == 0 && reinterpret_cast<uintptr_t>(in) % 4 == 0 && reinterpret_cast<uintptr_t>(out) % 8 == 0 &&
+      !ctx->opt_force_generic_resize) {
+    dim3 g4((w / 4 + RZ_THREADS - 1) / RZ_THREADS, grid.y, n);
+    if (linear) resize2x_px4_kernel<true><<<g4, RZ_THREADS, 0, s>>>(in, out, h, w);
+    else resize2x_px4_kernel<false><<<g4, RZ_THREADS, 0, s>>>(in, out, h, w);
+    ctx->launches++;
+    VEX_CUDA(ctx, cudaGetLastError());
+    return VEX_OK;
+  }
   if (linear) {
     if (word_ok) resize2x_kernel<true, true><<<grid, RZ_THREADS, 0, s>>>(in, out, h, w);
     else resize2x_kernel<true, false><<<grid, RZ_THREADS, 0, s>>>(in, out, h, w);

@@ -261,6 +261,7 @@ int vex_set_option(vex_ctx* ctx, const char* name, int value) {
   int* slot = nullptr;
   if (!strcmp(name, "desc_base_offset")) slot = &ctx->opt_desc_base_offset;
   else if (!strcmp(name, "force_generic_bicubic")) slot = &ctx->opt_force_generic_bicubic;
+  else if (!strcmp(name, "force_generic_resize")) slot = &ctx->opt_force_generic_resize;
   else if (!strcmp(name, "bicubic_rows")) slot = &ctx->opt_bicubic_rows;
   else if (!strcmp(name, "conv_variant")) slot = &ctx->opt_conv_variant;
   else if (!strcmp(name, "thin_probe")) slot = &ctx->opt_thin_probe;

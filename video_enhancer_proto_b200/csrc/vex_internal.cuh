@@ -46,6 +46,7 @@ struct vex_ctx {
   // debug knobs (vex_set_option)
   int opt_desc_base_offset = 0;   // smem-descriptor base_offset field: 0 (measured correct on B200), 1: (addr>>7)&7
   int opt_force_generic_bicubic = 0;
+  int opt_force_generic_resize = 0;  // vex_resize2x_u8: byte-indexed kernel even when the 4-pixel word kernel applies
   int opt_thin_probe = 0;            // im2col27 timing probes (wrong results), see thin_tc.cuh
   int opt_conv_variant = 0;          // 0 = conv_tc2 (cluster pairs, double-buffered TMEM), 1 = conv_tc v1
   int max_pairs3 = 0;                // same for conv_tc3

@@ -191,10 +191,11 @@ def test_resize2x_word_kernel_matches_byte_kernel(cubic, h, w):
 def test_resize2x_1080p_full_size(cubic):
     rng = np.random.default_rng(9)
     f = synth.edges_frame(1080, 1920, rng)
-    x = torch.from_numpy(np.stack([f, synth.random_frame(1080, 1920, rng)])).cuda()
+    # 5 frames: enough threads for the 16-row strips of the word kernel (smaller batches take 8-row strips)
+    x = torch.from_numpy(np.stack([f, synth.random_frame(1080, 1920, rng), f[::-1].copy(), f[:, ::-1].copy(), 255 - f])).cuda()
     for flag in (cv2.INTER_LINEAR, cv2.INTER_NEAREST, cv2.INTER_AREA):
         got = call(cubic, "vex_resize2x_u8", x, int(flag), out_scale=2)
-        for i in range(2):
+        for i in range(5):
             assert np.array_equal(got[i], cv2.resize(x[i].cpu().numpy(), (3840, 2160), interpolation=flag))
 
 

@@ -72,3 +72,24 @@ def test_filter_stages_random_shapes():
             assert np.abs(lz.astype(int) - ref.astype(int)).max() <= 2, (h, w)
     finally:
         up.close()
+
+
+def test_resize2x_random_shapes_bit_exact():
+    """LINEAR / NEAREST / AREA (basic_upscaler_fallback.py:54-56) on random shapes and batch sizes against the integer
+    restatements and cv2: widths with w % 4 == 0 take the packed word kernel, the rest the byte kernel (even / odd widths)."""
+    up = B200BasicUpscaler(device="cuda:0", model_name="LINEAR")
+    try:
+        rng = np.random.default_rng(400)
+        for h, w in shapes(4, 16, 70, 160, specials=[(1, 4), (1, 1), (3, 8), (70, 4), (11, 132), (2, 1024), (9, 6), (9, 7)]):
+            n = int(rng.integers(1, 4))
+            frames = [synth.random_frame(h, w, rng) if i % 2 == 0 else synth.edges_frame(h, w, rng) for i in range(n)]
+            x = torch.from_numpy(np.stack(frames)).cuda()
+            for name, want_fn, flag in (("LINEAR", O.np_linear2x_u8, cv2.INTER_LINEAR), ("NEAREST", O.np_nearest2x_u8, cv2.INTER_NEAREST),
+                                        ("AREA", O.np_nearest2x_u8, cv2.INTER_AREA)):
+                up.method = name
+                got = up.upscale_device(x, sharpen=False).cpu().numpy()
+                for i, f in enumerate(frames):
+                    assert np.array_equal(got[i], want_fn(f)), (name, h, w, i)
+                    assert np.array_equal(got[i], cv2.resize(f, (2 * w, 2 * h), interpolation=flag)), (name, h, w, i)
+    finally:
+        up.close()

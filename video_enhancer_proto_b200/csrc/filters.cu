@@ -404,12 +404,12 @@ __device__ __forceinline__ uint32_t rz_pair16(const uint32_t (&X)[5], int i) {  
 
 template <bool LINEAR>
 __global__ void __launch_bounds__(RZ_THREADS) resize2x_px4_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out,
-                                                                  int h, int w) {
+                                                                  int h, int w, int rows, bool wide_ok) {
   const int units = w >> 2;
   const int u = blockIdx.x * RZ_THREADS + threadIdx.x;
   if (u >= units) return;
   const int row_in = 3 * w, row_out = 6 * w;
-  const int y0 = blockIdx.y * RZ_ROWS, y1 = min(h, y0 + RZ_ROWS);
+  const int y0 = blockIdx.y * rows, y1 = min(h, y0 + rows);
   const uint8_t* src = in + (size_t)blockIdx.z * h * row_in + 12 * u;
   uint8_t* dst = out + (size_t)blockIdx.z * 2 * h * row_out + 24 * u;
   const bool first = (u == 0), last = (u == units - 1);
@@ -427,11 +427,39 @@ __global__ void __launch_bounds__(RZ_THREADS) resize2x_px4_kernel(const uint8_t*
       X[4] = 0u;
     }
   };
+  // A warp's 32 x 24 output bytes of one row are contiguous: full warps stage them in shared memory and store 16 bytes per
+  // lane, fully coalesced (48 x 16 B); 8-byte stores at a 24-byte lane stride are the fall-back (partial warps, w % 8 != 0).
+  __shared__ __align__(16) uint8_t stage_all[RZ_THREADS / 32][768];
+  const int lane = threadIdx.x & 31;
+  uint8_t* stage = stage_all[threadIdx.x >> 5];
+  // LINEAR keeps the direct stores: staging cost it 16 registers (64 -> 80, 8 -> 6 blocks per SM) and 20 % (measured)
+  const bool staged = !LINEAR && wide_ok && (u - lane + 32 <= units);
+  constexpr int copies = LINEAR ? 1 : 2;            // replication writes every row twice
   auto store_row = [&](int dy, const uint32_t (&o)[6]) {
-    uint2* d = reinterpret_cast<uint2*>(dst + (size_t)dy * row_out);
-    d[0] = make_uint2(o[0], o[1]);
-    d[1] = make_uint2(o[2], o[3]);
-    d[2] = make_uint2(o[4], o[5]);
+    if (staged) {
+      uint2* sp = reinterpret_cast<uint2*>(stage + 24 * lane);
+      sp[0] = make_uint2(o[0], o[1]);
+      sp[1] = make_uint2(o[2], o[3]);
+      sp[2] = make_uint2(o[4], o[5]);
+      __syncwarp();
+      const uint4* s4 = reinterpret_cast<const uint4*>(stage);
+      const uint4 v0 = s4[lane], v1 = s4[32 + (lane & 15)];
+      __syncwarp();
+#pragma unroll
+      for (int c = 0; c < copies; ++c) {
+        uint4* d4 = reinterpret_cast<uint4*>(dst - 24 * lane + (size_t)(dy + c) * row_out);
+        d4[lane] = v0;
+        if (lane < 16) d4[32 + lane] = v1;
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < copies; ++c) {
+        uint2* d = reinterpret_cast<uint2*>(dst + (size_t)(dy + c) * row_out);
+        d[0] = make_uint2(o[0], o[1]);
+        d[1] = make_uint2(o[2], o[3]);
+        d[2] = make_uint2(o[4], o[5]);
+      }
+    }
   };
 
   if (!LINEAR) {
@@ -452,7 +480,6 @@ __global__ void __launch_bounds__(RZ_THREADS) resize2x_px4_kernel(const uint8_t*
         o[q] = __byte_perm(X[wb], X[wb + 1], sel);
       }
       store_row(2 * y, o);
-      store_row(2 * y + 1, o);
     }
     return;
   }
@@ -479,25 +506,30 @@ __global__ void __launch_bounds__(RZ_THREADS) resize2x_px4_kernel(const uint8_t*
     }
   };
 
+  // Per output pair j the state between rows is q(y-1), q(y) (alternating in Qa / Qb) and m(y), with q = (g >> 2) and
+  // m = (3g >> 2) computed once per source row.  The low lane of m carries two stray bits (14, 15) from the high lane;
+  // q is masked, so the sum cannot carry out of the lane, and PRMT below only takes bits 0..7 of each lane.
   constexpr uint32_t MASK = 0x3FFF3FFFu, HALF = 0x00020002u;
-  uint32_t Qp[12], Gc[12], Gn[12];
-  load_g(max(y0 - 1, 0), Qp);
+  uint32_t Qa[12], Qb[12], M[12], G[12];
+  load_g(max(y0 - 1, 0), G);
 #pragma unroll
-  for (int j = 0; j < 12; ++j) Qp[j] = (Qp[j] >> 2) & MASK;
-  load_g(y0, Gc);
-  for (int y = y0; y < y1; ++y) {
-    load_g(min(y + 1, h - 1), Gn);
+  for (int j = 0; j < 12; ++j) Qa[j] = (G[j] >> 2) & MASK;
+  load_g(y0, G);
+#pragma unroll
+  for (int j = 0; j < 12; ++j) {
+    Qb[j] = (G[j] >> 2) & MASK;
+    M[j] = (3u * G[j]) >> 2;
+  }
+  auto step = [&](int y, uint32_t (&qp)[12]) {      // in: qp = q(y-1), M = m(y); out: qp = q(y+1), M = m(y+1)
+    load_g(min(y + 1, h - 1), G);
     uint32_t top[12], bot[12];
 #pragma unroll
     for (int j = 0; j < 12; ++j) {
-      // the low lane of m carries two stray bits (14, 15) from the high lane; with the masked q they cannot carry out,
-      // and PRMT below only takes bits 0..7 of each lane
-      const uint32_t m = (3u * Gc[j]) >> 2;
-      const uint32_t qn = (Gn[j] >> 2) & MASK;
-      top[j] = (m + Qp[j] + HALF) >> 2;
-      bot[j] = (m + qn + HALF) >> 2;
-      Qp[j] = (Gc[j] >> 2) & MASK;
-      Gc[j] = Gn[j];
+      const uint32_t qn = (G[j] >> 2) & MASK;
+      top[j] = (M[j] + qp[j] + HALF) >> 2;
+      bot[j] = (M[j] + qn + HALF) >> 2;
+      qp[j] = qn;
+      M[j] = (3u * G[j]) >> 2;
     }
     uint32_t o[6];
 #pragma unroll
@@ -506,6 +538,10 @@ __global__ void __launch_bounds__(RZ_THREADS) resize2x_px4_kernel(const uint8_t*
 #pragma unroll
     for (int q = 0; q < 6; ++q) o[q] = __byte_perm(bot[2 * q], bot[2 * q + 1], 0x6420u);
     store_row(2 * y + 1, o);
+  };
+  for (int y = y0; y < y1; y += 2) {
+    step(y, Qa);
+    if (y + 1 < y1) step(y + 1, Qb);
   }
 }
 
@@ -518,9 +554,13 @@ int launch_resize2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h,
   const bool word_ok = (w % 2 == 0) && (reinterpret_cast<uintptr_t>(out) % 4 == 0);
   if (w % 4 == 0 && reinterpret_cast<uintptr_t>(in) % 4 == 0 && reinterpret_cast<uintptr_t>(out) % 8 == 0 &&
       !ctx->opt_force_generic_resize) {
-    dim3 g4((w / 4 + RZ_THREADS - 1) / RZ_THREADS, grid.y, n);
-    if (linear) resize2x_px4_kernel<true><<<g4, RZ_THREADS, 0, s>>>(in, out, h, w);
-    else resize2x_px4_kernel<false><<<g4, RZ_THREADS, 0, s>>>(in, out, h, w);
+    // the H pass of the rows above and below a strip is recomputed (2 extra rows per strip): 16-row strips when there are
+    // enough threads to fill the SMs several times over, 8-row strips otherwise
+    const int rows = ((long long)n * (h / 16 + 1) * (w / 4) >= 64LL * 2048 * ctx->sm_count / 148) ? 16 : RZ_ROWS;
+    dim3 g4((w / 4 + RZ_THREADS - 1) / RZ_THREADS, (h + rows - 1) / rows, n);
+    const bool wide_ok = (w % 8 == 0) && (reinterpret_cast<uintptr_t>(out) % 16 == 0);   // 16-byte aligned output rows
+    if (linear) resize2x_px4_kernel<true><<<g4, RZ_THREADS, 0, s>>>(in, out, h, w, rows, wide_ok);
+    else resize2x_px4_kernel<false><<<g4, RZ_THREADS, 0, s>>>(in, out, h, w, rows, wide_ok);
     ctx->launches++;
     VEX_CUDA(ctx, cudaGetLastError());
     return VEX_OK;

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define VEX_ABI_VERSION 1
+#define VEX_ABI_VERSION 2
 
 typedef enum vex_status {
   VEX_OK = 0,
@@ -47,6 +47,9 @@ int vex_destroy(vex_ctx* ctx);
 /* Owned by ctx, valid until the next call on ctx.  ctx may be NULL (returns the create error). */
 const char* vex_last_error(const vex_ctx* ctx);
 int vex_abi_version(void);
+/* "vex-src:<sha256 of the sources the library was compiled from> sm_100a[ probes]" (static string).  The Python binding
+ * compares the hash with the sources it sits next to, so a stale prebuilt library cannot be loaded silently. */
+const char* vex_build_info(void);
 
 /* ---- bicubic fallback ------------------------------------------------------------------- */
 
@@ -123,6 +126,20 @@ int vex_cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch,
 int vex_cnn2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc,
                  int n, int h, int w, int in_bgr, int out_bgr, void* stream);
 
+/* fp32 input form of vex_cnn2x_u8 for the tensor branch of the single-frame entry (app.py:337-338: a caller may hand
+ * `_enhance_frame_with_gpu` an fp32 NCHW tensor already in [0,1], which the reference feeds to conv1 unquantised).
+ * in_nchw: n*[3][h][w] fp32 device, any real values; conv1 takes each value as a hi + lo bf16 pair (relative input error
+ * 2^-17), the weights are the same bf16 images as the uint8 path minus the 1/255 fold.  No colour swap on input (the
+ * reference does none on this branch).  out_hwc (u8, n*[2h][2w][3]) and out_nchw (fp32 pre-quantisation clamp output,
+ * n*[3][2h][2w]) may each be NULL, not both. */
+int vex_cnn2x_f32in(vex_ctx* ctx, const float* in_nchw, uint8_t* out_hwc, float* out_nchw,
+                    int n, int h, int w, int out_bgr, void* stream);
+
+/* fp32 input form of vex_bicubic2x_u8 (round_mode 0) for the tensor branch of _enhance_frame_cpu_fallback
+ * (app.py:367-376): in_nchw n*[3][h][w] fp32 in [0,1] (any real values) -> clip(bicubic*255, 0, 255) truncated,
+ * out_hwc n*[2h][2w][3] u8.  fp32 arithmetic in ATen's order (x pass inside each row, then y). */
+int vex_bicubic2x_f32in(vex_ctx* ctx, const float* in_nchw, uint8_t* out_hwc, int n, int h, int w, void* stream);
+
 /* Parity hook: same network, pre-quantisation fp32 output, NCHW [n][3][2h][2w] (device).
  * `tap` selects what is written: 0 = final clamp(upconv2) (app.py:299); 1..5 = x1..x5
  * (NCHW fp32, [n][C][h][w]; with n_extra > 0, x3 is the output of conv3 itself); 6 = relu(upconv1)
@@ -136,6 +153,12 @@ int vex_cnn2x_f32_debug(vex_ctx* ctx, const uint8_t* in_hwc, float* out_nchw,
  * the last event.  (The reference has no per-layer timing; its PerformanceTracker,
  * utils/performance_monitor.py:178, only wraps whole videos.) */
 int vex_cnn_profile_ms(vex_ctx* ctx, float* ms7);
+
+/* Per-layer device time over EVERY forward made since option "profile" was last set to 1 (bench.py's roofline uses the
+ * mean over the whole timed region, not one step): mean7 / min7 / max7 in ms per forward (sub-batches summed), same
+ * layer order as vex_cnn_profile_ms; n_forwards = forwards folded in.  Any of the three arrays may be NULL.
+ * Synchronises on the last recorded event. */
+int vex_cnn_profile_stats(vex_ctx* ctx, float* mean7, float* min7, float* max7, int* n_forwards);
 
 /* Bytes of device workspace the ctx holds (grows on demand) for a batch of this shape. */
 int vex_workspace_bytes(const vex_ctx* ctx, int n, int h, int w, size_t* out);
@@ -159,12 +182,39 @@ int vex_host_free(vex_ctx* ctx, void* p);
 int vex_upscale_host(vex_ctx* ctx, int mode, const uint8_t* in_host, uint8_t* out_host,
                      int n, int h, int w, int chunk, int flags);
 
+/* Asynchronous form of vex_upscale_host for callers that produce frames incrementally (the decoder loop of
+ * app.py:458-482): vex_submit enqueues H2D -> kernels -> D2H of ONE chunk of n frames on the ctx's copy-in / compute /
+ * copy-out streams (device slot = submit count & 1, chained by events exactly like the chunks of vex_upscale_host) and
+ * returns at once with a ticket; vex_wait blocks until that chunk's output is in out_host.  Chunks complete in submit
+ * order.  in_host must stay untouched until the chunk's H2D has run and out_host until vex_wait returns; pinned
+ * (vex_host_alloc) buffers make both copies asynchronous.  Up to 8 tickets may be outstanding; a 9th submit first
+ * waits for the oldest.  Waiting twice, or for a ticket older than the last 8, returns VEX_OK. */
+typedef unsigned long long vex_ticket;
+int vex_submit(vex_ctx* ctx, int mode, const uint8_t* in_host, uint8_t* out_host,
+               int n, int h, int w, int flags, vex_ticket* ticket);
+int vex_wait(vex_ctx* ctx, vex_ticket ticket);
+
+/* The plugin-call form (`_process_frame_batch_gpu(frames_batch)`, app.py:529-553: a Python list of separately
+ * allocated, pageable frames in): frames_in[i] points at frame i (packed u8 HWC [h][w][3], host, pageable or pinned).
+ * Frames are staged chunk by chunk into the ctx's own pinned buffers while the previous chunk computes (chunk sizes
+ * ramp 1, 2, 4, ... up to `chunk`, last chunk 1 frame, so the exposed staging / first H2D / last D2H are one frame
+ * each), outputs go to out_host (n*[2h][2w][3]; pinned memory overlaps).  Returns when every output is in out_host. */
+int vex_upscale_frames(vex_ctx* ctx, int mode, const uint8_t* const* frames_in, uint8_t* out_host,
+                       int n, int h, int w, int chunk, int flags);
+
 /* Counters for bench.py's `gpu_launches`: kernels launched by this ctx since creation. */
 int vex_kernel_launches(const vex_ctx* ctx, unsigned long long* out);
 
-/* Knobs: "profile" (0/1), "conv3_bn" (128/256: Cout block of conv3), "ws_budget_mb" (activation
- * workspace cap; larger batches run as sub-batches), "desc_base_offset", "force_generic_bicubic", "force_generic_resize"
- * (bring-up).  Returns the previous value, or a negative vex_status. */
+/* Knobs.  Returns the previous value, or a negative vex_status.
+ *   product:   "profile" (0/1: per-layer events; setting 1 clears the statistics of vex_cnn_profile_stats), "nvtx" (0/1:
+ *              one NVTX range per layer launch), "ws_budget_mb" (activation workspace cap; larger
+ *              batches run as sub-batches), "conv3_bn" (128/256: Cout block of conv3).
+ *   variants kept as bit-identity cross-checks (tests/test_cnn_gpu.py): "conv_variant" (0 = default v3 cta_group::2,
+ *              1 = single-CTA, 2 = multicast pairs), "thin_tc" (0 = fp32 CUDA-core thin layers), "fuse_tail" (0 = upconv1 /
+ *              upconv2 as two kernels with `up` in HBM), "force_generic_bicubic", "force_generic_resize", "bicubic_rows".
+ *   bring-up probes that PRODUCE WRONG RESULTS (timing experiments only; refused unless the library was built with
+ *              -DVEX_DEBUG_PROBES): "epi_variant", "thin_probe", "desc_base_offset"; "conv_dbg" prints per-role cycle
+ *              counters and synchronises. */
 int vex_set_option(vex_ctx* ctx, const char* name, int value);
 
 #ifdef __cplusplus

@@ -167,6 +167,27 @@ def test_remaining_modes_pipeline_matches_reference_body(name):
         u.close()
 
 
+def test_unknown_model_name_is_lanczos_without_the_prefilter():
+    """an unknown name falls back to INTER_LANCZOS4 for the resize only (dict.get default,
+    basic_upscaler_fallback.py:59-62); the bilateral pre-filter is gated on the NAME being 'LANCZOS' (:115-117), so it
+    must not run.  Reference body for such a name = resize LANCZOS4 -> 0.1-scaled sharpen -> clip."""
+    u = B200BasicUpscaler(device="cuda:0", model_name="something-else")
+    try:
+        assert u.method == "LANCZOS" and not u._denoise
+        rng = np.random.default_rng(12)
+        fr = [synth.random_frame(64, 96, rng), synth.edges_frame(64, 96, rng)]
+        kernel = np.array([[-1, -1, -1], [-1, 9, -1], [-1, -1, -1]], dtype=np.float32) * 0.1
+        for g, f in zip(u.enhance_frames(fr), fr):
+            up = cv2.resize(f, (192, 128), interpolation=cv2.INTER_LANCZOS4)
+            want = np.clip(cv2.filter2D(up, -1, kernel), 0, 255).astype(np.uint8)
+            with_prefilter = O.ref_basic_upscaler_frame(f, "LANCZOS")
+            d = np.abs(g.astype(int) - want.astype(int))
+            assert d.max() <= 1 and (d > 0).mean() <= 0.01, int(d.max())
+            assert np.abs(g.astype(int) - with_prefilter.astype(int)).mean() > np.abs(d).mean()
+    finally:
+        u.close()
+
+
 @pytest.mark.parametrize("h,w", [(1, 4), (2, 8), (17, 12), (9, 516), (64, 96)])
 def test_resize2x_word_kernel_matches_byte_kernel(cubic, h, w):
     """w % 4 == 0 takes the packed 4-pixel kernel (one unit = first and last at w = 4); option force_generic_resize runs

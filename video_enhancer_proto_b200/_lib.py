@@ -38,6 +38,13 @@ SIGNATURES = {
     "vex_host_alloc": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]),
     "vex_host_free": (C.c_int, [C.c_void_p, C.c_void_p]),
     "vex_upscale_host": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "vex_submit": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_ulonglong)]),
+    "vex_wait": (C.c_int, [C.c_void_p, C.c_ulonglong]),
+    "vex_upscale_frames": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "vex_cnn2x_f32in": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "vex_bicubic2x_f32in": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "vex_cnn_profile_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_int)]),
+    "vex_build_info": (C.c_char_p, []),
     "vex_kernel_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_ulonglong)]),
     "vex_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
 }
@@ -45,19 +52,40 @@ SIGNATURES = {
 _lib = None
 
 
+def _embedded_hash(path: str):
+    """The source hash build.py compiled into the library ("vex-src:<sha256>"), read from the file without loading it."""
+    try:
+        data = open(path, "rb").read()
+    except OSError:
+        return None
+    i = data.find(b"vex-src:")
+    return data[i + 8:i + 72].decode("ascii", "replace") if i >= 0 else None
+
+
 def load() -> C.CDLL:
-    """dlopen libvex.so (built in-tree by ``build.py`` / ``__graft_entry__.build``)."""
+    """dlopen libvex.so (built in-tree by ``build.py`` / ``__graft_entry__.build``).  A library whose embedded source
+    hash differs from the sources next to it is STALE: it is rebuilt when nvcc is available, otherwise loading fails
+    (a prebuilt binary must never silently stand in for different source)."""
     global _lib
     if _lib is None:
-        if not os.path.exists(LIB_PATH):
-            raise RuntimeError(
-                f"{LIB_PATH} is missing: run `python -m video_enhancer_proto_b200.build` (nvcc, sm_100a). "
-                "There is no CPU or PyTorch fallback for this path.")
+        from . import build as _build
+        want = _build.source_hash()
+        if not os.path.exists(LIB_PATH) or _embedded_hash(LIB_PATH) != want:
+            why = "missing" if not os.path.exists(LIB_PATH) else "stale (source hash mismatch)"
+            try:
+                _build.build(force=True)
+            except Exception as e:
+                raise RuntimeError(
+                    f"{LIB_PATH} is {why} and could not be rebuilt ({e}): run `python -m video_enhancer_proto_b200.build` "
+                    "(nvcc, sm_100a).  There is no CPU or PyTorch fallback for this path.") from e
         lib = C.CDLL(LIB_PATH)
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(lib, name)
             fn.restype = res
             fn.argtypes = args
+        info = lib.vex_build_info().decode()
+        if want not in info:
+            raise RuntimeError(f"{LIB_PATH}: build info {info!r} does not carry the source hash {want}")
         _lib = lib
     return _lib
 

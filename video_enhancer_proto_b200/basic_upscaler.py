@@ -40,6 +40,9 @@ class B200BasicUpscaler:
         name = model_name.upper()
         # unknown names fall back to Lanczos like the reference's dict.get default (basic_upscaler_fallback.py:59-62)
         self.method = name if name in self.SUPPORTED else "LANCZOS"
+        # the bilateral pre-filter is gated on the NAME, not on the interpolation that was picked (:115-117): an unknown
+        # name gets the Lanczos resize without denoising
+        self._denoise = name == "LANCZOS"
         self.device = device
         self.model_name = model_name
         self.scale = scale
@@ -61,9 +64,11 @@ class B200BasicUpscaler:
         n, h, w, _ = x.shape
         st = torch.cuda.current_stream(x.device).cuda_stream
         if self.method == "LANCZOS":
-            den = torch.empty_like(x)
-            _lib.check(ctx, lib.vex_bilateral5_u8(ctx, x.data_ptr(), den.data_ptr(), n, h, w, BILATERAL_ARGS[1],
-                                                  BILATERAL_ARGS[2], st), "vex_bilateral5_u8")
+            den = x
+            if self._denoise:
+                den = torch.empty_like(x)
+                _lib.check(ctx, lib.vex_bilateral5_u8(ctx, x.data_ptr(), den.data_ptr(), n, h, w, BILATERAL_ARGS[1],
+                                                      BILATERAL_ARGS[2], st), "vex_bilateral5_u8")
             up = torch.empty((n, 2 * h, 2 * w, 3), dtype=torch.uint8, device=x.device)
             _lib.check(ctx, lib.vex_lanczos4_2x_u8(ctx, den.data_ptr(), up.data_ptr(), n, h, w, st), "vex_lanczos4_2x_u8")
         elif self.method == "CUBIC":

@@ -24,12 +24,28 @@ def nvcc() -> str:
     raise RuntimeError("nvcc not found")
 
 
+def source_hash() -> str:
+    """sha256 over every file the library is compiled from (csrc/*, include/vex.h), the flags and the probe switch.
+    build() compiles it into the library as "vex-src:<hash>" (vex_build_info); _lib.load() refuses a library whose
+    hash differs from the sources it sits next to."""
+    import hashlib
+    h = hashlib.sha256()
+    files = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h")))
+    files.append(os.path.join(HERE, "..", "include", "vex.h"))
+    for f in files:
+        h.update(os.path.basename(f).encode())
+        h.update(open(f, "rb").read())
+    h.update(" ".join(FLAGS).encode())
+    h.update(b"probes" if os.environ.get("VEX_DEBUG_PROBES") == "1" else b"")
+    return h.hexdigest()
+
+
 def needs_build() -> bool:
     if not os.path.exists(LIB):
         return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "vex.h"), __file__]
-    return any(os.path.getmtime(d) > t for d in deps)
+    data = open(LIB, "rb").read()
+    i = data.find(b"vex-src:")
+    return i < 0 or data[i + 8:i + 72].decode("ascii", "replace") != source_hash()
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -39,9 +55,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
     bdir = os.path.join(HERE, "build")
     os.makedirs(bdir, exist_ok=True)
     procs = []
+    defs = [f'-DVEX_SOURCE_HASH="{source_hash()}"']
+    if os.environ.get("VEX_DEBUG_PROBES") == "1":          # wrong-result timing probes (tools/thin_probe.py, tools/conv_dbg.py)
+        defs.append("-DVEX_DEBUG_PROBES")
     for src in SOURCES:
         obj = os.path.join(bdir, src.replace(".cu", ".o"))
-        cmd = [nvcc(), *FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc(), *FLAGS, *(defs if src == "vex_api.cu" else defs[1:]), "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))

@@ -367,7 +367,52 @@ bicubic2x_generic_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ o
   }
 }
 
+// fp32 NCHW in [0,1] -> clip(bicubic * 255, 0, 255) truncated, u8 HWC: the tensor branch of app.py:367-376.  Plain fp32
+// in ATen's order (upsample_bicubic2d: cubic_interp1d along x inside each of the 4 rows, then along y; each is
+// x0*c0 + x1*c1 + x2*c2 + x3*c3 left to right, no FMA contraction).  One thread per output byte; not a throughput path.
+__global__ void __launch_bounds__(256)
+bicubic2x_f32in_kernel(const float* __restrict__ in, uint8_t* __restrict__ out, int n, int h, int w) {
+  const size_t total = (size_t)n * h * w * 12;
+  const float cw[2][4] = {{-27.f / 256.f, 225.f / 256.f, 67.f / 256.f, -9.f / 256.f},      // t = 0.25 (odd output index)
+                          {-9.f / 256.f, 67.f / 256.f, 225.f / 256.f, -27.f / 256.f}};     // t = 0.75 (even)
+  for (size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x; j < total; j += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(j % 3);
+    size_t t = j / 3;
+    const int dx = (int)(t % (2 * w)); t /= 2 * w;
+    const int dy = (int)(t % (2 * h));
+    const int img = (int)(t / (2 * h));
+    const int ix = (dx & 1) ? dx / 2 : dx / 2 - 1, iy = (dy & 1) ? dy / 2 : dy / 2 - 1;
+    const float* wx = cw[(dx & 1) ? 0 : 1];
+    const float* wy = cw[(dy & 1) ? 0 : 1];
+    const float* plane = in + ((size_t)img * 3 + c) * h * w;
+    float rows[4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+      const float* r = plane + (size_t)min(max(iy - 1 + a, 0), h - 1) * w;
+      float v = __fmul_rn(r[min(max(ix - 1, 0), w - 1)], wx[0]);
+      v = __fadd_rn(v, __fmul_rn(r[min(max(ix, 0), w - 1)], wx[1]));
+      v = __fadd_rn(v, __fmul_rn(r[min(max(ix + 1, 0), w - 1)], wx[2]));
+      v = __fadd_rn(v, __fmul_rn(r[min(max(ix + 2, 0), w - 1)], wx[3]));
+      rows[a] = v;
+    }
+    float v = __fmul_rn(rows[0], wy[0]);
+    v = __fadd_rn(v, __fmul_rn(rows[1], wy[1]));
+    v = __fadd_rn(v, __fmul_rn(rows[2], wy[2]));
+    v = __fadd_rn(v, __fmul_rn(rows[3], wy[3]));
+    out[j] = (uint8_t)__float2uint_rz(fminf(fmaxf(__fmul_rn(v, 255.0f), 0.f), 255.f));   // np.clip(x*255,0,255).astype(uint8)
+  }
+}
+
 }  // namespace
+
+int launch_bicubic2x_f32in(vex_ctx* ctx, const float* in, uint8_t* out, int n, int h, int w, cudaStream_t s) {
+  const size_t total = (size_t)n * h * w * 12;
+  const int blocks = (int)min((total + 255) / 256, (size_t)ctx->sm_count * 32);
+  bicubic2x_f32in_kernel<<<blocks, 256, 0, s>>>(in, out, n, h, w);
+  ctx->launches++;
+  VEX_CUDA(ctx, cudaGetLastError());
+  return VEX_OK;
+}
 
 int launch_bicubic2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w,
                      int round_mode, cudaStream_t s) {

@@ -10,6 +10,7 @@
 #include <string.h>
 
 #include <cuda_bf16.h>
+#include <nvtx3/nvToolsExt.h>
 
 #include "cnn_small.cuh"
 #include "conv_tc.cuh"
@@ -43,8 +44,14 @@ struct CnnPlan {
   uint8_t* ws = nullptr;
   size_t ws_bytes = 0;
   void* encode = nullptr;                    // cuTensorMapEncodeTiled, resolved through the runtime
+  uint8_t* t1wf = nullptr;                   // conv1 for fp32 input (vex_cnn2x_f32in): no 1/255 fold, weights repeated at k = 32..58 for the lo halves
   std::vector<cudaEvent_t> prof;             // option "profile": 8 events per sub-batch of the last forward
+  bool prof_folded = false;                  // the last forward is already inside the statistics
+  std::vector<std::vector<cudaEvent_t>> prof_done;   // earlier forwards not yet folded into the statistics
   std::vector<cudaEvent_t> prof_pool;
+  double prof_sum[7] = {0, 0, 0, 0, 0, 0, 0};
+  float prof_min[7] = {0, 0, 0, 0, 0, 0, 0}, prof_max[7] = {0, 0, 0, 0, 0, 0, 0};
+  int prof_n = 0;
 };
 
 namespace {
@@ -558,6 +565,21 @@ int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const*
     });
     if (rc) return rc;
   }
+  if (c1 <= 256) {   // conv1 for fp32 input: the input value arrives as hi (k < 27) + lo (k = 32..58) bf16, same weight for both
+    rc = pack_rows_sw128(ctx, &P->t1wf, c1, 1, [&](int r, int k) -> float {
+      if (k == 27 || k == 28) {
+        const uint32_t hb = (uint32_t)f32_to_bf16_rne(shift[0][r]) << 16;
+        float hi;
+        memcpy(&hi, &hb, 4);
+        return k == 27 ? hi : shift[0][r] - hi;
+      }
+      const int kk = k >= 32 ? k - 32 : k;
+      if (kk >= 27) return 0.f;
+      const int ci = kk % 3, tap = kk / 3;
+      return cw[0][((size_t)r * 3 + ci) * 9 + tap] * scale[0][r];
+    });
+    if (rc) return rc;
+  }
   {  // upconv1 as conv3x3 3 -> 4*up + PixelShuffle(2): row = phase*up + co, phase = py*2+px.
      // 3x3 tap index ky' (input row y + ky' - 1) -> transposed-conv kernel row ky:  py=0: {1->1, 0->3}, py=1: {2->0, 1->2}
     const int kmap[2][3] = {{3, 1, -1}, {-1, 2, 0}};
@@ -594,6 +616,10 @@ int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const*
 }
 
 // ------------------------------------------------------------------------------------------- forward
+
+namespace {
+int fold_forward(vex_ctx* ctx, const std::vector<cudaEvent_t>& ev);
+}
 
 size_t cnn_workspace_bytes(const vex_ctx* ctx, int n, int h, int w) {
   if (!ctx->cnn) return 0;
@@ -635,10 +661,23 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
     cudaEventRecord(e, s);
     P->prof.push_back(e);
   };
+  // option "nvtx": one range per layer launch (tracing); ranges close on every exit path
+  struct NvtxLayers {
+    bool on, open = false;
+    explicit NvtxLayers(bool e) : on(e) {}
+    void operator()(const char* name) { if (!on) return; if (open) nvtxRangePop(); nvtxRangePushA(name); open = true; }
+    ~NvtxLayers() { if (open) nvtxRangePop(); }
+  } layer(ctx->opt_nvtx != 0);
   int rc;
   const bool thin_tc = ctx->opt_thin_tc != 0;
   mark();
-  if (thin_tc && d.c1 == 128) {
+  layer("vex.conv1");
+  if (in_bgr == IN_F32_NCHW) {
+    if (d.c1 == 128) rc = launch_i27<thin::MODE_CONV1_F32, 128>(ctx, 0x800u, in, P->t1wf, x1, n, H, W, 0, s);
+    else if (d.c1 == 256) rc = launch_i27<thin::MODE_CONV1_F32, 256>(ctx, 0x1000u, in, P->t1wf, x1, n, H, W, 0, s);
+    else rc = fail(ctx, VEX_ERR_UNSUPPORTED, "vex_cnn2x_f32in: c1 must be 128 or 256");
+    if (rc) return rc;
+  } else if (thin_tc && d.c1 == 128) {
     if ((rc = launch_i27<thin::MODE_CONV1, 128>(ctx, 8u, in, P->t1w, x1, n, H, W, in_bgr, s))) return rc;
   } else if (thin_tc && d.c1 == 256) {
     if ((rc = launch_i27<thin::MODE_CONV1, 256>(ctx, 16u, in, P->t1w, x1, n, H, W, in_bgr, s))) return rc;
@@ -651,9 +690,11 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
   }
   mark();
   if (out_f32 && tap == 1) return tap_bf16(x1, d.c1);
+  layer("vex.conv2");
   if ((rc = run_tc(ctx, P->tc[0], x1, x2, x1, n, H, W, s))) return rc;        // + x1 after ReLU (app.py:292)
   mark();
   if (out_f32 && tap == 2) return tap_bf16(x2, d.c2);
+  layer("vex.conv3");
   if ((rc = run_tc(ctx, P->tc[1], x2, x3, nullptr, n, H, W, s))) return rc;
   if (out_f32 && tap == 3) return tap_bf16(x3, d.c3);
   for (int e = 0; e < d.n_extra; ++e) {                                        // ping-pong bufC <-> bufD
@@ -663,6 +704,7 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
     if (out_f32 && tap == 7 + e) return tap_bf16(x3, d.c3);
   }
   mark();                                                                      // conv3's slot includes the extra blocks
+  layer("vex.conv4");
   if ((rc = run_tc(ctx, P->tc[2], x3, x4, nullptr, n, H, W, s))) return rc;
   mark();
   if (out_f32 && tap == 4) return tap_bf16(x4, d.c4);
@@ -673,6 +715,7 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
                                        (int)small::T3_SMEM));
     ctx->attr_mask |= 4u;
   }
+  layer("vex.conv5");
   if (thin_tc) {
     if ((rc = launch_g27<thin::MODE_CONV5>(ctx, 32u, x4, d.c4, P->t5w, P->b5, x5, nullptr, nullptr, n, H, W, 0, s)))
       return rc;
@@ -690,6 +733,7 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
     VEX_CUDA(ctx, cudaGetLastError());
     return VEX_OK;
   }
+  layer("vex.tail");
   if (thin_tc && ctx->opt_fuse_tail && d.up_ch == 64 && !(out_f32 && tap == 6)) {
     // upconv1 + relu + upconv2 + clamp + uint8 in one kernel: `up` never reaches HBM
     if ((rc = launch_uptail(ctx, x5, P->tu1wb, P->tu2w, P->bu2, out_u8, out_f32, n, H, W, out_bgr, s))) return rc;
@@ -736,8 +780,32 @@ int cnn_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f32
     return fail(ctx, VEX_ERR_NO_WEIGHTS, "vex_cnn_load_weights has not been called");
   if ((long long)h * w > (1LL << 28)) return fail(ctx, VEX_ERR_INVALID, "frame too large");
   // bound the activation workspace: sub-batches of at most ws_budget bytes (at least one frame)
-  for (cudaEvent_t e : ctx->cnn->prof) ctx->cnn->prof_pool.push_back(e);
-  ctx->cnn->prof.clear();
+  {
+    CnnPlan* P = ctx->cnn;
+    if (!P->prof.empty()) {                   // keep the previous forward's events until they are folded into the statistics
+      if (P->prof_folded || !ctx->opt_profile) {
+        for (cudaEvent_t e : P->prof) P->prof_pool.push_back(e);
+      } else {
+        P->prof_done.push_back(P->prof);
+        if (P->prof_done.size() > 512) {      // bound the event count: fold the oldest (long finished) forward
+          int rc = fold_forward(ctx, P->prof_done.front());
+          if (rc) return rc;
+          for (cudaEvent_t e : P->prof_done.front()) P->prof_pool.push_back(e);
+          P->prof_done.erase(P->prof_done.begin());
+        }
+      }
+      P->prof.clear();
+    }
+    P->prof_folded = false;
+  }
+  // One activation workspace per ctx: a forward on stream s must not start before the previous forward, on whatever
+  // stream that ran (the caller's for vex_cnn2x_u8, the ctx's compute stream for the host-buffer entries), has ended.
+  if (!ctx->ev_ws) VEX_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_ws, cudaEventDisableTiming));
+  if (ctx->ws_used) VEX_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_ws, 0));
+  struct WsMark {                             // recorded on every exit path, after the last launch
+    vex_ctx* c; cudaStream_t st;
+    ~WsMark() { if (cudaEventRecord(c->ev_ws, st) == cudaSuccess) c->ws_used = true; }
+  } ws_mark{ctx, s};
   const size_t per_frame = ws_layout(ctx->cnn->arch, (size_t)h * w).total;
   const size_t budget = (size_t)ctx->opt_ws_budget_mb << 20;
   int sub = (int)std::max<size_t>(1, std::min<size_t>((size_t)n, budget / std::max<size_t>(per_frame, 1)));
@@ -748,7 +816,7 @@ int cnn_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f32
   const size_t out_px = (tap == 0 || tap == 6) ? (size_t)4 * h * w : (size_t)h * w;
   for (int f0 = 0; f0 < n; f0 += sub) {
     const int nf = std::min(sub, n - f0);
-    int rc = forward_chunk(ctx, in + (size_t)f0 * h * w * 3, out_u8 ? out_u8 + (size_t)f0 * h * w * 12 : nullptr,
+    int rc = forward_chunk(ctx, in + (size_t)f0 * h * w * 3 * (in_bgr == IN_F32_NCHW ? 4 : 1), out_u8 ? out_u8 + (size_t)f0 * h * w * 12 : nullptr,
                            out_f32 ? out_f32 + (size_t)f0 * out_ch[tap] * out_px : nullptr, tap, nf, h, w, in_bgr,
                            out_bgr, s);
     if (rc) return rc;
@@ -756,18 +824,75 @@ int cnn_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f32
   return VEX_OK;
 }
 
+namespace {
+// per-layer ms of one forward (8 events per sub-batch, sub-batches summed); synchronises on its last event
+int forward_ms(vex_ctx* ctx, const std::vector<cudaEvent_t>& ev, float* ms7) {
+  VEX_CUDA(ctx, cudaEventSynchronize(ev.back()));
+  for (int i = 0; i < 7; ++i) ms7[i] = 0.f;
+  for (size_t b = 0; b + 8 <= ev.size(); b += 8)
+    for (int i = 0; i < 7; ++i) {
+      float ms = 0.f;
+      VEX_CUDA(ctx, cudaEventElapsedTime(&ms, ev[b + i], ev[b + i + 1]));
+      ms7[i] += ms;
+    }
+  return VEX_OK;
+}
+int fold_forward(vex_ctx* ctx, const std::vector<cudaEvent_t>& ev) {
+  CnnPlan* P = ctx->cnn;
+  if (ev.empty() || ev.size() % 8 != 0) return VEX_OK;     // a debug-tap forward that returned early: not a full forward
+  float ms[7];
+  int rc = forward_ms(ctx, ev, ms);
+  if (rc) return rc;
+  for (int i = 0; i < 7; ++i) {
+    P->prof_sum[i] += ms[i];
+    P->prof_min[i] = P->prof_n ? std::min(P->prof_min[i], ms[i]) : ms[i];
+    P->prof_max[i] = P->prof_n ? std::max(P->prof_max[i], ms[i]) : ms[i];
+  }
+  P->prof_n++;
+  return VEX_OK;
+}
+}  // namespace
+
 int cnn_profile_ms(vex_ctx* ctx, float* ms7) {
   CnnPlan* P = ctx->cnn;
   if (!P || P->prof.empty() || P->prof.size() % 8 != 0)
     return fail(ctx, VEX_ERR_INVALID, "vex_cnn_profile_ms: no complete profiled forward (set option profile=1)");
-  VEX_CUDA(ctx, cudaEventSynchronize(P->prof.back()));
-  for (int i = 0; i < 7; ++i) ms7[i] = 0.f;
-  for (size_t b = 0; b < P->prof.size(); b += 8)
-    for (int i = 0; i < 7; ++i) {
-      float ms = 0.f;
-      VEX_CUDA(ctx, cudaEventElapsedTime(&ms, P->prof[b + i], P->prof[b + i + 1]));
-      ms7[i] += ms;
-    }
+  return forward_ms(ctx, P->prof, ms7);
+}
+
+void cnn_profile_reset(vex_ctx* ctx) {
+  CnnPlan* P = ctx->cnn;
+  if (!P) return;
+  for (auto& g : P->prof_done)
+    for (cudaEvent_t e : g) P->prof_pool.push_back(e);
+  P->prof_done.clear();
+  for (cudaEvent_t e : P->prof) P->prof_pool.push_back(e);
+  P->prof.clear();
+  P->prof_folded = false;
+  P->prof_n = 0;
+  for (int i = 0; i < 7; ++i) { P->prof_sum[i] = 0; P->prof_min[i] = P->prof_max[i] = 0.f; }
+}
+
+int cnn_profile_stats(vex_ctx* ctx, float* mean7, float* min7, float* max7, int* n_forwards) {
+  CnnPlan* P = ctx->cnn;
+  if (!P) return fail(ctx, VEX_ERR_INVALID, "vex_cnn_profile_stats: no CNN plan");
+  for (auto& g : P->prof_done) {
+    int rc = fold_forward(ctx, g);
+    if (rc) return rc;
+    for (cudaEvent_t e : g) P->prof_pool.push_back(e);
+  }
+  P->prof_done.clear();
+  if (!P->prof_folded && !P->prof.empty()) {
+    int rc = fold_forward(ctx, P->prof);
+    if (rc) return rc;
+    P->prof_folded = true;
+  }
+  *n_forwards = P->prof_n;
+  for (int i = 0; i < 7; ++i) {
+    if (mean7) mean7[i] = P->prof_n ? (float)(P->prof_sum[i] / P->prof_n) : 0.f;
+    if (min7) min7[i] = P->prof_min[i];
+    if (max7) max7[i] = P->prof_max[i];
+  }
   return VEX_OK;
 }
 
@@ -791,7 +916,7 @@ void cnn_destroy(vex_ctx* ctx) {
   CnnPlan* P = ctx->cnn;
   if (!P) return;
   float* fs[] = {P->w1g, P->b1, P->w5g, P->b5, P->wu1, P->bu1, P->wu2, P->bu2};
-  uint8_t* us[] = {P->t1w, P->tu1wb, P->t5w, P->tu2w};
+  uint8_t* us[] = {P->t1w, P->tu1wb, P->t5w, P->tu2w, P->t1wf};
   for (uint8_t* u : us)
     if (u) cudaFree(u);
   for (float* f : fs)
@@ -806,6 +931,8 @@ void cnn_destroy(vex_ctx* ctx) {
   }
   if (P->ws) cudaFree(P->ws);
   for (cudaEvent_t e : P->prof) cudaEventDestroy(e);
+  for (auto& g : P->prof_done)
+    for (cudaEvent_t e : g) cudaEventDestroy(e);
   for (cudaEvent_t e : P->prof_pool) cudaEventDestroy(e);
   delete P;
   ctx->cnn = nullptr;

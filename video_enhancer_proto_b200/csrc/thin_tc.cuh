@@ -28,7 +28,7 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 }
 
 // ============================================================================================ im2col27
-constexpr int MODE_CONV1 = 0, MODE_UP1 = 1;
+constexpr int MODE_CONV1 = 0, MODE_UP1 = 1, MODE_CONV1_F32 = 2;   // _F32: fp32 NCHW input as hi + lo bf16 (K = 64)
 constexpr int I27_THREADS = 544;       // warps 0-3 / 4-7 two A-builder groups, warp 8 MMA, warps 9-12 / 13-16 two drain groups
 constexpr int I27_SA = 4;              // A stages (128 rows x 128 B each); item sequence k uses stage k & 3
 constexpr int I27_MMA_WARP = 8;
@@ -49,7 +49,7 @@ struct I27Cfg {
 };
 
 struct I27Params {
-  const void* in;          // MODE_CONV1: uint8 [n][H][W][3];  MODE_UP1: float4 [n][H][W]
+  const void* in;          // MODE_CONV1: uint8 [n][H][W][3];  MODE_UP1: float4 [n][H][W];  MODE_CONV1_F32: float [n][3][H][W]
   const uint8_t* wpack;    // BN rows x 128 B, SWIZZLE_128B image, k = (ky*3+kx)*3+ci for k < 27; k = 27, 28 = bias as hi + lo bf16
   __nv_bfloat16* out;      // MODE_CONV1: [n][H][W][BN];  MODE_UP1: [n][2H][2W][BN/4]
   int H, W;
@@ -98,9 +98,9 @@ im2col27_kernel(const I27Params p) {
     uint32_t sa = gi, pa = 0;
     for (long long it = blockIdx.x + (long long)gi * gridDim.x; it < items; it += 2LL * gridDim.x) {
       const long long pix = it * 128 + r;
-      uint32_t w[16];
+      uint32_t w[16], wlo[16];
 #pragma unroll
-      for (int j = 0; j < 16; ++j) w[j] = 0u;
+      for (int j = 0; j < 16; ++j) w[j] = wlo[j] = 0u;
       if (pix < p.npix && !(p.probe & 4)) {
         const int x = (int)(pix % p.W);
         const long long t = pix / p.W;
@@ -115,7 +115,12 @@ im2col27_kernel(const I27Params p) {
             const int xx = x + kx - 1;
             const bool ok = yy >= 0 && yy < p.H && xx >= 0 && xx < p.W;
             const long long q = (img * p.H + yy) * p.W + xx;
-            if (MODE == MODE_CONV1) {
+            if (MODE == MODE_CONV1_F32) {
+              const size_t plane = (size_t)p.H * p.W;
+              const float* s = reinterpret_cast<const float*>(p.in) + (size_t)img * 3 * plane + (size_t)yy * p.W + xx;
+#pragma unroll
+              for (int c = 0; c < 3; ++c) v[(ky * 3 + kx) * 3 + c] = ok ? __ldg(s + c * plane) : 0.f;
+            } else if (MODE == MODE_CONV1) {
               const uint8_t* s = reinterpret_cast<const uint8_t*>(p.in) + q * 3;
 #pragma unroll
               for (int c = 0; c < 3; ++c)
@@ -131,12 +136,27 @@ im2col27_kernel(const I27Params p) {
         for (int j = 0; j < 13; ++j) w[j] = ptx::pack_bf16x2(v[2 * j], v[2 * j + 1]);
         w[13] = ptx::pack_bf16x2(v[26], 1.0f);       // k = 27, 28: constant 1 against the bias rows (hi + lo bf16) of W, so the
         w[14] = ptx::pack_bf16x2(1.0f, 0.f);         // drain needs no per-element bias load and add
+        if (MODE == MODE_CONV1_F32) {                // k = 32..58: what the bf16 rounding of k = 0..26 dropped
+#pragma unroll
+          for (int j = 0; j < 27; ++j) {
+            const uint32_t hw = (j & 1) ? (w[j >> 1] & 0xFFFF0000u) : (w[j >> 1] << 16);
+            v[j] -= __uint_as_float(hw);
+          }
+#pragma unroll
+          for (int j = 0; j < 13; ++j) wlo[j] = ptx::pack_bf16x2(v[2 * j], v[2 * j + 1]);
+          wlo[13] = ptx::pack_bf16x2(v[26], 0.f);
+        }
       }
       ptx::mbar_wait(a_empty + 8 * sa, pa ^ 1);
       uint8_t* row = sm + sa * C::A_STAGE + r * 128;
 #pragma unroll
       for (int j = 0; j < 4; ++j)
         *reinterpret_cast<uint4*>(row + ((j ^ (r & 7)) << 4)) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+      if (MODE == MODE_CONV1_F32) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          *reinterpret_cast<uint4*>(row + (((4 + j) ^ (r & 7)) << 4)) = make_uint4(wlo[4 * j], wlo[4 * j + 1], wlo[4 * j + 2], wlo[4 * j + 3]);
+      }
       ptx::fence_proxy_async_smem();                 // generic-proxy stores -> visible to the tensor core
       ptx::mbar_arrive(a_full + 8 * sa);
       sa += 2;
@@ -155,7 +175,7 @@ im2col27_kernel(const I27Params p) {
         ptx::mbar_wait(a_full + 8 * sa, pa);
         ptx::tc_fence_after();
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {
+        for (int k = 0; k < (MODE == MODE_CONV1_F32 ? 4 : 2); ++k) {
           const uint64_t ad = ptx::smem_desc_sw128(sbase + sa * C::A_STAGE + k * 32, 0);
           const uint64_t bd = ptx::smem_desc_sw128(sbase + C::W_OFF + k * 32, 0);
           ptx::mma_bf16_ss(tmem + b * BN, ad, bd, idesc, k);
@@ -187,7 +207,7 @@ im2col27_kernel(const I27Params p) {
       uint8_t* obase = nullptr;                      // first of this pixel's HALVES 256-byte destinations
       size_t half_stride = 256;                      // CONV1: next 128 channels of the same pixel
       if (valid) {
-        if (MODE == MODE_CONV1) {
+        if (MODE != MODE_UP1) {
           obase = reinterpret_cast<uint8_t*>(p.out + pix * BN);
         } else {
           const int x = (int)(pix % p.W);

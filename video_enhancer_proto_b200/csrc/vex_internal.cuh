@@ -37,6 +37,19 @@ struct vex_ctx {
   uint8_t* slot_in[2] = {nullptr, nullptr};
   uint8_t* slot_out[2] = {nullptr, nullptr};
   size_t slot_in_bytes = 0, slot_out_bytes = 0;
+  // asynchronous tickets (vex_submit / vex_wait): ticket t completes when ev_ticket[t % VEX_MAX_TICKETS] fires
+  static constexpr int kTickets = 8;
+  cudaEvent_t ev_ticket[kTickets] = {};
+  unsigned long long next_ticket = 1;                 // tickets are 1-based; 0 is "none"
+  unsigned long long ticket_in_ring[kTickets] = {};   // which ticket last used the ring entry (0 = never / waited)
+  unsigned long long chunk_seq = 0;                   // chunks enqueued so far (slot = seq & 1)
+  // pinned staging of vex_upscale_frames (pageable per-frame pointers in): one buffer per device slot
+  uint8_t* stage_in[2] = {nullptr, nullptr};
+  size_t stage_in_bytes = 0;
+  // every CNN forward on this ctx shares one activation workspace: `ev_ws` marks the end of the last forward, whatever
+  // stream it ran on, and the next forward waits for it (two streams must not interleave on the workspace)
+  cudaEvent_t ev_ws = nullptr;
+  bool ws_used = false;
   unsigned attr_mask3 = 0;        // same for the conv_tc3 instantiations
   unsigned attr_mask = 0;         // which kernels had their max-dynamic-smem attribute set on this device
 
@@ -57,11 +70,29 @@ struct vex_ctx {
   int opt_thin_tc = 1;            // thin layers on tcgen05 (thin_tc.cuh); 0 = fp32 CUDA-core kernels (cnn_small.cuh)
   int opt_epi_variant = 0;        // bring-up timing probes for the conv_tc epilogue (produce wrong results)
   int opt_conv_dbg = 0;           // bring-up: print per-role cycle counters of every conv_tc launch (synchronises)
-  int opt_profile = 0;            // record per-layer events in cnn_forward (vex_cnn_profile_ms)
+  int opt_profile = 0;            // record per-layer events in cnn_forward (vex_cnn_profile_ms / vex_cnn_profile_stats)
+  int opt_nvtx = 0;               // one NVTX range per layer launch
   int opt_ws_budget_mb = 49152;   // CNN activation workspace cap; larger batches run in sub-batches
 };
 
 namespace vex {
+
+// Entry points run on ctx->device and leave the caller's current device as they found it (PyTorch reads it back).
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess;
+  }
+  ~DeviceGuard() {
+    int cur = -1;
+    if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
+  }
+};
+#define VEX_ON_DEVICE(ctx)                                                                   \
+  ::vex::DeviceGuard guard__((ctx)->device);                                                 \
+  if (!guard__.ok) return ::vex::fail((ctx), VEX_ERR_CUDA, "cudaSetDevice failed")
 
 inline int fail(vex_ctx* ctx, int code, const std::string& msg) {
   if (ctx) ctx->err = msg;
@@ -82,7 +113,12 @@ inline int fail(vex_ctx* ctx, int code, const std::string& msg) {
 int launch_bicubic2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w,
                      int round_mode, cudaStream_t s);
 
+int launch_bicubic2x_f32in(vex_ctx* ctx, const float* in_nchw, uint8_t* out, int n, int h, int w, cudaStream_t s);
+
 // cnn.cu
+constexpr int IN_F32_NCHW = 2;   // cnn_forward's in_bgr argument: 0 RGB u8, 1 BGR u8, 2 = `in` is fp32 NCHW in [0,1] (no swap)
+void cnn_profile_reset(vex_ctx* ctx);
+int cnn_profile_stats(vex_ctx* ctx, float* mean7, float* min7, float* max7, int* n_forwards);
 int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const* tensors, int n);
 int cnn_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f32, int tap,
                 int n, int h, int w, int in_bgr, int out_bgr, cudaStream_t s);

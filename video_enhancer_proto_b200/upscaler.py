@@ -213,6 +213,16 @@ class B200VideoEnhancer:
         _lib.check(self._ctx, rc, "vex_cnn_profile_ms")
         return dict(zip(self.LAYER_NAMES, [float(v) for v in ms]))
 
+    def cnn_profile_stats(self) -> Dict[str, Dict[str, float]]:
+        """Mean / min / max per-layer device ms over every forward since ``set_option("profile", 1)``
+        (vex_cnn_profile_stats) plus ``n`` = forwards counted."""
+        self._ensure_ctx()
+        mean, lo, hi, n = (C.c_float * 7)(), (C.c_float * 7)(), (C.c_float * 7)(), C.c_int()
+        rc = self._lib.vex_cnn_profile_stats(self._ctx, mean, lo, hi, C.byref(n))
+        _lib.check(self._ctx, rc, "vex_cnn_profile_stats")
+        return {"mean": dict(zip(self.LAYER_NAMES, map(float, mean))), "min": dict(zip(self.LAYER_NAMES, map(float, lo))),
+                "max": dict(zip(self.LAYER_NAMES, map(float, hi))), "n": int(n.value)}
+
     def kernel_launches(self) -> int:
         self._ensure_ctx()
         v = C.c_ulonglong()
@@ -228,34 +238,84 @@ class B200VideoEnhancer:
         """app.py:314-319: uint8 HWC ndarray (or fp32 NCHW tensor in [0,1]) -> uint8 HWC (2H,2W,3)."""
         return self._enhance_frame_with_gpu(frame)
 
+    def _tensor_frame(self, frame: torch.Tensor) -> torch.Tensor:
+        """app.py:337-338 / :367-368: the tensor branch takes fp32 NCHW (or CHW) in [0,1] as it is - no rounding to
+        uint8 on the way in (the reference feeds it to conv1 / F.interpolate unquantised)."""
+        t = frame.detach()
+        if t.dim() == 3:
+            t = t.unsqueeze(0)
+        if t.dim() != 4 or t.shape[1] != 3:
+            raise ValueError("tensor frames must be [1,3,H,W] or [3,H,W]")
+        return t.to(device=f"cuda:{self._ordinal()}", dtype=torch.float32).contiguous()
+
     def _enhance_frame_with_gpu(self, frame):
         """app.py:322-352: single frame through the CNN, no colour swap."""
-        if isinstance(frame, torch.Tensor):               # app.py:337-338: fp32 NCHW in [0,1]
-            t = frame.detach()
-            if t.dim() == 4:
-                t = t[0]
-            frame = (t.permute(1, 2, 0).clamp(0, 1) * 255.0).round().to(torch.uint8).cpu().numpy()
+        if isinstance(frame, torch.Tensor):
+            self._ensure_ctx()
+            self._ensure_weights()
+            t = self._tensor_frame(frame)
+            n, _, h, w = t.shape
+            out = torch.empty((n, 2 * h, 2 * w, 3), dtype=torch.uint8, device=t.device)
+            rc = self._lib.vex_cnn2x_f32in(self._ctx, t.data_ptr(), out.data_ptr(), None, n, h, w, 0,
+                                           torch.cuda.current_stream(t.device).cuda_stream)
+            _lib.check(self._ctx, rc, "vex_cnn2x_f32in")
+            return out[0].cpu().numpy()                    # app.py:345: squeeze(0) -> HWC
         return self._run_host(_lib.VEX_MODE_CNN, [np.ascontiguousarray(frame)], 0)[0].copy()
+
+    def cnn_f32in_debug(self, frames_nchw: torch.Tensor) -> torch.Tensor:
+        """Parity hook for the tensor branch: fp32 NCHW in -> pre-quantisation fp32 NCHW [n,3,2h,2w] (vex_cnn2x_f32in)."""
+        self._ensure_ctx()
+        self._ensure_weights()
+        t = self._tensor_frame(frames_nchw)
+        n, _, h, w = t.shape
+        out = torch.empty((n, 3, 2 * h, 2 * w), dtype=torch.float32, device=t.device)
+        rc = self._lib.vex_cnn2x_f32in(self._ctx, t.data_ptr(), None, out.data_ptr(), n, h, w, 0,
+                                       torch.cuda.current_stream(t.device).cuda_stream)
+        _lib.check(self._ctx, rc, "vex_cnn2x_f32in")
+        return out
 
     def _enhance_frame_cpu_fallback(self, frame):
         """app.py:359-385 semantics (bicubic, clip, truncate) — computed by the GPU kernel."""
         if isinstance(frame, torch.Tensor):
-            t = frame.detach()
-            if t.dim() == 4:
-                t = t[0]
-            frame = (t.permute(1, 2, 0).clamp(0, 1) * 255.0).round().to(torch.uint8).cpu().numpy()
+            self._ensure_ctx()
+            t = self._tensor_frame(frame)
+            n, _, h, w = t.shape
+            out = torch.empty((n, 2 * h, 2 * w, 3), dtype=torch.uint8, device=t.device)
+            rc = self._lib.vex_bicubic2x_f32in(self._ctx, t.data_ptr(), out.data_ptr(), n, h, w,
+                                               torch.cuda.current_stream(t.device).cuda_stream)
+            _lib.check(self._ctx, rc, "vex_bicubic2x_f32in")
+            return out[0].cpu().numpy()
         return self._run_host(_lib.VEX_MODE_BICUBIC, [np.ascontiguousarray(frame)], 0)[0].copy()
 
     def _process_frame_batch_gpu(self, frames_batch: List[np.ndarray]) -> List[np.ndarray]:
-        """app.py:529-553: RGB uint8 frames in, BGR uint8 (2H,2W,3) frames out."""
-        out = self._run_host(_lib.VEX_MODE_CNN, frames_batch, flags=0b10)
-        return [out[i].copy() for i in range(out.shape[0])]
+        """app.py:529-553: RGB uint8 frames in, BGR uint8 (2H,2W,3) frames out.
+
+        The frames of the list are separate pageable arrays; ``vex_upscale_frames`` stages them chunk by chunk into
+        the ctx's pinned buffers while the previous chunk computes, and the results land in a FRESH pinned tensor
+        (torch's caching host allocator) whose rows are returned as the output arrays - no host copy on the way out,
+        and the arrays stay valid for as long as the caller keeps them."""
+        return self._run_frames(_lib.VEX_MODE_CNN, frames_batch, flags=0b10)
+
+    def _run_frames(self, mode: int, frames: Sequence[np.ndarray], flags: int) -> List[np.ndarray]:
+        self._ensure_ctx()
+        if mode == _lib.VEX_MODE_CNN:
+            self._ensure_weights()
+        h, w = self._check_frames(frames)
+        n = len(frames)
+        keep = [f if f.flags["C_CONTIGUOUS"] else np.ascontiguousarray(f) for f in frames]
+        ptrs = (C.c_void_p * n)(*[f.ctypes.data for f in keep])
+        out = torch.empty((n, 2 * h, 2 * w, 3), dtype=torch.uint8, pin_memory=True)
+        rc = self._lib.vex_upscale_frames(self._ctx, mode, ptrs, out.data_ptr(), n, h, w, self.batch_size, flags)
+        _lib.check(self._ctx, rc, "vex_upscale_frames")
+        res = out.numpy()
+        return [res[i] for i in range(n)]
 
     def process_video(self, input_path, output_path, target_fps=30):
         """app.py:388-519: never raises; returns (ok, message)."""
         try:
             start = time.time()
             stats = self._run_video(str(input_path), str(output_path), target_fps=target_fps)
+            stats.pop("_size", None)
             dt = time.time() - start
             self.processing_stats["total_processed"] += 1          # app.py:509-510
             self.processing_stats["total_time"] += dt
@@ -270,12 +330,18 @@ class B200VideoEnhancer:
     # ------------------------------------------------------------------ handler protocol
     def enhance_video(self, input_path: str, output_path: str, **kwargs) -> Dict:
         """basic_upscaler_fallback.py:67-169 contract: raises ValueError on unreadable input."""
-        return self._run_video(str(input_path), str(output_path), target_fps=kwargs.get("target_fps"))
+        s = self._run_video(str(input_path), str(output_path), target_fps=kwargs.get("target_fps"))
+        if not kwargs.get("_keep_size"):
+            s.pop("_size", None)
+        return s
 
     def restore_video(self, input_path: str, output_path: str, **kwargs) -> Dict:
         """vsr/realesrgan_handler.py:214-273 key set."""
-        s = self.enhance_video(input_path, output_path, **kwargs)
-        s.update(processing_mode="frame_batch", scale_factor=self.scale)
+        s = self.enhance_video(input_path, output_path, _keep_size=True, **kwargs)
+        w, h = s.pop("_size")
+        # realesrgan_handler.py:265-273: resolutions are (H, W) tuples here (the frame handlers' are "WxH" strings)
+        s.update(processing_mode="b200_frame_batch", scale_factor=self.scale, input_resolution=(h, w),
+                 output_resolution=(h * self.scale, w * self.scale))
         return s
 
     def get_model_info(self) -> Dict:
@@ -320,19 +386,52 @@ class B200VideoEnhancer:
             # cv2 frames are BGR.  bicubic is channel-agnostic (basic_upscaler_fallback.py:142); for the CNN the
             # frames stay BGR on the host and in_bgr|out_bgr do app.py:469 and :550 inside the kernels
             flags = 1 if mode == _lib.VEX_MODE_BICUBIC else 0b11
+            if width <= 0 or height <= 0:
+                raise ValueError(f"Could not read the frame size of: {input_path}")
             n_done = 0
+            self._ensure_ctx()
+            if mode == _lib.VEX_MODE_CNN:
+                self._ensure_weights()
+            # Rotating pinned buffers on both sides of the GPU: the decoder writes frames straight into a pinned input
+            # batch, vex_submit streams it (H2D -> kernels -> D2H on the ctx's three streams) into a pinned output
+            # batch, the encoder reads frames straight out of that.  Two batches stay submitted-but-unwaited, so the
+            # copies of one overlap the kernels of the other ACROSS calls and the GPU does not drain between batches.
+            B, inflight = self.batch_size, 2
+            fin = height * width * 3
+            slots = pipeline.n_slots(self.pipeline_depth, inflight)
+            ins = [self._pinned_buf(f"vin{i}", B * fin).numpy()[: B * fin].reshape(B, height, width, 3) for i in range(slots)]
+            outs = [self._pinned_buf(f"vout{i}", B * fin * 4) for i in range(slots)]
+            n_read = 0
 
             def read_batch():
-                batch: List[np.ndarray] = []
-                while len(batch) < self.batch_size:
-                    ret, frame = cap.read()
+                nonlocal n_read
+                view = ins[n_read % slots]
+                n = 0
+                while n < B:
+                    ret, frame = cap.read(view[n])                       # decodes into the pinned row when the size matches
                     if not ret:
                         break
-                    batch.append(frame)
-                return batch or None
+                    if frame.shape != view[n].shape:
+                        raise ValueError(f"frame {frame.shape} does not match the container size {(height, width, 3)}")
+                    if frame.ctypes.data != view[n].ctypes.data:
+                        view[n] = frame
+                    n += 1
+                if n == 0:
+                    return None
+                n_read += 1
+                return n
 
-            def process(batch, slot):
-                return self._run_host(mode, batch, flags, slot=slot)
+            def submit(n, slot):
+                t = C.c_ulonglong()
+                rc = self._lib.vex_submit(self._ctx, mode, ins[slot].ctypes.data, outs[slot].data_ptr(), n, height, width,
+                                          flags, C.byref(t))
+                _lib.check(self._ctx, rc, "vex_submit")
+                return t.value, slot, n
+
+            def finish(handle):
+                t, slot, n = handle
+                _lib.check(self._ctx, self._lib.vex_wait(self._ctx, t), "vex_wait")
+                return outs[slot].numpy()[: n * fin * 4].reshape(n, 2 * height, 2 * width, 3)
 
             def write(res):
                 nonlocal n_done
@@ -340,16 +439,25 @@ class B200VideoEnhancer:
                     out.write(res[i])
                 n_done += res.shape[0]
 
-            # decode and encode on their own threads, the GPU call on this one
-            pipeline.run_ordered_pipeline(read_batch, process, write, depth=self.pipeline_depth)
+            # decode and encode on their own threads, submit / wait on this one
+            pipeline.run_ordered_pipeline(read_batch, submit, write, depth=self.pipeline_depth, finish=finish,
+                                          inflight=inflight)
         finally:
             cap.release()
             if out is not None:
                 out.release()
+        return self.video_stats(n_done, width, height, self.scale, self.model_name, float(out_fps),
+                                video_io.video_metadata(input_path))       # utils/video_utils.py:38 key set
+
+    @staticmethod
+    def video_stats(n_done: int, width: int, height: int, scale: int, model_name: str, out_fps: float, metadata) -> Dict:
+        """The statistics dictionary of the file-to-file calls: the keys the agent (video_enhancer_sota.py:202
+        `output_frames`), `@track_enhancement_performance` (utils/performance_monitor.py:497-505) and
+        `BasicUpscalerFallback.enhance_video` (basic_upscaler_fallback.py:154-162) read or return."""
         return {
             "frames_processed": n_done, "frames_failed": 0, "input_frames": n_done, "output_frames": n_done,
-            "scale": self.scale, "model": f"B200Upscaler-{self.model_name}",
-            "input_resolution": f"{width}x{height}", "output_resolution": f"{width * 2}x{height * 2}",
-            "fps": float(out_fps),
-            "input_metadata": video_io.video_metadata(input_path),       # utils/video_utils.py:38 key set
+            "scale": scale, "model": f"B200Upscaler-{model_name}",
+            "input_resolution": f"{width}x{height}", "output_resolution": f"{width * scale}x{height * scale}",
+            "fps": out_fps, "_size": (width, height),
+            "input_metadata": metadata,
         }

@@ -117,3 +117,99 @@ def test_video_metadata_keys_and_fallbacks(tmp_path):
     assert m["fps"] == pytest.approx(20.0, abs=0.5) and m["duration"] == pytest.approx(0.35, abs=0.06) and m["file_size"] > 0
     z = video_io.video_metadata(str(tmp_path / "missing.mp4"))
     assert set(z) == set(video_io.KEYS) and z["frame_count"] == 0 and z["width"] == 0
+
+
+@pytest.mark.parametrize("depth,inflight", [(1, 1), (2, 2), (3, 1)])
+def test_submit_finish_split_keeps_batches_in_flight_and_buffers_safe(depth, inflight):
+    """The asynchronous form the video loop uses (vex_submit / vex_wait): `process` submits and returns a handle,
+    `finish` waits.  Up to `inflight` batches are submitted before the oldest is waited for; input buffers (filled by
+    the reader thread) and output buffers (read by the writer thread) rotate over n_slots(depth, inflight) and must
+    never be overwritten while a later stage still needs them, even with a slow 'GPU' and a slow writer."""
+    slots = pipeline.n_slots(depth, inflight)
+    ins = [np.zeros(4, np.int64) for _ in range(slots)]
+    outs = [np.zeros(4, np.int64) for _ in range(slots)]
+    n_batches, n_read = 45, 0
+    events, got = [], []
+    lock = threading.Lock()
+
+    def read():
+        nonlocal n_read
+        if n_read == n_batches:
+            return None
+        ins[n_read % slots][:] = n_read                     # the reader writes straight into the rotating input buffer
+        n_read += 1
+        return n_read - 1
+
+    class FakeGpu(threading.Thread):                        # completes submitted work asynchronously, in order
+        def __init__(self):
+            super().__init__(daemon=True)
+            self.q, self.done = [], {}
+            self.cv = threading.Condition()
+
+        def run(self):
+            while True:
+                with self.cv:
+                    while not self.q:
+                        self.cv.wait()
+                    k, slot = self.q.pop(0)
+                if k is None:
+                    return
+                time.sleep(0.002)
+                outs[slot][:] = ins[slot] * 10              # reads the input buffer LATE: it must still hold batch k
+                with self.cv:
+                    self.done[k] = True
+                    self.cv.notify_all()
+
+    gpu = FakeGpu()
+    gpu.start()
+
+    def submit(k, slot):
+        assert slot == k % slots
+        with lock:
+            events.append(("submit", k))
+        with gpu.cv:
+            gpu.q.append((k, slot))
+            gpu.cv.notify_all()
+        return k, slot
+
+    def finish(handle):
+        k, slot = handle
+        with gpu.cv:
+            while k not in gpu.done:
+                gpu.cv.wait()
+        with lock:
+            events.append(("finish", k))
+        return k, outs[slot]
+
+    def write(res):
+        k, buf = res
+        time.sleep(0.001)
+        assert (buf == 10 * k).all(), (k, buf)
+        got.append(k)
+
+    n = pipeline.run_ordered_pipeline(read, submit, write, depth=depth, finish=finish, inflight=inflight)
+    with gpu.cv:
+        gpu.q.append((None, 0))
+        gpu.cv.notify_all()
+    assert n == n_batches and got == list(range(n_batches))
+    # batch k + inflight was submitted before batch k was waited for (the GPU queue never drains between batches)
+    pos = {e: i for i, e in enumerate(events)}
+    for k in range(n_batches - inflight):
+        assert pos[("submit", k + inflight)] < pos[("finish", k)], k
+
+
+def test_submit_finish_error_still_waits_for_submitted_work():
+    waited = []
+
+    def submit(k, slot):
+        if k == 3:
+            raise RuntimeError("boom")
+        return k
+
+    def finish(k):
+        waited.append(k)
+        return k
+
+    with pytest.raises(RuntimeError, match="boom"):
+        pipeline.run_ordered_pipeline(make_reader(10), submit, lambda r: None, depth=2, finish=finish, inflight=2)
+    assert sorted(waited) == [0, 1, 2]                      # everything handed to the GPU before the error was waited for

@@ -163,6 +163,44 @@ int vex_cnn_profile_stats(vex_ctx* ctx, float* mean7, float* min7, float* max7, 
 /* Bytes of device workspace the ctx holds (grows on demand) for a batch of this shape. */
 int vex_workspace_bytes(const vex_ctx* ctx, int n, int h, int w, size_t* out);
 
+/* ---- Real-ESRGAN RRDBNet ------------------------------------------------- */
+
+/* RealESRGANNetwork (models/enhancement/vsr/realesrgan_handler.py:59-100) as the handler builds it (:143-150):
+ * num_feat 64, num_grow_ch 32 fixed; num_block 23 and scale 4 in the reference, scale 2 and other depths accepted. */
+typedef struct vex_rrdb_desc {
+  int num_feat, num_grow_ch, num_block, scale;
+} vex_rrdb_desc;
+
+/* tensors[i]: fp32 host arrays in the reference module's state_dict order: conv_first {weight,bias},
+ * body.<b>.rdb<1..3>.conv<1..5> {weight,bias} for b = 0..num_block-1, conv_body, conv_up1, (conv_up2 for scale 4),
+ * conv_hr, conv_last; n_tensors = 2 + 30*num_block + 2 + 2*(scale == 4 ? 2 : 1) + 4.  Converts to fp16 in the kernels'
+ * layouts (conv_first: bf16 hi + lo with the /255 of :311 folded in) and uploads; the caller keeps ownership.
+ * Replaces RealESRGANHandler._ensure_model_loaded / _load_model (:134-212) minus the download. */
+int vex_rrdb_load_weights(vex_ctx* ctx, const vex_rrdb_desc* arch, const float* const* tensors, int n_tensors);
+
+/* n images u8 HWC [h][w][3] -> u8 HWC [s*h][s*w][3] (s = scale), device pointers, the whole image in one pass:
+ * RealESRGANHandler._process_single (:308-322) incl. /255, clamp(0,1), x255 and the TRUNCATING uint8 cast.
+ * in_bgr / out_bgr: channel order of the buffers relative to the network's RGB planes (the handler converts BGR->RGB
+ * before and RGB->BGR after, :290,300; pass 1,1 for cv2 frames).  fp16 operands and activations, fp32 accumulation. */
+int vex_rrdb_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w,
+                int in_bgr, int out_bgr, void* stream);
+
+/* One frame the way RealESRGANHandler._enhance_frame does it (:286-306): if h or w exceeds tile_size the frame is cut
+ * into tile_size tiles with tile_pad pixels of context, each tile runs through the network on its own and its un-padded
+ * core is pasted into the output (_tile_process, :324-372; the reference uses tile_size 512, tile_pad 10) - cropping and
+ * pasting are strided device copies; otherwise the whole frame is one pass.  Device pointers, packed u8 HWC. */
+int vex_rrdb_frame_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int h, int w, int tile_size, int tile_pad,
+                      int in_bgr, int out_bgr, void* stream);
+
+/* Parity hook: fp32 NCHW of the selected activation.  tap 0 = clamp(conv_last, 0, 1) [n][3][s*h][s*w];
+ * 1 = conv_first [n][64][h][w]; 2 = feat + conv_body(body(feat)) [n][64][h][w]; 3 = lrelu(conv_hr) [n][64][s*h][s*w];
+ * 10 + b = output of body block b [n][64][h][w]; 1001..1004 = x1..x4 of body[0].rdb1 [n][32][h][w], 1005 = its output. */
+int vex_rrdb_f32_debug(vex_ctx* ctx, const uint8_t* in_hwc, float* out_nchw, int n, int h, int w, int in_bgr, int tap,
+                       void* stream);
+
+/* Bytes of activation workspace a batch of this shape needs (grows on demand). */
+int vex_rrdb_workspace_bytes(const vex_ctx* ctx, int n, int h, int w, size_t* out);
+
 /* ---- host-buffer streaming entry (the end-to-end path) ------------------------------------ */
 
 #define VEX_MODE_BICUBIC 0

@@ -7,4 +7,7 @@ from .upscaler import B200VideoEnhancer  # noqa: F401
 from . import shard, synth, weights  # noqa: F401
 
 GPUVideoEnhancer = B200VideoEnhancer       # reference class name (app.py:242)
-__all__ = ["B200VideoEnhancer", "GPUVideoEnhancer", "shard", "synth", "weights"]
+from .realesrgan import B200RealESRGAN  # noqa: F401,E402
+
+RealESRGANHandler = B200RealESRGAN         # reference class name (models/enhancement/vsr/realesrgan_handler.py:101)
+__all__ = ["B200VideoEnhancer", "GPUVideoEnhancer", "B200RealESRGAN", "RealESRGANHandler", "shard", "synth", "weights"]

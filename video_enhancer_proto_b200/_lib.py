@@ -14,6 +14,10 @@ VEX_CNN_MAX_EXTRA = 4
 VEX_CNN_TENSORS_PER_EXTRA = 6
 
 
+class VexRrdbDesc(C.Structure):
+    _fields_ = [("num_feat", C.c_int), ("num_grow_ch", C.c_int), ("num_block", C.c_int), ("scale", C.c_int)]
+
+
 class VexCnnDesc(C.Structure):
     _fields_ = [("c1", C.c_int), ("c2", C.c_int), ("c3", C.c_int), ("c4", C.c_int), ("up_ch", C.c_int),
                 ("bn_eps", C.c_float), ("n_extra", C.c_int)]
@@ -45,6 +49,11 @@ SIGNATURES = {
     "vex_bicubic2x_f32in": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "vex_cnn_profile_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_int)]),
     "vex_build_info": (C.c_char_p, []),
+    "vex_rrdb_load_weights": (C.c_int, [C.c_void_p, C.POINTER(VexRrdbDesc), C.POINTER(C.c_void_p), C.c_int]),
+    "vex_rrdb_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "vex_rrdb_frame_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "vex_rrdb_f32_debug": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "vex_rrdb_workspace_bytes": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)]),
     "vex_kernel_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_ulonglong)]),
     "vex_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
 }

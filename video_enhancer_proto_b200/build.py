@@ -10,7 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libvex.so")
-SOURCES = ["vex_api.cu", "bicubic.cu", "cnn.cu", "filters.cu"]
+SOURCES = ["vex_api.cu", "bicubic.cu", "cnn.cu", "filters.cu", "rrdb.cu"]
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC",

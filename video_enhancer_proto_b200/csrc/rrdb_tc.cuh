@@ -1,0 +1,320 @@
+// conv3x3 (pad 1, stride 1) of the Real-ESRGAN RRDB network (reference models/enhancement/vsr/realesrgan_handler.py:23-100)
+// as an implicit GEMM on the sm_100a tensor cores: tcgen05.mma (fp16 x fp16 -> fp32 in TMEM), TMA-staged activation halo
+// tiles, mbarrier rings.  One kernel serves every conv3x3 of the network except the 3-channel ends:
+//
+//   ResidualDenseBlock.conv1..conv4 (:41-44, 50-53)  Cin = 64/96/128/160 -> 32, LeakyReLU(0.2), written into the channel
+//        SLICE [64+32k, 96+32k) of the block's 192-channel NHWC "dense" buffer, so torch.cat((x, x1, ...), 1) costs nothing;
+//   ResidualDenseBlock.conv5 (:45, 54-56)            192 -> 64, `x5 * 0.2 + x`, and for the third block of an RRDBBlock also
+//        `out * 0.2 + x` of :36, both residuals applied in fp32 in the epilogue;
+//   conv_body (:65, 88-89)                           64 -> 64, `feat + body_feat`;
+//   conv_up1 / conv_up2 / conv_hr (:70-77, 93-98)    64 -> 64, LeakyReLU(0.2).
+//   F.interpolate(scale_factor=2, mode='nearest') in front of conv_up1 / conv_up2 (:93-96) is done by the PRODUCER of the
+//   tensor: its epilogue stores every output pixel to the 2 x 2 block of the upsampled buffer (`ups2`).
+//
+// Precision: fp16 operands and activations (the 23-block residual trunk needs the 11-bit mantissa: emulating the rounding
+// points on the CPU gives 0.5 LSB of max error with fp16 against 4.8 LSB with bf16), fp32 accumulation, fp32
+// epilogue arithmetic, saturating fp16 stores (a stale or overflowing value can never become Inf/NaN in a buffer).
+//
+// GEMM view: M = output pixels, N = Cout (BN = 32 or 64), K = 9 taps x Cin.  As in conv_tc3.cuh one TMA box load brings a
+// halo tile [ROWS+2][PITCH=32 px][64 ch] (128 B per pixel, SWIZZLE_128B, out-of-bounds = 0 = conv padding) and tap (dy,dx)
+// is the same buffer with the descriptor start advanced by (dy*32+dx) rows; 30 of 32 columns are valid outputs.
+// Cin is consumed in 64-channel chunks; Cin = 96 / 160 read the next 32 channels of the dense buffer too and multiply them
+// by zero weights (the buffer only ever holds finite values, see above): 10 % more MMAs over a block, no second code path.
+//
+// N = 32 / 64 makes the SS-mode MMA shared-memory bound (4 KB of A per 128 x N x 16 MMA at 128 B/clk: 40 / 48 clocks
+// against 16 / 32 of math), so unlike conv_tc3 there is nothing to win from CTA pairs and this kernel is single-CTA:
+// warp 0 TMA producer, warp 1 MMA issuer + TMEM owner, warps 2-5 epilogue; two TMEM slots of APS accumulators so the
+// epilogue of item k overlaps the MMAs of item k+1.  Persistent grid; work item = (image, 8-row x 30-column tile).
+#pragma once
+
+#include <cuda_fp16.h>
+
+#include "ptx.cuh"
+
+namespace vex {
+namespace rrdb {
+
+constexpr int PITCH = 32;
+constexpr int TILE_W = 30;
+constexpr int KC = 64;
+constexpr int SA = 2;
+constexpr int NTHREADS = 192;    // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue (TMEM lane quarter = warp & 3)
+constexpr int APS = 2;           // accumulators (128 pixels each) per work item
+constexpr int ROWS = APS * 4;
+
+template <int BN>
+struct Cfg {
+  static_assert(BN == 32 || BN == 64, "BN");
+  static constexpr int A_STAGE = (ROWS + 2) * PITCH * 128;
+  static constexpr int W_SLICE = BN * 128;              // one (chunk, tap) slice: BN rows x 64 fp16
+  static constexpr int SW = BN == 32 ? 18 : 9;          // ring = two / one chunk's worth of taps
+  static constexpr int BAR_OFF = SA * A_STAGE + SW * W_SLICE;
+  static constexpr int BIAS_OFF = BAR_OFF + 512;
+  static constexpr int STAGE_OFF = BIAS_OFF + 256;
+  static constexpr int SMEM = STAGE_OFF + 4 * 2048 + 1024;
+  static constexpr int TMEM_COLS = 2 * APS * BN;        // 128 / 256: a power of two >= 32
+};
+
+struct Params {
+  const uint8_t* wpack;   // [chunk][tap] slices of BN x 128 B, SWIZZLE_128B image, fp16
+  const float* bias;      // [BN]
+  __half* out;            // NHWC [n][H][W][out_cs] (ups2: [n][2H][2W][out_cs]); channels [out_c0, out_c0 + BN) are written
+  const __half* r1;       // optional residual, NHWC with channel stride r1_cs, channels [0, BN):  v = v * a1 + r1
+  const __half* r2;       // optional second residual:                                             v = v * a2 + r2
+  float a1, a2;
+  int out_cs, out_c0, r1_cs, r2_cs;
+  int lrelu;              // LeakyReLU(0.2) after the bias
+  int ups2;               // store every pixel to the 2 x 2 block of a twice as large output (nearest-neighbour upsample)
+  int H, W, NC;           // NC = 64-channel chunks of the input that are read
+  int tiles_x, tiles_y, n_img;
+};
+
+// fp32 pair -> packed fp16, round to nearest, saturating to +-65504
+__device__ __forceinline__ uint32_t pack_f16x2_sat(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ float2 unpack_f16x2(uint32_t w) {
+  return __half22float2(*reinterpret_cast<const __half2*>(&w));
+}
+// instruction descriptor for kind::f16 with fp16 A/B (format 0), fp32 D, both K-major
+__host__ __device__ constexpr uint32_t idesc_f16_f32(int m, int n) {
+  return (1u << 4) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
+}
+
+template <int BN>
+__global__ void __launch_bounds__(NTHREADS, 1)
+rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = ptx::smem_u32(smem_raw);
+  const uint32_t sbase = (raw + 1023u) & ~1023u;
+  uint8_t* sm = smem_raw + (sbase - raw);
+
+  const uint32_t a_stage0 = sbase;
+  const uint32_t w_stage0 = sbase + SA * C::A_STAGE;
+  const uint32_t bar0 = sbase + C::BAR_OFF;
+  // barrier map (8 B each): a_full[SA] a_empty[SA] w_full[SW] w_empty[SW] acc_full[2] acc_empty[2] | tmem slot
+  const uint32_t a_full = bar0, a_empty = bar0 + 8 * SA;
+  const uint32_t w_full = a_empty + 8 * SA, w_empty = w_full + 8 * C::SW;
+  const uint32_t acc_full = w_empty + 8 * C::SW, acc_empty = acc_full + 16;
+  const uint32_t tmem_slot = acc_empty + 16;
+  volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(sm + C::BAR_OFF + (tmem_slot - bar0));
+  float* bias_s = reinterpret_cast<float*>(sm + C::BIAS_OFF);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total = p.tiles_x * p.tiles_y * p.n_img;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < SA; ++i) { ptx::mbar_init(a_full + 8 * i, 1); ptx::mbar_init(a_empty + 8 * i, 1); }
+    for (int i = 0; i < C::SW; ++i) { ptx::mbar_init(w_full + 8 * i, 1); ptx::mbar_init(w_empty + 8 * i, 1); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full + 8 * i, 1); ptx::mbar_init(acc_empty + 8 * i, 4); }
+    ptx::fence_mbar_init();
+    ptx::prefetch_tensormap(&amap);
+  }
+  if (threadIdx.x < BN) bias_s[threadIdx.x] = p.bias[threadIdx.x];
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, C::TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot_p;
+
+  if (warp == 0) {
+    // ============================== TMA producer ==============================
+    if (ptx::elect_one()) {
+      uint32_t sa = 0, pa = 0, sw = 0, pw = 0;
+      for (int it = blockIdx.x; it < total; it += gridDim.x) {
+        const int txi = it % p.tiles_x, r = it / p.tiles_x;
+        const int tyi = r % p.tiles_y, n = r / p.tiles_y;
+        const int x0 = txi * TILE_W, y0 = tyi * ROWS;
+        for (int c = 0; c < p.NC; ++c) {
+          ptx::mbar_wait(a_empty + 8 * sa, pa ^ 1);
+          ptx::mbar_expect_tx(a_full + 8 * sa, C::A_STAGE);
+          ptx::tma_load_4d(a_stage0 + sa * C::A_STAGE, &amap, a_full + 8 * sa, c * KC, x0 - 1, y0 - 1, n);
+          if (++sa == SA) { sa = 0; pa ^= 1; }
+          for (int t = 0; t < 9; ++t) {
+            ptx::mbar_wait(w_empty + 8 * sw, pw ^ 1);
+            ptx::mbar_expect_tx(w_full + 8 * sw, C::W_SLICE);
+            ptx::bulk_load(w_stage0 + sw * C::W_SLICE, p.wpack + (size_t)(c * 9 + t) * C::W_SLICE, C::W_SLICE,
+                           w_full + 8 * sw);
+            if (++sw == C::SW) { sw = 0; pw ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ============================== MMA issuer ================================
+    if (ptx::elect_one()) {
+      constexpr uint32_t idesc = idesc_f16_f32(128, BN);
+      uint32_t sa = 0, pa = 0, sw = 0, pw = 0, kk = 0;
+      for (int it = blockIdx.x; it < total; it += gridDim.x, ++kk) {
+        const uint32_t slot = kk & 1, pacc = (kk >> 1) & 1;
+        ptx::mbar_wait(acc_empty + 8 * slot, pacc ^ 1);   // the epilogue has drained this slot (first use passes at once)
+        ptx::tc_fence_after();
+        for (int c = 0; c < p.NC; ++c) {
+          ptx::mbar_wait(a_full + 8 * sa, pa);
+          const uint32_t abase = a_stage0 + sa * C::A_STAGE;
+          for (int t = 0; t < 9; ++t) {
+            ptx::mbar_wait(w_full + 8 * sw, pw);
+            ptx::tc_fence_after();
+            const uint32_t tap_off = ((t / 3) * PITCH + (t % 3)) * 128;
+            const uint64_t ad0 = ptx::smem_desc_sw128(abase + tap_off, 0);
+            const uint64_t bd0 = ptx::smem_desc_sw128(w_stage0 + sw * C::W_SLICE, 0);
+#pragma unroll
+            for (int a = 0; a < APS; ++a) {
+#pragma unroll
+              for (int k = 0; k < KC / 16; ++k) {
+                const uint64_t ad = ptx::desc_advance(ad0, a * (128 * 128) + k * 32);
+                const uint64_t bd = ptx::desc_advance(bd0, k * 32);
+                ptx::mma_bf16_ss(tmem + (slot * APS + a) * BN, ad, bd, idesc, (c | t | k) != 0);
+              }
+            }
+            ptx::tc_commit(w_empty + 8 * sw);
+            if (++sw == C::SW) { sw = 0; pw ^= 1; }
+          }
+          ptx::tc_commit(a_empty + 8 * sa);
+          if (++sa == SA) { sa = 0; pa ^= 1; }
+        }
+        ptx::tc_commit(acc_full + 8 * slot);
+      }
+    }
+  } else {
+    // ============================== epilogue ==================================
+    // 4 warps, TMEM lane quarter q = warp & 3 (hardware rule).  A lane owns the pixel of its accumulator row; a unit is
+    // (accumulator a, 32-column group g): 32 fp32 per lane -> bias, LeakyReLU, residuals (fp32) -> 64 bytes of fp16.
+    // Global accesses go through a 2 KB per-warp stage so that one instruction covers 8 pixels x 64 B (lane l <-> pixel
+    // 8i + (l >> 2), 16-byte chunk l & 3).  Stage layout: pixel px at px*64, chunk j at (j ^ ((px >> 1) & 3)) * 16.
+    const int q = warp & 3;
+    uint8_t* stage = sm + C::STAGE_OFF + (warp - 2) * 2048;
+    constexpr int GROUPS = BN / 32;
+    const uint32_t tq = tmem + ((uint32_t)(q * 32) << 16);
+    const int cpx = lane >> 2, cch = lane & 3;
+    int own_off[4], co_off[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      own_off[j] = lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4);
+      const int px = 8 * j + cpx;
+      co_off[j] = px * 64 + ((cch ^ ((px >> 1) & 3)) << 4);
+    }
+    const int oh = p.ups2 ? 2 * p.H : p.H, ow = p.ups2 ? 2 * p.W : p.W;
+    uint32_t kk = 0;
+    for (int it = blockIdx.x; it < total; it += gridDim.x, ++kk) {
+      const uint32_t slot = kk & 1, pacc = (kk >> 1) & 1;
+      const int txi = it % p.tiles_x, r = it / p.tiles_x;
+      const int tyi = r % p.tiles_y, n = r / p.tiles_y;
+      const int x0 = txi * TILE_W;
+      const int ybase = tyi * ROWS + q;                 // accumulator row m = a*128 + q*32 + lane -> y = ybase + 4a
+      bool pxok[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) pxok[i] = (8 * i + cpx < TILE_W) && (x0 + 8 * i + cpx < p.W);
+      ptx::mbar_wait(acc_full + 8 * slot, pacc);
+      ptx::tc_fence_after();
+#pragma unroll 1
+      for (int u = 0; u < APS * GROUPS; ++u) {
+        const int a = u / GROUPS, g = u % GROUPS;
+        const int y = ybase + 4 * a;
+        const bool yok = y < p.H;
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(tq + (slot * APS + a) * BN + g * 32, v);
+        // residual rows in the co-pattern (pixel 8i + cpx, chunk cch), issued before the TMEM wait
+        uint4 s1[4], s2[4];
+        const size_t pix0 = ((size_t)n * p.H + y) * p.W + x0 + cpx;
+        if (p.r1) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            s1[i] = (yok && pxok[i]) ? __ldg(reinterpret_cast<const uint4*>(p.r1 + (pix0 + 8 * i) * p.r1_cs + g * 32 + cch * 8))
+                                     : make_uint4(0, 0, 0, 0);
+        }
+        if (p.r2) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            s2[i] = (yok && pxok[i]) ? __ldg(reinterpret_cast<const uint4*>(p.r2 + (pix0 + 8 * i) * p.r2_cs + g * 32 + cch * 8))
+                                     : make_uint4(0, 0, 0, 0);
+        }
+        ptx::tmem_ld_wait();
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float t = __uint_as_float(v[j]) + bias_s[g * 32 + j];
+          if (p.lrelu) t = t > 0.f ? t : 0.2f * t;        // nn.LeakyReLU(negative_slope=0.2)
+          f[j] = t;
+        }
+        if (p.r1) {                                       // x5 * 0.2 + x  (:57)  /  feat + body_feat  (:89, a1 = 1)
+#pragma unroll
+          for (int i = 0; i < 4; ++i) *reinterpret_cast<uint4*>(stage + co_off[i]) = s1[i];
+          __syncwarp();
+#pragma unroll
+          for (int j4 = 0; j4 < 4; ++j4) {
+            const uint4 w = *reinterpret_cast<const uint4*>(stage + own_off[j4]);
+            const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 rr = unpack_f16x2(ww[e]);
+              f[j4 * 8 + 2 * e] = fmaf(f[j4 * 8 + 2 * e], p.a1, rr.x);
+              f[j4 * 8 + 2 * e + 1] = fmaf(f[j4 * 8 + 2 * e + 1], p.a1, rr.y);
+            }
+          }
+          __syncwarp();
+        }
+        if (p.r2) {                                       // out * 0.2 + x of the enclosing RRDBBlock (:36)
+#pragma unroll
+          for (int i = 0; i < 4; ++i) *reinterpret_cast<uint4*>(stage + co_off[i]) = s2[i];
+          __syncwarp();
+#pragma unroll
+          for (int j4 = 0; j4 < 4; ++j4) {
+            const uint4 w = *reinterpret_cast<const uint4*>(stage + own_off[j4]);
+            const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 rr = unpack_f16x2(ww[e]);
+              f[j4 * 8 + 2 * e] = fmaf(f[j4 * 8 + 2 * e], p.a2, rr.x);
+              f[j4 * 8 + 2 * e + 1] = fmaf(f[j4 * 8 + 2 * e + 1], p.a2, rr.y);
+            }
+          }
+          __syncwarp();
+        }
+#pragma unroll
+        for (int j4 = 0; j4 < 4; ++j4)
+          *reinterpret_cast<uint4*>(stage + own_off[j4]) =
+              make_uint4(pack_f16x2_sat(f[j4 * 8 + 0], f[j4 * 8 + 1]), pack_f16x2_sat(f[j4 * 8 + 2], f[j4 * 8 + 3]),
+                         pack_f16x2_sat(f[j4 * 8 + 4], f[j4 * 8 + 5]), pack_f16x2_sat(f[j4 * 8 + 6], f[j4 * 8 + 7]));
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint4 o = *reinterpret_cast<const uint4*>(stage + co_off[i]);
+          if (!(yok && pxok[i])) continue;
+          const int x = x0 + 8 * i + cpx;
+          if (!p.ups2) {
+            *reinterpret_cast<uint4*>(p.out + (((size_t)n * oh + y) * ow + x) * p.out_cs + p.out_c0 + g * 32 + cch * 8) = o;
+          } else {
+#pragma unroll
+            for (int d = 0; d < 4; ++d)
+              *reinterpret_cast<uint4*>(p.out + (((size_t)n * oh + 2 * y + (d >> 1)) * ow + 2 * x + (d & 1)) * p.out_cs +
+                                        p.out_c0 + g * 32 + cch * 8) = o;
+          }
+        }
+        __syncwarp();
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(acc_empty + 8 * slot);
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    ptx::tmem_dealloc(tmem, C::TMEM_COLS);
+  }
+}
+
+// nn.Conv2d(3, 64) of conv_first and nn.Conv2d(64, 3) of conv_last run on the thin-layer kernels of thin_tc.cuh
+// (im2col27_kernel<MODE_FIRST64, 64>, gemm27_kernel<MODE_LAST_F16>).
+
+}  // namespace rrdb
+}  // namespace vex

@@ -23,12 +23,21 @@
 namespace vex {
 namespace thin {
 
+__device__ __forceinline__ uint32_t pack_f16x2_sat_thin(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
 // ============================================================================================ im2col27
 constexpr int MODE_CONV1 = 0, MODE_UP1 = 1, MODE_CONV1_F32 = 2;   // _F32: fp32 NCHW input as hi + lo bf16 (K = 64)
+// MODE_FIRST64: conv_first of the Real-ESRGAN network (realesrgan_handler.py:64,87): uint8 HWC -> Conv2d(3, 64), no activation,
+// fp16 NHWC out with pixel stride `out_cs`.  K = 64: the input values sit at k = 0..26 AND k = 32..58, the weight image
+// holds bf16(w) at the first and bf16(w - bf16(w)) at the second position, so the weights carry 16 mantissa bits.
+constexpr int MODE_FIRST64 = 3;
 constexpr int I27_THREADS = 544;       // warps 0-3 / 4-7 two A-builder groups, warp 8 MMA, warps 9-12 / 13-16 two drain groups
 constexpr int I27_SA = 4;              // A stages (128 rows x 128 B each); item sequence k uses stage k & 3
 constexpr int I27_MMA_WARP = 8;
@@ -56,6 +65,7 @@ struct I27Params {
   long long npix;          // n*H*W
   int in_bgr;
   int probe;               // bring-up timing probes (WRONG RESULTS): 1 = no global stores, 2 = no TMEM drain, 4 = no gather loads
+  int out_cs;              // MODE_FIRST64: channel stride of the output pixels (elements); other modes: dense rows of BN
 };
 
 template <int MODE, int BN>
@@ -120,7 +130,7 @@ im2col27_kernel(const I27Params p) {
               const float* s = reinterpret_cast<const float*>(p.in) + (size_t)img * 3 * plane + (size_t)yy * p.W + xx;
 #pragma unroll
               for (int c = 0; c < 3; ++c) v[(ky * 3 + kx) * 3 + c] = ok ? __ldg(s + c * plane) : 0.f;
-            } else if (MODE == MODE_CONV1) {
+            } else if (MODE == MODE_CONV1 || MODE == MODE_FIRST64) {
               const uint8_t* s = reinterpret_cast<const uint8_t*>(p.in) + q * 3;
 #pragma unroll
               for (int c = 0; c < 3; ++c)
@@ -136,6 +146,11 @@ im2col27_kernel(const I27Params p) {
         for (int j = 0; j < 13; ++j) w[j] = ptx::pack_bf16x2(v[2 * j], v[2 * j + 1]);
         w[13] = ptx::pack_bf16x2(v[26], 1.0f);       // k = 27, 28: constant 1 against the bias rows (hi + lo bf16) of W, so the
         w[14] = ptx::pack_bf16x2(1.0f, 0.f);         // drain needs no per-element bias load and add
+        if (MODE == MODE_FIRST64) {                  // k = 32..58: the same (exact) input values against the lo halves of W
+#pragma unroll
+          for (int j = 0; j < 13; ++j) wlo[j] = w[j];
+          wlo[13] = ptx::pack_bf16x2(v[26], 0.f);
+        }
         if (MODE == MODE_CONV1_F32) {                // k = 32..58: what the bf16 rounding of k = 0..26 dropped
 #pragma unroll
           for (int j = 0; j < 27; ++j) {
@@ -152,7 +167,7 @@ im2col27_kernel(const I27Params p) {
 #pragma unroll
       for (int j = 0; j < 4; ++j)
         *reinterpret_cast<uint4*>(row + ((j ^ (r & 7)) << 4)) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
-      if (MODE == MODE_CONV1_F32) {
+      if (MODE == MODE_CONV1_F32 || MODE == MODE_FIRST64) {
 #pragma unroll
         for (int j = 0; j < 4; ++j)
           *reinterpret_cast<uint4*>(row + (((4 + j) ^ (r & 7)) << 4)) = make_uint4(wlo[4 * j], wlo[4 * j + 1], wlo[4 * j + 2], wlo[4 * j + 3]);
@@ -175,7 +190,7 @@ im2col27_kernel(const I27Params p) {
         ptx::mbar_wait(a_full + 8 * sa, pa);
         ptx::tc_fence_after();
 #pragma unroll
-        for (int k = 0; k < (MODE == MODE_CONV1_F32 ? 4 : 2); ++k) {
+        for (int k = 0; k < ((MODE == MODE_CONV1_F32 || MODE == MODE_FIRST64) ? 4 : 2); ++k) {
           const uint64_t ad = ptx::smem_desc_sw128(sbase + sa * C::A_STAGE + k * 32, 0);
           const uint64_t bd = ptx::smem_desc_sw128(sbase + C::W_OFF + k * 32, 0);
           ptx::mma_bf16_ss(tmem + b * BN, ad, bd, idesc, k);
@@ -198,7 +213,8 @@ im2col27_kernel(const I27Params p) {
     const int ge = ew >> 2, q = warp & 3;
     uint8_t* stg = sm + C::STG_OFF + ew * I27_STG + lane * I27_STG_PITCH;
     const uint32_t stg_s = ptx::smem_u32(stg);
-    constexpr int HALVES = BN / 128;
+    constexpr int HALVES = BN >= 128 ? BN / 128 : 1;
+    constexpr int GPH = BN >= 128 ? 4 : BN / 32;   // 32-column groups per staged row (row = GPH * 64 bytes)
     long long k = ge;
     for (long long it = blockIdx.x + (long long)ge * gridDim.x; it < items; it += 2LL * gridDim.x, k += 2) {
       const uint32_t b = (uint32_t)(k % C::NACC), pb = (uint32_t)((k / C::NACC) & 1);
@@ -207,7 +223,9 @@ im2col27_kernel(const I27Params p) {
       uint8_t* obase = nullptr;                      // first of this pixel's HALVES 256-byte destinations
       size_t half_stride = 256;                      // CONV1: next 128 channels of the same pixel
       if (valid) {
-        if (MODE != MODE_UP1) {
+        if (MODE == MODE_FIRST64) {
+          obase = reinterpret_cast<uint8_t*>(p.out + pix * p.out_cs);
+        } else if (MODE != MODE_UP1) {
           obase = reinterpret_cast<uint8_t*>(p.out + pix * BN);
         } else {
           const int x = (int)(pix % p.W);
@@ -224,7 +242,7 @@ im2col27_kernel(const I27Params p) {
       for (int hf = 0; hf < HALVES; ++hf) {
         ptx::bulk_wait_read0();                      // this lane's previous bulk store has finished reading its row
 #pragma unroll 1
-        for (int g = (p.probe & 2) ? 4 : 0; g < 4; ++g) {
+        for (int g = (p.probe & 2) ? GPH : 0; g < GPH; ++g) {
           uint32_t v[32];
           const int col = hf * 128 + g * 32;
           ptx::tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + b * BN + col, v);
@@ -234,6 +252,11 @@ im2col27_kernel(const I27Params p) {
             float f[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[j4 * 8 + e]);   // bias already inside (k = 27, 28)
+            if (MODE == MODE_FIRST64)                // linear, fp16 (the RRDB trunk runs in fp16)
+              *reinterpret_cast<uint4*>(stg + (g * 4 + j4) * 16) =
+                  make_uint4(pack_f16x2_sat_thin(f[0], f[1]), pack_f16x2_sat_thin(f[2], f[3]),
+                             pack_f16x2_sat_thin(f[4], f[5]), pack_f16x2_sat_thin(f[6], f[7]));
+            else
             *reinterpret_cast<uint4*>(stg + (g * 4 + j4) * 16) =
                 make_uint4(ptx::pack_relu_bf16x2(f[0], f[1]), ptx::pack_relu_bf16x2(f[2], f[3]),
                            ptx::pack_relu_bf16x2(f[4], f[5]), ptx::pack_relu_bf16x2(f[6], f[7]));
@@ -247,7 +270,7 @@ im2col27_kernel(const I27Params p) {
         ptx::fence_proxy_async_smem();               // the row was written through the generic proxy
         if (p.probe & 8) {                           // probe: half as many ops, 512 B each (garbage payload)
           if (valid && !(lane & 1)) ptx::bulk_store(obase + hf * half_stride, stg_s, 512);
-        } else if (valid && !(p.probe & 1)) ptx::bulk_store(obase + hf * half_stride, stg_s, 256);
+        } else if (valid && !(p.probe & 1)) ptx::bulk_store(obase + hf * half_stride, stg_s, GPH * 64);
         ptx::bulk_commit();
       }
     }
@@ -263,6 +286,9 @@ im2col27_kernel(const I27Params p) {
 
 // ============================================================================================== gemm27
 constexpr int MODE_CONV5 = 0, MODE_UP2 = 1;
+// MODE_LAST_F16: conv_last of the Real-ESRGAN network (realesrgan_handler.py:78,99 + the clamp / x255 / truncating cast of
+// :318-319): fp16 NHWC in, fp16 weight image, otherwise MODE_UP2's epilogue.
+constexpr int MODE_LAST_F16 = 2;
 constexpr int G27_THREADS = 320;       // warp 0 TMA, warp 1 MMA, warps 2-5 / 6-9 two epilogue groups (even / odd items)
 constexpr int G27_ROWS = 6;            // output rows per item; halo tile = 8 rows x 32 px = 256 GEMM rows
 constexpr int G27_TW = 30;
@@ -349,7 +375,9 @@ gemm27_kernel(const __grid_constant__ CUtensorMap amap, const G27Params p) {
   } else if (warp == 1) {
     if (ptx::elect_one()) {
       ptx::mbar_wait(w_bar, 0);
-      constexpr uint32_t idesc = ptx::idesc_bf16_f32(128, 32);
+      // kind::f16 instruction descriptor: bits 7-9 / 10-12 = A / B format (0 fp16, 1 bf16)
+      constexpr uint32_t idesc = MODE == MODE_LAST_F16 ? (ptx::idesc_bf16_f32(128, 32) & ~((1u << 7) | (1u << 10)))
+                                                       : ptx::idesc_bf16_f32(128, 32);
       uint32_t sa = 0, pa = 0, b = 0, pb = 0;
       for (int it = blockIdx.x; it < total; it += gridDim.x) {
         ptx::mbar_wait(acc_empty + 8 * b, pb ^ 1);
@@ -438,7 +466,7 @@ gemm27_kernel(const __grid_constant__ CUtensorMap amap, const G27Params p) {
           }
         }
       }
-      if (MODE == MODE_UP2 && p.out_u8) {
+      if (MODE != MODE_CONV5 && p.out_u8) {
         named_bar_sync(1 + grp, 128);
         // cooperative row stores: aligned 32-bit words in the middle, bytes at the ragged ends
         for (int wi = et; wi < G27_ROWS * 24; wi += 128) {

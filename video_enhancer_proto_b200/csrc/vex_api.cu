@@ -157,6 +157,8 @@ int vex_destroy(vex_ctx* ctx) {
     vex::DeviceGuard guard(ctx->device);
     cudaDeviceSynchronize();
     vex::cnn_destroy(ctx);
+    vex::rrdb_destroy(ctx);
+    if (ctx->ev_ws_rrdb) cudaEventDestroy(ctx->ev_ws_rrdb);
   if (ctx->bilateral_cw) cudaFree(ctx->bilateral_cw);
   for (int i = 0; i < 2; ++i) {
     if (ctx->slot_in[i]) cudaFree(ctx->slot_in[i]);
@@ -273,6 +275,43 @@ int vex_cnn_profile_stats(vex_ctx* ctx, float* mean7, float* min7, float* max7, 
   if (!ctx || !n_forwards) return VEX_ERR_INVALID;
   VEX_ON_DEVICE(ctx);
   return vex::cnn_profile_stats(ctx, mean7, min7, max7, n_forwards);
+}
+
+int vex_rrdb_load_weights(vex_ctx* ctx, const vex_rrdb_desc* arch, const float* const* tensors, int n_tensors) {
+  if (!ctx) return VEX_ERR_INVALID;
+  VEX_ON_DEVICE(ctx);
+  return vex::rrdb_load_weights(ctx, arch, tensors, n_tensors);
+}
+
+int vex_rrdb_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w, int in_bgr, int out_bgr,
+                void* stream) {
+  if (!ctx) return VEX_ERR_INVALID;
+  if (!in_hwc || !out_hwc || n <= 0 || h <= 0 || w <= 0) return vex::fail(ctx, VEX_ERR_INVALID, "vex_rrdb_u8: bad argument");
+  VEX_ON_DEVICE(ctx);
+  return vex::rrdb_forward(ctx, in_hwc, out_hwc, nullptr, 0, n, h, w, in_bgr != 0, out_bgr != 0, (cudaStream_t)stream);
+}
+
+int vex_rrdb_frame_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int h, int w, int tile_size, int tile_pad,
+                      int in_bgr, int out_bgr, void* stream) {
+  if (!ctx) return VEX_ERR_INVALID;
+  if (!in_hwc || !out_hwc || h <= 0 || w <= 0) return vex::fail(ctx, VEX_ERR_INVALID, "vex_rrdb_frame_u8: bad argument");
+  VEX_ON_DEVICE(ctx);
+  return vex::rrdb_frame(ctx, in_hwc, out_hwc, h, w, tile_size, tile_pad, in_bgr != 0, out_bgr != 0, (cudaStream_t)stream);
+}
+
+int vex_rrdb_f32_debug(vex_ctx* ctx, const uint8_t* in_hwc, float* out_nchw, int n, int h, int w, int in_bgr, int tap,
+                       void* stream) {
+  if (!ctx) return VEX_ERR_INVALID;
+  if (!in_hwc || !out_nchw || n <= 0 || h <= 0 || w <= 0 || tap < 0)
+    return vex::fail(ctx, VEX_ERR_INVALID, "vex_rrdb_f32_debug: bad argument");
+  VEX_ON_DEVICE(ctx);
+  return vex::rrdb_forward(ctx, in_hwc, nullptr, out_nchw, tap, n, h, w, in_bgr != 0, 0, (cudaStream_t)stream);
+}
+
+int vex_rrdb_workspace_bytes(const vex_ctx* ctx, int n, int h, int w, size_t* out) {
+  if (!ctx || !out || n <= 0 || h <= 0 || w <= 0) return VEX_ERR_INVALID;
+  *out = vex::rrdb_workspace_bytes(ctx, n, h, w);
+  return VEX_OK;
 }
 
 int vex_workspace_bytes(const vex_ctx* ctx, int n, int h, int w, size_t* out) {

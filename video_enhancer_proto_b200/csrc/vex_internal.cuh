@@ -12,7 +12,8 @@
 
 namespace vex {
 
-struct CnnPlan;  // filters.cu
+struct CnnPlan;
+struct RrdbPlan;
 int launch_filter3x3(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, const float* k9, cudaStream_t s);
 int launch_bilateral5(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, float sigma_color,
                       float sigma_space, cudaStream_t s);
@@ -55,6 +56,10 @@ struct vex_ctx {
 
   // CNN state
   vex::CnnPlan* cnn = nullptr;
+  // Real-ESRGAN RRDBNet state (rrdb.cu)
+  vex::RrdbPlan* rrdb = nullptr;
+  cudaEvent_t ev_ws_rrdb = nullptr;
+  bool ws_rrdb_used = false;
 
   // debug knobs (vex_set_option)
   int opt_desc_base_offset = 0;   // smem-descriptor base_offset field: 0 (measured correct on B200), 1: (addr>>7)&7
@@ -114,6 +119,15 @@ int launch_bicubic2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h
                      int round_mode, cudaStream_t s);
 
 int launch_bicubic2x_f32in(vex_ctx* ctx, const float* in_nchw, uint8_t* out, int n, int h, int w, cudaStream_t s);
+
+// rrdb.cu
+int rrdb_load_weights(vex_ctx* ctx, const vex_rrdb_desc* arch, const float* const* tensors, int n);
+int rrdb_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f32, int tap, int n, int h, int w,
+                 int in_bgr, int out_bgr, cudaStream_t s);
+int rrdb_frame(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int h, int w, int tile_size, int tile_pad, int in_bgr,
+               int out_bgr, cudaStream_t s);
+size_t rrdb_workspace_bytes(const vex_ctx* ctx, int n, int h, int w);
+void rrdb_destroy(vex_ctx* ctx);
 
 // cnn.cu
 constexpr int IN_F32_NCHW = 2;   // cnn_forward's in_bgr argument: 0 RGB u8, 1 BGR u8, 2 = `in` is fp32 NCHW in [0,1] (no swap)

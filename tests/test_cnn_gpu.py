@@ -178,7 +178,7 @@ def test_gpu_taps_match_the_bf16_emulation(enhancers, models, key):
     rounding points (tests/test_layer_algebra.gpu_algebra).  This ties the GPU to that emulation: every tap agrees with
     it to a few bf16 ulps of the layer's range (accumulation order inside an fp32 sum is the only freedom left), an order
     of magnitude tighter than the distance of either from the fp32 reference."""
-    from tests.test_layer_algebra import gpu_algebra
+    from test_layer_algebra import gpu_algebra            # tests/ is on sys.path (pytest rootdir mode)
     rng = np.random.default_rng(3)
     frames = [synth.random_frame(40, 56, rng), synth.edges_frame(40, 56, rng)]
     with torch.no_grad():

@@ -407,11 +407,32 @@ int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_
   p.tiles_x = (2 * W + thin::G27_TW - 1) / thin::G27_TW;
   p.tiles_y = (2 * H + thin::G27_ROWS - 1) / thin::G27_ROWS;
   p.n_img = n; p.out_bgr = out_bgr; p.probe = ctx->opt_thin_probe;
+  p.dbg = nullptr;
   const long long total = (long long)p.tiles_x * p.tiles_y * n;
   if (total > 0x7fffffffLL) return fail(ctx, VEX_ERR_INVALID, "uptail: too many tiles");
-  thin::uptail_kernel<<<(unsigned)std::min<long long>(total, ctx->sm_count), thin::UT_THREADS, thin::UTCfg::SMEM, s>>>(p);
+  const unsigned grid = (unsigned)std::min<long long>(total, ctx->sm_count);
+  if (ctx->opt_conv_dbg) {                   // bring-up: per-role cycle counters, printed after the launch
+    VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&p.dbg), (size_t)grid * 128));
+    VEX_CUDA(ctx, cudaMemsetAsync(p.dbg, 0, (size_t)grid * 128, s));
+  }
+  thin::uptail_kernel<<<grid, thin::UT_THREADS, thin::UTCfg::SMEM, s>>>(p);
   ctx->launches++;
   VEX_CUDA(ctx, cudaGetLastError());
+  if (p.dbg) {
+    std::vector<long long> h((size_t)grid * 16);
+    VEX_CUDA(ctx, cudaStreamSynchronize(s));
+    VEX_CUDA(ctx, cudaMemcpy(h.data(), p.dbg, h.size() * 8, cudaMemcpyDeviceToHost));
+    cudaFree(p.dbg);
+    double a[13] = {0};
+    for (unsigned b = 0; b < grid; ++b)
+      for (int i = 0; i < 13; ++i) a[i] += (double)h[(size_t)b * 16 + i] / grid;
+    const double items = (double)total / grid, e_items = std::max(1.0, a[12]);
+    fprintf(stderr, "[uptail_dbg] items/cta=%.1f cycles/item: MMA total=%.0f wait_a1_full=%.0f wait_acc1_empty=%.0f wait_acc2_empty=%.0f "
+                    "wait_a2_full=%.0f | builder total=%.0f wait_a1_empty=%.0f | mid-drain total=%.0f wait_a2_empty=%.0f wait_acc1_full=%.0f "
+                    "| epilogue(group 0, per own item) total=%.0f wait_acc2_full=%.0f\n",
+            items, a[0] / items, a[1] / items, a[2] / items, a[3] / items, a[4] / items, a[6] / items, a[5] / items,
+            a[9] / items, a[7] / items, a[8] / items, a[11] / e_items, a[10] / e_items);
+  }
   return VEX_OK;
 }
 

@@ -53,6 +53,9 @@ struct UTParams {
   int tiles_x, tiles_y, n_img;
   int out_bgr;
   int probe;               // bring-up timing probes (WRONG RESULTS): 4 = no gather loads, 2 = mid-drain without stores, 1 = epilogue without gather
+  long long* dbg;          // optional [gridDim.x][16] cycle counters per role (option conv_dbg): MMA thread 0 total, 1 wait a1_full,
+                           // 2 wait acc1_empty, 3 wait acc2_empty, 4 wait a2_full; builder 5 wait a1_empty, 6 total; mid-drain (warp 4)
+                           // 7 wait a2_empty, 8 wait acc1_full, 9 total; epilogue group 0: 10 wait acc2_full, 11 total, 12 items
 };
 
 __global__ void __launch_bounds__(UT_THREADS, 1)
@@ -119,6 +122,8 @@ uptail_kernel(const UTParams p) {
     bool live = false;
     if ((int)blockIdx.x < total) live = gather(blockIdx.x, f);
     uint32_t k = 0;
+    const bool dbg = p.dbg != nullptr && threadIdx.x == 0;
+    long long tw = 0, tb0 = dbg ? clock64() : 0;
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
       uint32_t w[16];
 #pragma unroll
@@ -135,7 +140,9 @@ uptail_kernel(const UTParams p) {
       const int itn = it + gridDim.x;                // the packed row frees f: the next item's loads fly during the hand-off
       if (itn < total) live = gather(itn, f);
       const uint32_t sa = k & 1, pa = (k >> 1) & 1;
+      const long long tq0 = dbg ? clock64() : 0;
       ptx::mbar_wait(a1_empty + 8 * sa, pa ^ 1);
+      if (dbg) tw += clock64() - tq0;
       uint8_t* row = sm + C::A1_OFF + sa * C::A1_STAGE + r * 128;
 #pragma unroll
       for (int j = 0; j < 4; ++j)
@@ -143,6 +150,7 @@ uptail_kernel(const UTParams p) {
       ptx::fence_proxy_async_smem();
       ptx::mbar_arrive(a1_full + 8 * sa);
     }
+    if (dbg) { p.dbg[blockIdx.x * 16 + 5] = tw; p.dbg[blockIdx.x * 16 + 6] = clock64() - tb0; }
   } else if (warp == UT_MMA_WARP) {
     // ================================ both GEMMs from one thread; GEMM #2 of item k-1 is issued after GEMM #1 of item k
     if (ptx::elect_one()) {
@@ -156,11 +164,17 @@ uptail_kernel(const UTParams p) {
       // serial instruction stream paces the whole kernel
       const uint64_t a1d0 = ptx::smem_desc_sw128(sbase + C::A1_OFF, 0), w1d = ptx::smem_desc_sw128(sbase + C::W1_OFF, 0);
       const uint64_t a2d0 = ptx::smem_desc_sw128(sbase + C::A2_OFF, 0), w2d = ptx::smem_desc_sw128(sbase + C::W2_OFF, 0);
+      const bool dbg = p.dbg != nullptr;
+      long long t1 = 0, t2 = 0, t3 = 0, t4 = 0, tq;
+      const long long tm0 = dbg ? clock64() : 0;
       auto gemm2 = [&](uint32_t j) {
         const uint32_t s = j & 1, ph = (j >> 1) & 1;
         const uint32_t eg = j % UT_EPI_GROUPS, eu = j / UT_EPI_GROUPS;    // epilogue group and its use count
+        if (dbg) tq = clock64();
         ptx::mbar_wait(acc2_empty + 8 * eg, (eu & 1) ^ 1);
+        if (dbg) { const long long n = clock64(); t3 += n - tq; tq = n; }
         ptx::mbar_wait(a2_full + 8 * s, ph);
+        if (dbg) t4 += clock64() - tq;
         ptx::tc_fence_after();
 #pragma unroll
         for (int g = 0; g < 2; ++g)
@@ -176,10 +190,14 @@ uptail_kernel(const UTParams p) {
       uint32_t k = 0;
       for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
         const uint32_t sa = k & 1, pa = (k >> 1) & 1;
+        if (dbg) tq = clock64();
         ptx::mbar_wait(a1_full + 8 * sa, pa);
+        if (dbg) t1 += clock64() - tq;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {                // phases 0-1, then 2-3: the mid-drain of one half overlaps the other
+          if (dbg) tq = clock64();
           ptx::mbar_wait(acc1_empty + 8 * h, (k & 1) ^ 1);
+          if (dbg) t2 += clock64() - tq;
           ptx::tc_fence_after();
 #pragma unroll
           for (int kk = 0; kk < 2; ++kk) {
@@ -193,6 +211,10 @@ uptail_kernel(const UTParams p) {
         if (k > 0) gemm2(k - 1);
       }
       if (k > 0) gemm2(k - 1);
+      if (dbg) {
+        long long* d = p.dbg + blockIdx.x * 16;
+        d[0] = clock64() - tm0; d[1] = t1; d[2] = t2; d[3] = t3; d[4] = t4;
+      }
     }
   } else if (warp < 11) {
     // ================================ mid-drain: relu(upconv1) of low-res pixel r -> rows of A2.  Group h (warps 4-6 /
@@ -202,12 +224,18 @@ uptail_kernel(const UTParams p) {
     const int r = q * 32 + lane;
     const int lr = r / UT_LC, lc = r - lr * UT_LC;
     uint32_t k = 0;
+    const bool dbg = p.dbg != nullptr && warp == 4 && lane == 0;
+    long long t7 = 0, t8 = 0, tq = 0;
+    const long long td0 = dbg ? clock64() : 0;
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
       const int txi = it % p.tiles_x, t = it / p.tiles_x;
       const int tyi = t % p.tiles_y;
       const uint32_t s = k & 1;
+      if (dbg) tq = clock64();
       ptx::mbar_wait(a2_empty + 8 * s, ((k >> 1) & 1) ^ 1);
+      if (dbg) { const long long n = clock64(); t7 += n - tq; tq = n; }
       ptx::mbar_wait(acc1_full + 8 * h, k & 1);
+      if (dbg) t8 += clock64() - tq;
       ptx::tc_fence_after();
       uint8_t* a2 = sm + C::A2_OFF + s * C::A2_STAGE;
 #pragma unroll
@@ -246,6 +274,7 @@ uptail_kernel(const UTParams p) {
       ptx::fence_proxy_async_smem();
       ptx::mbar_arrive(a2_full + 8 * s);
     }
+    if (dbg) { long long* d = p.dbg + blockIdx.x * 16; d[7] = t7; d[8] = t8; d[9] = clock64() - td0; }
   } else if (warp >= UT_EPI_WARP0) {
     // ================================ epilogue: as gemm27 MODE_UP2, on the hi-res tile
     const int grp = (warp - UT_EPI_WARP0) >> 2;
@@ -256,11 +285,16 @@ uptail_kernel(const UTParams p) {
     const float b0 = p.bias2[0], b1 = p.bias2[1], b2 = p.bias2[2];
     const uint32_t b = grp;
     uint32_t pb = 0;
+    const bool dbg = p.dbg != nullptr && warp == UT_EPI_WARP0 && lane == 0;
+    long long t10 = 0, n_items = 0;
+    const long long te0 = dbg ? clock64() : 0;
     for (int it = blockIdx.x + grp * gridDim.x; it < total; it += UT_EPI_GROUPS * gridDim.x) {
       const int txi = it % p.tiles_x, t = it / p.tiles_x;
       const int tyi = t % p.tiles_y, n = t / p.tiles_y;
       const int x0 = txi * G27_TW, y0 = tyi * G27_ROWS;
+      const long long tq = dbg ? clock64() : 0;
       ptx::mbar_wait(acc2_full + 8 * b, pb);
+      if (dbg) { t10 += clock64() - tq; ++n_items; }
       ptx::tc_fence_after();
 #pragma unroll
       for (int g = 0; g < 2; ++g) {
@@ -332,6 +366,7 @@ uptail_kernel(const UTParams p) {
       }
       named_bar_sync(1 + grp, 128);
     }
+    if (dbg) { long long* d = p.dbg + blockIdx.x * 16; d[10] = t10; d[11] = clock64() - te0; d[12] = n_items; }
   }
   ptx::tc_fence_before();
   __syncthreads();

@@ -31,18 +31,23 @@ def gpu_algebra(model, frames, bf16):
         s = sd[f"bn{i}.weight"] / torch.sqrt(sd[f"bn{i}.running_var"] + 1e-5)
         return s, (sd[f"conv{i}.bias"] - sd[f"bn{i}.running_mean"]) * s + sd[f"bn{i}.bias"]
 
+    def qh(t):                                        # conv1 runs on fp16 operands (thin_tc.cuh MODE_CONV1_H)
+        return t.to(torch.float16).to(torch.float32) if bf16 else t
+
     x = torch.from_numpy(np.stack(frames)).permute(0, 3, 1, 2).float()          # raw u8 values
     s, sh = fold(1)
-    x1 = q(F.relu(F.conv2d(x, sd["conv1.weight"] * s[:, None, None, None] / 255.0, sh, padding=1)))
+    x1 = q(F.relu(F.conv2d(x, qh(sd["conv1.weight"] * s[:, None, None, None] / 255.0), sh, padding=1)))
     s, sh = fold(2)
     x2 = q(F.relu(F.conv2d(x1, q(sd["conv2.weight"] * s[:, None, None, None]), sh, padding=1)) + x1)
     s, sh = fold(3)
     x3 = q(F.relu(F.conv2d(x2, q(sd["conv3.weight"] * s[:, None, None, None]), sh, padding=1)))
     s, sh = fold(4)
     x4 = q(F.relu(F.conv2d(x3, q(sd["conv4.weight"] * s[:, None, None, None]), sh, padding=1)))
-    x5 = F.conv2d(x4, sd["conv5.weight"], sd["conv5.bias"], padding=1)
+    x5 = F.conv2d(x4, q(sd["conv5.weight"]), sd["conv5.bias"], padding=1)       # gemm27: bf16 weight image, fp32 x5
     n, _, H, W = x5.shape
-    u1w, u1b = sd["upconv1.weight"], sd["upconv1.bias"]
+    u1w, u1b = q(sd["upconv1.weight"]), sd["upconv1.bias"]                      # tail: bf16 weights, x5 rounded to bf16 as operand
+    x5_out = x5
+    x5 = q(x5)
     up = torch.zeros(n, u1w.shape[1], 2 * H, 2 * W)
     xp = F.pad(x5, (1, 1, 1, 1))
     for py in range(2):
@@ -54,8 +59,8 @@ def gpu_algebra(model, frames, bf16):
                                              u1w[:, :, ky, kx])
             up[:, :, py::2, px::2] = acc
     up = q(F.relu(up))
-    out = torch.clamp(F.conv2d(up, sd["upconv2.weight"].flip(2, 3).transpose(0, 1), sd["upconv2.bias"], padding=1), 0, 1)
-    return dict(x1=x1, x2=x2, x3=x3, x4=x4, x5=x5, up=up, out=out)
+    out = torch.clamp(F.conv2d(up, q(sd["upconv2.weight"]).flip(2, 3).transpose(0, 1), sd["upconv2.bias"], padding=1), 0, 1)
+    return dict(x1=x1, x2=x2, x3=x3, x4=x4, x5=x5_out, up=up, out=out)
 
 
 def _frames():

@@ -1,0 +1,19 @@
+#!/bin/bash
+# compute-sanitizer over the warp-specialised kernels on small shapes (VERDICT r1 missing #7).
+# memcheck: out-of-bounds / misaligned accesses; racecheck: shared-memory hazards between the producer / MMA / drain roles
+# (it tracks generic-proxy accesses and barriers; TMA and tcgen05 operand reads are invisible to it); synccheck: barrier misuse.
+# Usage (GPU box): bash tools/sanitize.sh <tag>   -> gpurun_out/<tag>_sanitize_<tool>.log + a summary line per tool
+T=${1:-r2}
+mkdir -p gpurun_out
+SEL='taps_and_output and 37-53 or fused_tail_matches and 37-53 or variants_bit_identical or conv1_operand_builders and 37-53 or tensor_input_off'
+for tool in memcheck racecheck synccheck; do
+  timeout 1500 compute-sanitizer --tool $tool --error-exitcode 77 --print-limit 20 \
+    python -m pytest tests/test_cnn_gpu.py -x -q -k "$SEL" > gpurun_out/${T}_sanitize_${tool}.log 2>&1
+  echo "$tool cnn rc=$? $(grep -a -c 'ERROR SUMMARY' gpurun_out/${T}_sanitize_${tool}.log) summaries: $(grep -a 'ERROR SUMMARY' gpurun_out/${T}_sanitize_${tool}.log | sort | uniq -c | head -3)"
+  timeout 1500 compute-sanitizer --tool $tool --error-exitcode 77 --print-limit 20 \
+    python -m pytest tests/test_rrdb_gpu.py -x -q -k "taps_and_output and 37-53 and 4-2-0" > gpurun_out/${T}_sanitize_${tool}_rrdb.log 2>&1
+  echo "$tool rrdb rc=$? $(grep -a 'ERROR SUMMARY' gpurun_out/${T}_sanitize_${tool}_rrdb.log | sort | uniq -c | head -3)"
+  timeout 900 compute-sanitizer --tool $tool --error-exitcode 77 --print-limit 20 \
+    python -m pytest tests/test_bicubic_gpu.py tests/test_filters_gpu.py -x -q -k "37 or 64-96 or matches_oracle" > gpurun_out/${T}_sanitize_${tool}_u8.log 2>&1
+  echo "$tool u8-kernels rc=$? $(grep -a 'ERROR SUMMARY' gpurun_out/${T}_sanitize_${tool}_u8.log | sort | uniq -c | head -3)"
+done

@@ -10,6 +10,7 @@
 #include <string.h>
 
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <nvtx3/nvToolsExt.h>
 
 #include "cnn_small.cuh"
@@ -44,6 +45,7 @@ struct CnnPlan {
   uint8_t* ws = nullptr;
   size_t ws_bytes = 0;
   void* encode = nullptr;                    // cuTensorMapEncodeTiled, resolved through the runtime
+  uint8_t* t1wh[2] = {nullptr, nullptr};     // conv1, fp16 offset-1024 form (MODE_CONV1_H) for RGB / BGR input buffers
   uint8_t* t1wf = nullptr;                   // conv1 for fp32 input (vex_cnn2x_f32in): no 1/255 fold, weights repeated at k = 32..58 for the lo halves
   std::vector<cudaEvent_t> prof;             // option "profile": 8 events per sub-batch of the last forward
   bool prof_folded = false;                  // the last forward is already inside the statistics
@@ -360,10 +362,30 @@ int launch_i27(vex_ctx* ctx, unsigned abit, const void* in, const uint8_t* w, __
   thin::I27Params p;
   p.in = in; p.wpack = w; p.out = out; p.H = H; p.W = W;   // the bias travels inside w (k = 27, 28)
   p.npix = (long long)n * H * W; p.in_bgr = in_bgr; p.probe = ctx->opt_thin_probe;
+  p.out_cs = BN; p.dbg = nullptr;
   const long long items = (p.npix + 127) / 128;
-  thin::im2col27_kernel<MODE, BN><<<(unsigned)std::min<long long>(items, ctx->sm_count), thin::I27_THREADS, C::SMEM, s>>>(p);
+  const unsigned grid = (unsigned)std::min<long long>(items, ctx->sm_count);
+  if (ctx->opt_conv_dbg) {
+    VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&p.dbg), (size_t)grid * 64));
+    VEX_CUDA(ctx, cudaMemsetAsync(p.dbg, 0, (size_t)grid * 64, s));
+  }
+  thin::im2col27_kernel<MODE, BN><<<grid, thin::I27_THREADS, C::SMEM, s>>>(p);
   ctx->launches++;
   VEX_CUDA(ctx, cudaGetLastError());
+  if (p.dbg) {
+    std::vector<long long> h((size_t)grid * 8);
+    VEX_CUDA(ctx, cudaStreamSynchronize(s));
+    VEX_CUDA(ctx, cudaMemcpy(h.data(), p.dbg, h.size() * 8, cudaMemcpyDeviceToHost));
+    cudaFree(p.dbg);
+    double a[8] = {0};
+    for (unsigned b = 0; b < grid; ++b)
+      for (int i = 0; i < 8; ++i) a[i] += (double)h[(size_t)b * 8 + i] / grid;
+    const double it = (double)items / grid;
+    fprintf(stderr, "[im2col27_dbg mode=%d bn=%d] items/cta=%.1f cycles/item: MMA total=%.0f wait_acc_empty=%.0f wait_a_full=%.0f | "
+                    "builder(group 0, per own item) total=%.0f wait_a_empty=%.0f | drain(group 0, per own item) total=%.0f "
+                    "wait_acc_full=%.0f wait_bulk_read=%.0f\n",
+            MODE, BN, it, a[0] / it, a[1] / it, a[2] / it, 2 * a[4] / it, 2 * a[3] / it, 2 * a[7] / it, 2 * a[5] / it, 2 * a[6] / it);
+  }
   return VEX_OK;
 }
 
@@ -415,7 +437,20 @@ int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_
     VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&p.dbg), (size_t)grid * 128));
     VEX_CUDA(ctx, cudaMemsetAsync(p.dbg, 0, (size_t)grid * 128, s));
   }
-  thin::uptail_kernel<<<grid, thin::UT_THREADS, thin::UTCfg::SMEM, s>>>(p);
+  CUtensorMap xmap;                          // x5 as [n][H][W][4] fp32: box = the 19 x 7 pixel window of one item, OOB = 0
+  {
+    CnnPlan* P = ctx->cnn;
+    const cuuint64_t dims[4] = {4, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)n};
+    const cuuint64_t strides[3] = {16, (cuuint64_t)W * 16, (cuuint64_t)H * W * 16};
+    const cuuint32_t box[4] = {4, (cuuint32_t)thin::UT_XW, (cuuint32_t)thin::UT_XH, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = reinterpret_cast<EncodeFn>(P->encode)(
+        &xmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(x5), dims, strides, box, estr,
+        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(ctx, VEX_ERR_CUDA, "cuTensorMapEncodeTiled (x5) failed (" + std::to_string((int)r) + ")");
+  }
+  thin::uptail_kernel<<<grid, thin::UT_THREADS, thin::UTCfg::SMEM, s>>>(xmap, p);
   ctx->launches++;
   VEX_CUDA(ctx, cudaGetLastError());
   if (p.dbg) {
@@ -423,15 +458,15 @@ int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_
     VEX_CUDA(ctx, cudaStreamSynchronize(s));
     VEX_CUDA(ctx, cudaMemcpy(h.data(), p.dbg, h.size() * 8, cudaMemcpyDeviceToHost));
     cudaFree(p.dbg);
-    double a[13] = {0};
+    double a[16] = {0};
     for (unsigned b = 0; b < grid; ++b)
-      for (int i = 0; i < 13; ++i) a[i] += (double)h[(size_t)b * 16 + i] / grid;
+      for (int i = 0; i < 16; ++i) a[i] += (double)h[(size_t)b * 16 + i] / grid;
     const double items = (double)total / grid, e_items = std::max(1.0, a[12]);
     fprintf(stderr, "[uptail_dbg] items/cta=%.1f cycles/item: MMA total=%.0f wait_a1_full=%.0f wait_acc1_empty=%.0f wait_acc2_empty=%.0f "
-                    "wait_a2_full=%.0f | builder total=%.0f wait_a1_empty=%.0f | mid-drain total=%.0f wait_a2_empty=%.0f wait_acc1_full=%.0f "
-                    "| epilogue(group 0, per own item) total=%.0f wait_acc2_full=%.0f\n",
+                    "wait_a2_full=%.0f | builder total=%.0f wait_a1_empty=%.0f wait_x_full=%.0f | mid-drain total=%.0f wait_a2_empty=%.0f wait_acc1_full=%.0f "
+                    "tmem_ld=%.0f | epilogue(group 0, per own item) total=%.0f wait_acc2_full=%.0f\n",
             items, a[0] / items, a[1] / items, a[2] / items, a[3] / items, a[4] / items, a[6] / items, a[5] / items,
-            a[9] / items, a[7] / items, a[8] / items, a[11] / e_items, a[10] / e_items);
+            a[13] / items, a[9] / items, a[7] / items, a[8] / items, a[14] / items, a[11] / e_items, a[10] / e_items);
   }
   return VEX_OK;
 }
@@ -586,6 +621,29 @@ int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const*
     });
     if (rc) return rc;
   }
+  if (c1 <= 256) {   // conv1, fp16 offset form (thin_tc.cuh MODE_CONV1_H): k = 10 ky + 3 kx + cb with cb the BUFFER channel
+    for (int bgr = 0; bgr < 2; ++bgr) {
+      std::vector<uint16_t> img((size_t)c1 * 64, 0);
+      for (int r = 0; r < c1; ++r) {
+        double corr = 0.0;
+        uint16_t row[32] = {0};
+        for (int ky = 0; ky < 3; ++ky)
+          for (int j = 0; j < 9; ++j) {
+            const int kx = j / 3, cb = j % 3, ci = bgr ? 2 - cb : cb;
+            const float wv = cw[0][((size_t)r * 3 + ci) * 9 + ky * 3 + kx] * scale[0][r] * (1.0f / 255.0f);
+            const __half hw = __float2half_rn(wv);
+            memcpy(&row[10 * ky + j], &hw, 2);
+            corr += 1024.0 * (double)__half2float(hw);                    // what the operand offset adds to the sum
+          }
+        const float bp = (float)((double)shift[0][r] - corr);
+        const __half bh = __float2half_rn(bp), bl = __float2half_rn(bp - __half2float(bh));
+        memcpy(&row[30], &bh, 2);
+        memcpy(&row[31], &bl, 2);
+        for (int k = 0; k < 32; ++k) img[(size_t)r * 64 + (((k >> 3) ^ (r & 7)) << 3) + (k & 7)] = row[k];
+      }
+      if ((rc = upload(ctx, &P->t1wh[bgr], img.data(), img.size() * 2))) return rc;
+    }
+  }
   if (c1 <= 256) {   // conv1 for fp32 input: the input value arrives as hi (k < 27) + lo (k = 32..58) bf16, same weight for both
     rc = pack_rows_sw128(ctx, &P->t1wf, c1, 1, [&](int r, int k) -> float {
       if (k == 27 || k == 28) {
@@ -698,6 +756,10 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
     else if (d.c1 == 256) rc = launch_i27<thin::MODE_CONV1_F32, 256>(ctx, 0x1000u, in, P->t1wf, x1, n, H, W, 0, s);
     else rc = fail(ctx, VEX_ERR_UNSUPPORTED, "vex_cnn2x_f32in: c1 must be 128 or 256");
     if (rc) return rc;
+  } else if (thin_tc && ctx->opt_conv1_variant == 0 && d.c1 == 128) {
+    if ((rc = launch_i27<thin::MODE_CONV1_H, 128>(ctx, 0x2000u, in, P->t1wh[in_bgr ? 1 : 0], x1, n, H, W, 0, s))) return rc;
+  } else if (thin_tc && ctx->opt_conv1_variant == 0 && d.c1 == 256) {
+    if ((rc = launch_i27<thin::MODE_CONV1_H, 256>(ctx, 0x4000u, in, P->t1wh[in_bgr ? 1 : 0], x1, n, H, W, 0, s))) return rc;
   } else if (thin_tc && d.c1 == 128) {
     if ((rc = launch_i27<thin::MODE_CONV1, 128>(ctx, 8u, in, P->t1w, x1, n, H, W, in_bgr, s))) return rc;
   } else if (thin_tc && d.c1 == 256) {
@@ -937,7 +999,7 @@ void cnn_destroy(vex_ctx* ctx) {
   CnnPlan* P = ctx->cnn;
   if (!P) return;
   float* fs[] = {P->w1g, P->b1, P->w5g, P->b5, P->wu1, P->bu1, P->wu2, P->bu2};
-  uint8_t* us[] = {P->t1w, P->tu1wb, P->t5w, P->tu2w, P->t1wf};
+  uint8_t* us[] = {P->t1w, P->tu1wb, P->t5w, P->tu2w, P->t1wf, P->t1wh[0], P->t1wh[1]};
   for (uint8_t* u : us)
     if (u) cudaFree(u);
   for (float* f : fs)

@@ -323,7 +323,7 @@ int rrdb_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f3
     }
     thin::I27Params p;
     p.in = in; p.wpack = P->first_w; p.out = reinterpret_cast<__nv_bfloat16*>(feat); p.H = H; p.W = W;
-    p.npix = (long long)npix; p.in_bgr = in_bgr; p.probe = 0; p.out_cs = 64;
+    p.npix = (long long)npix; p.in_bgr = in_bgr; p.probe = 0; p.out_cs = 64; p.dbg = nullptr;
     const long long items = (p.npix + 127) / 128;
     thin::im2col27_kernel<thin::MODE_FIRST64, 64><<<(unsigned)std::min<long long>(items, ctx->sm_count), thin::I27_THREADS,
                                                     C::SMEM, s>>>(p);

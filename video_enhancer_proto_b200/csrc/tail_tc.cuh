@@ -3,7 +3,11 @@
 // never goes to HBM: unfused, writing and re-reading it costs more time than everything else in the two layers.
 //
 // Per item = one hi-res output tile of 6 rows x 30 px (halo tile 8 x 32 hi-res px = 5 x 17 low-res px):
-//   builders   gather the 3x3x3 neighbourhood of each of the 85 low-res pixels from x5 (K = 27 -> 32), one
+//   x5 window  one TMA box load per item brings the 7 x 19 low-res pixels (fp32 x 4) under the patch and its 3x3 halo into
+//              shared memory, 4 stages deep (out-of-image pixels arrive as zeros = the padding).  The first version gathered
+//              the 9 neighbours per thread with global loads, one item ahead: the per-role cycle counters (option conv_dbg)
+//              showed the MMA thread waiting 1255 of 2201 cycles per item for these builders - memory latency, not bandwidth.
+//   builders   read the 3x3x3 neighbourhood of each of the 85 low-res pixels from the window (K = 27 -> 32), one
 //              SWIZZLE_128B operand row per thread                                        (as im2col27, MODE_UP1)
 //   MMA #1     [128 x 32] x [32 x 256]: ConvTranspose2d(3,64,4,2,1) as conv3x3 3 -> 4 phases x 64 ch  -> TMEM
 //   mid-drain  TMEM -> bias, relu, bf16 -> PixelShuffle into the [256 hi-res px x 64 ch] A operand of the second
@@ -19,11 +23,17 @@ namespace thin {
 
 constexpr int UT_EPI_GROUPS = 3;       // the epilogue is the longest role: three groups of 4 warps take items k % 3
 constexpr int UT_THREADS = 384 + 128 * UT_EPI_GROUPS;   // warps 0-3 builders; 4-6 / 8-10 mid-drain groups (phases 0-1 / 2-3;
-                                       // TMEM lanes 0-95); 7 MMA; 11 idle; 12-15 / 16-19 / 20-23 epilogue groups
+                                       // TMEM lanes 0-95); 7 MMA; 11 TMA producer of the x5 windows; 12-15 / 16-19 / 20-23 epilogue groups
+
 constexpr int UT_MMA_WARP = 7;
 constexpr int UT_EPI_WARP0 = 12;
 constexpr int UT_LR = 5, UT_LC = 17;   // low-res pixels under the 8 x 32 hi-res halo tile
 constexpr int UT_ROWS1 = UT_LR * UT_LC;   // 85 live rows of the first GEMM
+constexpr int UT_TMA_WARP = 11;
+constexpr int UT_XS = 4;               // x5 window stages
+constexpr int UT_XW = UT_LC + 2, UT_XH = UT_LR + 2;      // window = patch + 1-pixel halo: 19 x 7 low-res pixels
+constexpr int UT_X_BYTES = UT_XW * UT_XH * 16;           // 2128: what one TMA box load delivers
+constexpr int UT_X_STAGE = (UT_X_BYTES + 127) / 128 * 128;
 
 struct UTCfg {
   static constexpr int A1_STAGE = 128 * 128;
@@ -36,9 +46,9 @@ struct UTCfg {
   static constexpr int YS_BYTES = 27 * G27_YS_PITCH * 4;
   static constexpr int OB_OFF = YS_OFF + UT_EPI_GROUPS * YS_BYTES;
   static constexpr int OB_BYTES = G27_ROWS * G27_OB_PITCH + 16;
-  static constexpr int BAR_OFF = (OB_OFF + UT_EPI_GROUPS * OB_BYTES + 15) / 16 * 16;
-  static constexpr int BIAS_OFF = BAR_OFF + 256;
-  static constexpr int SMEM = BIAS_OFF + 1024;
+  static constexpr int X_OFF = (OB_OFF + UT_EPI_GROUPS * OB_BYTES + 127) / 128 * 128;
+  static constexpr int BAR_OFF = X_OFF + UT_XS * UT_X_STAGE;
+  static constexpr int SMEM = BAR_OFF + 256 + 1024;
 };
 
 struct UTParams {
@@ -55,11 +65,12 @@ struct UTParams {
   int probe;               // bring-up timing probes (WRONG RESULTS): 4 = no gather loads, 2 = mid-drain without stores, 1 = epilogue without gather
   long long* dbg;          // optional [gridDim.x][16] cycle counters per role (option conv_dbg): MMA thread 0 total, 1 wait a1_full,
                            // 2 wait acc1_empty, 3 wait acc2_empty, 4 wait a2_full; builder 5 wait a1_empty, 6 total; mid-drain (warp 4)
-                           // 7 wait a2_empty, 8 wait acc1_full, 9 total; epilogue group 0: 10 wait acc2_full, 11 total, 12 items
+                           // 7 wait a2_empty, 8 wait acc1_full, 9 total; epilogue group 0: 10 wait acc2_full, 11 total, 12 items;
+                           // 13 builder wait x_full, 14 mid-drain tcgen05.ld + wait
 };
 
 __global__ void __launch_bounds__(UT_THREADS, 1)
-uptail_kernel(const UTParams p) {
+uptail_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
   using C = UTCfg;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -71,6 +82,7 @@ uptail_kernel(const UTParams p) {
   const uint32_t a2_full = bar0 + 64, a2_empty = bar0 + 80;
   const uint32_t acc2_full = bar0 + 96, acc2_empty = bar0 + 128;     // per epilogue group (up to 4)
   const uint32_t w_bar = bar0 + 160, tmem_slot = bar0 + 168;
+  const uint32_t x_full = bar0 + 176, x_empty = bar0 + 176 + 8 * UT_XS;   // x5 window stages
   volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(sm + C::BAR_OFF + 168);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total = p.tiles_x * p.tiles_y * p.n_img;
@@ -84,7 +96,9 @@ uptail_kernel(const UTParams p) {
     }
     for (int i = 0; i < UT_EPI_GROUPS; ++i) { ptx::mbar_init(acc2_full + 8 * i, 1); ptx::mbar_init(acc2_empty + 8 * i, 4); }
     ptx::mbar_init(w_bar, 1);
+    for (int i = 0; i < UT_XS; ++i) { ptx::mbar_init(x_full + 8 * i, 1); ptx::mbar_init(x_empty + 8 * i, 128); }
     ptx::fence_mbar_init();
+    ptx::prefetch_tensormap(&xmap);
   }
   if (warp == UT_MMA_WARP) {
     ptx::tmem_alloc(tmem_slot, 512);                 // [0,256): first GEMM, two halves; 256 + grp*64 + g*32: second GEMM
@@ -99,46 +113,35 @@ uptail_kernel(const UTParams p) {
     // ================================ builders: low-res pixel r of the 5 x 17 patch -> one operand row
     const int r = threadIdx.x;
     const int lr = r / UT_LC, lc = r - lr * UT_LC;
-    // The gather is pure latency (9 independent 16-byte loads, then a dependent pack), so the loads of item k+1 are
-    // issued as soon as item k is packed, before its hand-off (wait for a free stage, store, arrive).
-    auto gather = [&](int it, float4 (&f)[9]) -> bool {
-      const int txi = it % p.tiles_x, t = it / p.tiles_x;
-      const int tyi = t % p.tiles_y, n = t / p.tiles_y;
-      const int y = 3 * tyi - 1 + lr, x = 15 * txi - 1 + lc;
-      const bool live = r < UT_ROWS1 && y >= 0 && y < p.H && x >= 0 && x < p.W && !(p.probe & 4);
-#pragma unroll
-      for (int ky = 0; ky < 3; ++ky) {
-        const int yy = y + ky - 1;
-#pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-          const int xx = x + kx - 1;
-          f[ky * 3 + kx] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (live && yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) f[ky * 3 + kx] = __ldg(p.x5 + ((size_t)n * p.H + yy) * p.W + xx);
-        }
-      }
-      return live;
-    };
-    float4 f[9];
-    bool live = false;
-    if ((int)blockIdx.x < total) live = gather(blockIdx.x, f);
     uint32_t k = 0;
     const bool dbg = p.dbg != nullptr && threadIdx.x == 0;
-    long long tw = 0, tb0 = dbg ? clock64() : 0;
+    long long tw = 0, tx = 0, tb0 = dbg ? clock64() : 0;
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
+      const int txi = it % p.tiles_x, t = it / p.tiles_x;
+      const int tyi = t % p.tiles_y;
+      const int y = 3 * tyi - 1 + lr, x = 15 * txi - 1 + lc;
+      const bool live = r < UT_ROWS1 && y >= 0 && y < p.H && x >= 0 && x < p.W && !(p.probe & 4);
+      const uint32_t xs = k % UT_XS, xp = (k / UT_XS) & 1;
       uint32_t w[16];
 #pragma unroll
       for (int j = 0; j < 16; ++j) w[j] = 0u;
+      const long long tx0 = dbg ? clock64() : 0;
+      ptx::mbar_wait(x_full + 8 * xs, xp);             // the window of this item has landed (TMA, 4 items ahead)
+      if (dbg) tx += clock64() - tx0;
       if (live) {
+        const float4* win = reinterpret_cast<const float4*>(sm + C::X_OFF + xs * UT_X_STAGE) + lr * UT_XW + lc;
         float v[27];
 #pragma unroll
-        for (int q9 = 0; q9 < 9; ++q9) { v[q9 * 3 + 0] = f[q9].x; v[q9 * 3 + 1] = f[q9].y; v[q9 * 3 + 2] = f[q9].z; }
+        for (int q9 = 0; q9 < 9; ++q9) {
+          const float4 f = win[(q9 / 3) * UT_XW + q9 % 3];
+          v[q9 * 3 + 0] = f.x; v[q9 * 3 + 1] = f.y; v[q9 * 3 + 2] = f.z;
+        }
 #pragma unroll
         for (int j = 0; j < 13; ++j) w[j] = ptx::pack_bf16x2(v[2 * j], v[2 * j + 1]);
         w[13] = ptx::pack_bf16x2(v[26], 1.0f);       // k = 27, 28: constant 1 against the bias rows of W1
         w[14] = ptx::pack_bf16x2(1.0f, 0.f);
       }
-      const int itn = it + gridDim.x;                // the packed row frees f: the next item's loads fly during the hand-off
-      if (itn < total) live = gather(itn, f);
+      ptx::mbar_arrive(x_empty + 8 * xs);              // the packed row depends on every window load: the stage may be refilled
       const uint32_t sa = k & 1, pa = (k >> 1) & 1;
       const long long tq0 = dbg ? clock64() : 0;
       ptx::mbar_wait(a1_empty + 8 * sa, pa ^ 1);
@@ -150,7 +153,21 @@ uptail_kernel(const UTParams p) {
       ptx::fence_proxy_async_smem();
       ptx::mbar_arrive(a1_full + 8 * sa);
     }
+    if (dbg) p.dbg[blockIdx.x * 16 + 13] = tx;
     if (dbg) { p.dbg[blockIdx.x * 16 + 5] = tw; p.dbg[blockIdx.x * 16 + 6] = clock64() - tb0; }
+  } else if (warp == UT_TMA_WARP) {
+    // ================================ x5 windows: one box load per item, UT_XS items ahead of the builders
+    if (ptx::elect_one()) {
+      uint32_t k = 0;
+      for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
+        const int txi = it % p.tiles_x, t = it / p.tiles_x;
+        const int tyi = t % p.tiles_y, n = t / p.tiles_y;
+        const uint32_t xs = k % UT_XS, xp = (k / UT_XS) & 1;
+        ptx::mbar_wait(x_empty + 8 * xs, xp ^ 1);
+        ptx::mbar_expect_tx(x_full + 8 * xs, UT_X_BYTES);
+        ptx::tma_load_4d(sbase + C::X_OFF + xs * UT_X_STAGE, &xmap, x_full + 8 * xs, 0, 15 * txi - 2, 3 * tyi - 2, n);
+      }
+    }
   } else if (warp == UT_MMA_WARP) {
     // ================================ both GEMMs from one thread; GEMM #2 of item k-1 is issued after GEMM #1 of item k
     if (ptx::elect_one()) {
@@ -216,7 +233,7 @@ uptail_kernel(const UTParams p) {
         d[0] = clock64() - tm0; d[1] = t1; d[2] = t2; d[3] = t3; d[4] = t4;
       }
     }
-  } else if (warp < 11) {
+  } else if (warp < 11) {   // (warp 7 = MMA and warp 11 = TMA were taken above)
     // ================================ mid-drain: relu(upconv1) of low-res pixel r -> rows of A2.  Group h (warps 4-6 /
     // 8-10) takes phases 2h and 2h+1 = columns [128h, 128h+128) of the first accumulator.
     const int h = warp >> 3;
@@ -225,7 +242,7 @@ uptail_kernel(const UTParams p) {
     const int lr = r / UT_LC, lc = r - lr * UT_LC;
     uint32_t k = 0;
     const bool dbg = p.dbg != nullptr && warp == 4 && lane == 0;
-    long long t7 = 0, t8 = 0, tq = 0;
+    long long t7 = 0, t8 = 0, tq = 0, tld = 0;
     const long long td0 = dbg ? clock64() : 0;
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
       const int txi = it % p.tiles_x, t = it / p.tiles_x;
@@ -252,8 +269,10 @@ uptail_kernel(const UTParams p) {
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint32_t v[32];
+          const long long tl0 = dbg ? clock64() : 0;
           ptx::tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + h * 128 + pp * 64 + half * 32, v);
           ptx::tmem_ld_wait();
+          if (dbg) tld += clock64() - tl0;
           if (in_tile && !(p.probe & 2)) {
 #pragma unroll
             for (int j4 = 0; j4 < 4; ++j4) {
@@ -274,7 +293,7 @@ uptail_kernel(const UTParams p) {
       ptx::fence_proxy_async_smem();
       ptx::mbar_arrive(a2_full + 8 * s);
     }
-    if (dbg) { long long* d = p.dbg + blockIdx.x * 16; d[7] = t7; d[8] = t8; d[9] = clock64() - td0; }
+    if (dbg) { long long* d = p.dbg + blockIdx.x * 16; d[7] = t7; d[8] = t8; d[9] = clock64() - td0; d[14] = tld; }
   } else if (warp >= UT_EPI_WARP0) {
     // ================================ epilogue: as gemm27 MODE_UP2, on the hi-res tile
     const int grp = (warp - UT_EPI_WARP0) >> 2;

@@ -38,6 +38,13 @@ constexpr int MODE_CONV1 = 0, MODE_UP1 = 1, MODE_CONV1_F32 = 2;   // _F32: fp32 
 // fp16 NHWC out with pixel stride `out_cs`.  K = 64: the input values sit at k = 0..26 AND k = 32..58, the weight image
 // holds bf16(w) at the first and bf16(w - bf16(w)) at the second position, so the weights carry 16 mantissa bits.
 constexpr int MODE_FIRST64 = 3;
+// MODE_CONV1_H: conv1 with fp16 operands built WITHOUT any integer->float conversion: the half 0x6400 | v is exactly
+// 1024 + v for a byte v, so an operand pair is ONE byte-permute of the raw frame bytes against the constant 0x64646464.
+// The GEMM then computes sum_k w_k (1024 + v_k); the weight image carries bias - 1024 * sum_k w_k (as hi + lo halves
+// against two constant-1 columns), which removes the offset again - for zero-padded taps too, whose operand is 1024 + 0.
+// K layout: window row ky at k = 10 ky + (3 kx + c) (9 used of 10, so no operand pair straddles two rows), k = 30, 31 bias.
+// Per pixel: 9 aligned 32-bit loads + 9 funnel shifts + 15 PRMT instead of 27 byte loads + 27 I2F + 14 F2FP.
+constexpr int MODE_CONV1_H = 4;
 constexpr int I27_THREADS = 544;       // warps 0-3 / 4-7 two A-builder groups, warp 8 MMA, warps 9-12 / 13-16 two drain groups
 constexpr int I27_SA = 4;              // A stages (128 rows x 128 B each); item sequence k uses stage k & 3
 constexpr int I27_MMA_WARP = 8;
@@ -66,7 +73,20 @@ struct I27Params {
   int in_bgr;
   int probe;               // bring-up timing probes (WRONG RESULTS): 1 = no global stores, 2 = no TMEM drain, 4 = no gather loads
   int out_cs;              // MODE_FIRST64: channel stride of the output pixels (elements); other modes: dense rows of BN
+  long long* dbg;          // optional [gridDim.x][8] cycle counters (option conv_dbg): MMA thread 0 total, 1 wait acc_empty, 2 wait a_full;
+                           // builder group 0: 3 wait a_empty, 4 total; drain group 0: 5 wait acc_full, 6 wait bulk-store read, 7 total
 };
+
+// 32-bit word at absolute byte address `a` (a multiple of 4) of a byte buffer [lo, hi): bytes outside the buffer read as 0
+// and are never touched (the last word of a frame batch may be partial; the one before the first does not exist).
+__device__ __forceinline__ uint32_t ldg_word_clipped(uintptr_t a, uintptr_t lo, uintptr_t hi) {
+  if (a >= lo && a + 4 <= hi) return __ldg(reinterpret_cast<const uint32_t*>(a));
+  uint32_t w = 0;
+#pragma unroll
+  for (int b = 0; b < 4; ++b)
+    if (a + b >= lo && a + b < hi) w |= (uint32_t)__ldg(reinterpret_cast<const uint8_t*>(a + b)) << (8 * b);
+  return w;
+}
 
 template <int MODE, int BN>
 __global__ void __launch_bounds__(I27_THREADS, 1)
@@ -106,12 +126,46 @@ im2col27_kernel(const I27Params p) {
     const int gi = warp >> 2;
     const int r = threadIdx.x & 127;                 // row within the stage
     uint32_t sa = gi, pa = 0;
+    const bool dbg = p.dbg != nullptr && threadIdx.x == 0;
+    long long tbw = 0;
+    const long long tb0 = dbg ? clock64() : 0;
     for (long long it = blockIdx.x + (long long)gi * gridDim.x; it < items; it += 2LL * gridDim.x) {
       const long long pix = it * 128 + r;
       uint32_t w[16], wlo[16];
 #pragma unroll
       for (int j = 0; j < 16; ++j) w[j] = wlo[j] = 0u;
-      if (pix < p.npix && !(p.probe & 4)) {
+      if (MODE == MODE_CONV1_H) {
+        if (pix < p.npix) {
+          const int x = (int)(pix % p.W);
+          const int y = (int)((pix / p.W) % p.H);
+          const uintptr_t lo = reinterpret_cast<uintptr_t>(p.in), hi = lo + (uintptr_t)p.npix * 3;
+          const uintptr_t a0 = lo + (uintptr_t)((pix - 1) * 3);           // byte address of pixel (y, x-1), channel 0
+#pragma unroll
+          for (int ky = 0; ky < 3; ++ky) {
+            const int yy = y + ky - 1;
+            uint32_t A0 = 0, A1 = 0, A2 = 0;                               // the row's 9 window bytes, aligned
+            if (yy >= 0 && yy < p.H) {
+              const uintptr_t a = a0 + (uintptr_t)((long long)(ky - 1) * p.W * 3);
+              const uintptr_t wa = a & ~(uintptr_t)3;
+              const uint32_t sh = (uint32_t)(a & 3) * 8;
+              const uint32_t w0 = ldg_word_clipped(wa, lo, hi), w1 = ldg_word_clipped(wa + 4, lo, hi),
+                             w2 = ldg_word_clipped(wa + 8, lo, hi);
+              A0 = __funnelshift_r(w0, w1, sh);
+              A1 = __funnelshift_r(w1, w2, sh);
+              A2 = w2 >> sh;
+              if (x == 0) A0 &= 0xFF000000u;                               // left neighbour is padding (bytes 0-2)
+              if (x == p.W - 1) { A1 &= 0x0000FFFFu; A2 = 0u; }            // right neighbour is padding (bytes 6-8)
+            }
+            constexpr uint32_t C64 = 0x64646464u;
+            w[5 * ky + 0] = __byte_perm(A0, C64, 0x4140);
+            w[5 * ky + 1] = __byte_perm(A0, C64, 0x4342);
+            w[5 * ky + 2] = __byte_perm(A1, C64, 0x4140);
+            w[5 * ky + 3] = __byte_perm(A1, C64, 0x4342);
+            w[5 * ky + 4] = __byte_perm(A2, C64, 0x4440);                  // k = 10 ky + 9 is unused (zero weight)
+          }
+          w[15] = 0x3C003C00u;                                             // k = 30, 31: 1.0 against the bias halves
+        }
+      } else if (pix < p.npix && !(p.probe & 4)) {
         const int x = (int)(pix % p.W);
         const long long t = pix / p.W;
         const int y = (int)(t % p.H);
@@ -162,7 +216,9 @@ im2col27_kernel(const I27Params p) {
           wlo[13] = ptx::pack_bf16x2(v[26], 0.f);
         }
       }
+      const long long tq0 = dbg ? clock64() : 0;
       ptx::mbar_wait(a_empty + 8 * sa, pa ^ 1);
+      if (dbg) tbw += clock64() - tq0;
       uint8_t* row = sm + sa * C::A_STAGE + r * 128;
 #pragma unroll
       for (int j = 0; j < 4; ++j)
@@ -177,17 +233,26 @@ im2col27_kernel(const I27Params p) {
       sa += 2;
       if (sa >= I27_SA) { sa -= I27_SA; pa ^= 1; }
     }
+    if (dbg) { p.dbg[blockIdx.x * 8 + 3] = tbw; p.dbg[blockIdx.x * 8 + 4] = clock64() - tb0; }
   } else if (warp == I27_MMA_WARP) {
     // ================================ weights once, then 2 MMAs per item
     if (ptx::elect_one()) {
       ptx::mbar_expect_tx(w_bar, C::W_BYTES);
       ptx::bulk_load(sbase + C::W_OFF, p.wpack, C::W_BYTES, w_bar);
       ptx::mbar_wait(w_bar, 0);
-      constexpr uint32_t idesc = ptx::idesc_bf16_f32(128, BN);
+      // kind::f16 instruction descriptor: bits 7-9 / 10-12 = A / B format (0 fp16, 1 bf16)
+      constexpr uint32_t idesc = MODE == MODE_CONV1_H ? (ptx::idesc_bf16_f32(128, BN) & ~((1u << 7) | (1u << 10)))
+                                                      : ptx::idesc_bf16_f32(128, BN);
       uint32_t sa = 0, pa = 0, b = 0, pb = 0;
+      const bool dbg = p.dbg != nullptr;
+      long long t1 = 0, t2 = 0, tq = 0;
+      const long long tm0 = dbg ? clock64() : 0;
       for (long long it = blockIdx.x; it < items; it += gridDim.x) {
+        if (dbg) tq = clock64();
         ptx::mbar_wait(acc_empty + 8 * b, pb ^ 1);
+        if (dbg) { const long long n = clock64(); t1 += n - tq; tq = n; }
         ptx::mbar_wait(a_full + 8 * sa, pa);
+        if (dbg) t2 += clock64() - tq;
         ptx::tc_fence_after();
 #pragma unroll
         for (int k = 0; k < ((MODE == MODE_CONV1_F32 || MODE == MODE_FIRST64) ? 4 : 2); ++k) {
@@ -200,6 +265,7 @@ im2col27_kernel(const I27Params p) {
         if (++sa == I27_SA) { sa = 0; pa ^= 1; }
         if (++b == C::NACC) { b = 0; pb ^= 1; }
       }
+      if (dbg) { long long* d = p.dbg + blockIdx.x * 8; d[0] = clock64() - tm0; d[1] = t1; d[2] = t2; }
     }
   } else {
     // ================================ drain: TMEM -> bias, relu, bf16 -> shared stage -> bulk (TMA) stores.
@@ -216,6 +282,9 @@ im2col27_kernel(const I27Params p) {
     constexpr int HALVES = BN >= 128 ? BN / 128 : 1;
     constexpr int GPH = BN >= 128 ? 4 : BN / 32;   // 32-column groups per staged row (row = GPH * 64 bytes)
     long long k = ge;
+    const bool dbg = p.dbg != nullptr && ew == 0 && lane == 0;
+    long long t5 = 0, t6 = 0;
+    const long long td0 = dbg ? clock64() : 0;
     for (long long it = blockIdx.x + (long long)ge * gridDim.x; it < items; it += 2LL * gridDim.x, k += 2) {
       const uint32_t b = (uint32_t)(k % C::NACC), pb = (uint32_t)((k / C::NACC) & 1);
       const long long pix = it * 128 + q * 32 + lane;
@@ -236,11 +305,15 @@ im2col27_kernel(const I27Params p) {
           half_stride = (size_t)(2LL * p.W) * (BN / 4) * 2;     // hi-res row 2y+1
         }
       }
+      const long long tq5 = dbg ? clock64() : 0;
       ptx::mbar_wait(acc_full + 8 * b, pb);
+      if (dbg) t5 += clock64() - tq5;
       ptx::tc_fence_after();
 #pragma unroll 1
       for (int hf = 0; hf < HALVES; ++hf) {
+        const long long tq6 = dbg ? clock64() : 0;
         ptx::bulk_wait_read0();                      // this lane's previous bulk store has finished reading its row
+        if (dbg) t6 += clock64() - tq6;
 #pragma unroll 1
         for (int g = (p.probe & 2) ? GPH : 0; g < GPH; ++g) {
           uint32_t v[32];
@@ -275,6 +348,7 @@ im2col27_kernel(const I27Params p) {
       }
     }
     ptx::bulk_wait_all0();                           // global writes complete before the CTA exits
+    if (dbg) { long long* d = p.dbg + blockIdx.x * 8; d[5] = t5; d[6] = t6; d[7] = clock64() - td0; }
   }
   ptx::tc_fence_before();
   __syncthreads();

@@ -140,19 +140,40 @@ def test_video_order_and_colour_with_full_range_weights(tmp_path):
         assert abs(mid[:, 2].mean() - 60) < 12                               # R still the constant channel
     finally:
         enh.close()
-    # CNN mode with full-range weights: decoded input through the frame API vs the decoded output, per frame and tight
+    # CNN mode with full-range weights.  Their output is noise-like and does not survive the lossy codec, so the writer is
+    # replaced by a recorder: what the video loop HANDS to the encoder must equal, bit for bit and in order, the decoded
+    # input frames pushed through the frame API with the loop's colour flags (BGR in, BGR out).
+    recorded = []
+
+    class Recorder:
+        def __init__(self, path, fourcc, fps, size):
+            self.size = size
+
+        def isOpened(self):
+            return True
+
+        def write(self, frame):
+            assert frame.shape == (self.size[1], self.size[0], 3)
+            recorded.append(frame.copy())
+
+        def release(self):
+            pass
+
     stress = B200VideoEnhancer(device="cuda:0", state_dict=O.export_state(O.make_stress_model()))
     try:
-        dst2 = tmp_path / "tag_cnn.mp4"
-        stats = stress.enhance_video(str(src), str(dst2))
-        assert stats["frames_processed"] == n
-        got, _ = read_clip(dst2)
         ins, _ = read_clip(src)
         want = stress._run_host(1, ins, 0b11).copy()
         assert want.std() > 30                                              # full-range output: the comparison means something
-        errs = np.array([[np.abs(got[i].astype(np.float32) - want[j].astype(np.float32)).mean() for j in range(n)]
-                         for i in range(0, n, 6)])
-        for r, i in enumerate(range(0, n, 6)):
-            assert errs[r, i] < 6.0 and errs[r].argmin() == i, (i, errs[r, i], int(errs[r].argmin()))
+        real_writer = cv2.VideoWriter
+        cv2.VideoWriter = Recorder
+        try:
+            stats = stress.enhance_video(str(src), str(tmp_path / "unused.mp4"))
+        finally:
+            cv2.VideoWriter = real_writer
+        assert stats["frames_processed"] == n == len(recorded)
+        for i in range(n):
+            assert np.array_equal(recorded[i], want[i]), i
+        swapped = stress._run_host(1, ins[:1], 0b10)[0]                     # RGB-in interpretation of the same buffer
+        assert not np.array_equal(swapped, want[0])                         # ... so the flags are really being checked
     finally:
         stress.close()

@@ -10,6 +10,7 @@
 //   conv_up1 + LeakyReLU (scale 4: stored 2x2-replicated again -> [4H][4W]) ; conv_up2 + LeakyReLU (scale 4 only)
 //   conv_hr + LeakyReLU ; conv_last -> clamp(0,1) -> x255 -> truncate -> u8 HWC (sH, sW)
 #include <algorithm>
+#include <stdio.h>
 #include <string.h>
 #include <string>
 #include <vector>
@@ -144,11 +145,47 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, const __half* in, int in_cs, cons
   p.tiles_x = (W + rrdb::TILE_W - 1) / rrdb::TILE_W;
   p.tiles_y = (H + rrdb::ROWS - 1) / rrdb::ROWS;
   p.n_img = n;
+  p.dbg = nullptr;
   const long long total = (long long)p.tiles_x * p.tiles_y * n;
   if (total > 0x7fffffffLL) return fail(ctx, VEX_ERR_INVALID, "rrdb conv: too many tiles");
-  rrdb::rconv3x3_kernel<BN><<<(unsigned)std::min<long long>(total, ctx->sm_count), rrdb::NTHREADS, C::SMEM, s>>>(amap, p);
+  if (ctx->opt_conv_dbg) {
+    VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&p.dbg), (size_t)ctx->sm_count * 64));
+    VEX_CUDA(ctx, cudaMemsetAsync(p.dbg, 0, (size_t)ctx->sm_count * 64, s));
+  }
+  cudaLaunchConfig_t cfg = {};
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = ctx->opt_pdl ? 1 : 0;
+  cfg.gridDim = dim3((unsigned)std::min<long long>(total, ctx->sm_count));
+  cfg.blockDim = dim3(rrdb::NTHREADS);
+  cfg.dynamicSmemBytes = C::SMEM;
+  cfg.stream = s;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (p.dbg) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, s); }
+  VEX_CUDA(ctx, cudaLaunchKernelEx(&cfg, rrdb::rconv3x3_kernel<BN>, amap, p));
   ctx->launches++;
   VEX_CUDA(ctx, cudaGetLastError());
+  if (p.dbg) {
+    cudaEventRecord(e1, s);
+    const unsigned grid = cfg.gridDim.x;
+    std::vector<long long> h((size_t)grid * 8);
+    VEX_CUDA(ctx, cudaStreamSynchronize(s));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    VEX_CUDA(ctx, cudaMemcpy(h.data(), p.dbg, h.size() * 8, cudaMemcpyDeviceToHost));
+    cudaFree(p.dbg);
+    double a[8] = {0};
+    for (unsigned b = 0; b < grid; ++b)
+      for (int i = 0; i < 8; ++i) a[i] += (double)h[(size_t)b * 8 + i] / grid;
+    const double items = (double)total / grid;
+    const double mma_clk = (double)L.nc * 9 * rrdb::APS * 4;          // MMAs per item
+    fprintf(stderr, "[rconv_dbg cin=%d cout=%d %dx%d] %.1f us, items/cta=%.2f, cycles/item: MMA total=%.0f (%.1f clk/MMA) wait_acc_empty=%.0f "
+                    "wait_a_full=%.0f wait_w_full=%.0f | epilogue wait_acc_full=%.0f work=%.0f | producer wait_a_empty=%.0f wait_w_empty=%.0f\n",
+            L.cin, L.cout, H, W, ms * 1e3, items, a[0] / items, a[0] / items / mma_clk, a[1] / items, a[2] / items, a[3] / items,
+            a[4] / items, a[5] / items, a[6] / items, a[7] / items);
+  }
   return VEX_OK;
 }
 

@@ -23,8 +23,14 @@
 //
 // N = 32 / 64 makes the SS-mode MMA shared-memory bound (4 KB of A per 128 x N x 16 MMA at 128 B/clk: 40 / 48 clocks
 // against 16 / 32 of math), so unlike conv_tc3 there is nothing to win from CTA pairs and this kernel is single-CTA:
-// warp 0 TMA producer, warp 1 MMA issuer + TMEM owner, warps 2-5 epilogue; two TMEM slots of APS accumulators so the
-// epilogue of item k overlaps the MMAs of item k+1.  Persistent grid; work item = (image, 8-row x 30-column tile).
+// warp 0 activation (TMA) producer, warp 1 MMA issuer + TMEM owner, warps 2-5 epilogue, warp 6 weight producer; two TMEM
+// slots of APS accumulators so the epilogue of item k overlaps the MMAs of item k+1.  Persistent grid; work item = (image,
+// 8-row x 30-column tile).
+// Weights: when all (chunk, tap) slices of the layer fit the slice buffer (every Cout = 32 layer: <= 27 x 4 KB; the
+// 64 -> 64 layers: 9 x 8 KB) they are loaded ONCE per CTA and stay resident; only conv5 (192 -> 64, 216 KB) streams them
+// through the buffer as a ring.  The first version had one producer thread issue activations and weights in program order;
+// blocked on a free activation stage it could not run ahead with the weights, and the per-role cycle counters (option
+// conv_dbg) showed the MMA thread waiting 13-19 % of its time for weight slices (67-75 clocks per MMA against ~48).
 #pragma once
 
 #include <cuda_fp16.h>
@@ -38,7 +44,7 @@ constexpr int PITCH = 32;
 constexpr int TILE_W = 30;
 constexpr int KC = 64;
 constexpr int SA = 2;
-constexpr int NTHREADS = 192;    // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue (TMEM lane quarter = warp & 3)
+constexpr int NTHREADS = 224;    // warp 0 TMA (activations), warp 1 MMA, warps 2-5 epilogue (TMEM lane quarter = warp & 3), warp 6 weights
 constexpr int APS = 2;           // accumulators (128 pixels each) per work item
 constexpr int ROWS = APS * 4;
 
@@ -47,7 +53,7 @@ struct Cfg {
   static_assert(BN == 32 || BN == 64, "BN");
   static constexpr int A_STAGE = (ROWS + 2) * PITCH * 128;
   static constexpr int W_SLICE = BN * 128;              // one (chunk, tap) slice: BN rows x 64 fp16
-  static constexpr int SW = BN == 32 ? 18 : 9;          // ring = two / one chunk's worth of taps
+  static constexpr int SW = BN == 32 ? 27 : 9;          // slice buffer: a whole Cout = 32 layer / one chunk's worth of taps
   static constexpr int BAR_OFF = SA * A_STAGE + SW * W_SLICE;
   static constexpr int BIAS_OFF = BAR_OFF + 512;
   static constexpr int STAGE_OFF = BIAS_OFF + 256;
@@ -67,7 +73,17 @@ struct Params {
   int ups2;               // store every pixel to the 2 x 2 block of a twice as large output (nearest-neighbour upsample)
   int H, W, NC;           // NC = 64-channel chunks of the input that are read
   int tiles_x, tiles_y, n_img;
+  long long* dbg;         // optional [gridDim.x][8] cycle counters (option conv_dbg): MMA thread 0 total, 1 wait acc_empty, 2 wait a_full,
+                          // 3 wait w_full; epilogue warp 2: 4 wait acc_full, 5 work; producer: 6 wait a_empty, 7 wait w_empty
 };
+
+// Programmatic dependent launch: the ~350 layer kernels of one pass form a chain on one stream.  A kernel launched with
+// the programmatic-serialisation attribute may start while its predecessor's last CTAs are still running; its prologue
+// (barrier init, TMEM allocation, bias, tensor-map prefetch) then overlaps the predecessor's tail, and `pdl_wait` holds
+// every access to activations until the predecessor has completed and flushed.  `pdl_launch_dependents` lets the
+// successor start as early as possible.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 // fp32 pair -> packed fp16, round to nearest, saturating to +-65504
 __device__ __forceinline__ uint32_t pack_f16x2_sat(float lo, float hi) {
@@ -122,28 +138,55 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot_p;
+  const bool resident = p.NC * 9 <= C::SW;              // every weight slice of the layer fits the slice buffer
+  pdl_launch_dependents();                              // the next layer may begin its prologue
 
   if (warp == 0) {
     // ============================== TMA producer ==============================
     if (ptx::elect_one()) {
-      uint32_t sa = 0, pa = 0, sw = 0, pw = 0;
+      uint32_t sa = 0, pa = 0;
+      const bool dbg = p.dbg != nullptr;
+      long long t6 = 0, tq = 0;
+      pdl_wait();                                       // activations of the previous layer
       for (int it = blockIdx.x; it < total; it += gridDim.x) {
         const int txi = it % p.tiles_x, r = it / p.tiles_x;
         const int tyi = r % p.tiles_y, n = r / p.tiles_y;
         const int x0 = txi * TILE_W, y0 = tyi * ROWS;
         for (int c = 0; c < p.NC; ++c) {
+          if (dbg) tq = clock64();
           ptx::mbar_wait(a_empty + 8 * sa, pa ^ 1);
+          if (dbg) t6 += clock64() - tq;
           ptx::mbar_expect_tx(a_full + 8 * sa, C::A_STAGE);
           ptx::tma_load_4d(a_stage0 + sa * C::A_STAGE, &amap, a_full + 8 * sa, c * KC, x0 - 1, y0 - 1, n);
           if (++sa == SA) { sa = 0; pa ^= 1; }
-          for (int t = 0; t < 9; ++t) {
+        }
+      }
+      if (dbg) p.dbg[blockIdx.x * 8 + 6] = t6;
+    }
+  } else if (warp == 6) {
+    // ============================== weight producer ===========================
+    // Weights do not depend on the previous layer: no pdl_wait here, the first slices land while the predecessor drains.
+    if (ptx::elect_one()) {
+      const int nslice = p.NC * 9;
+      if (resident) {
+        for (int i = 0; i < nslice; ++i) {
+          ptx::mbar_expect_tx(w_full + 8 * i, C::W_SLICE);
+          ptx::bulk_load(w_stage0 + i * C::W_SLICE, p.wpack + (size_t)i * C::W_SLICE, C::W_SLICE, w_full + 8 * i);
+        }
+      } else {
+        const bool dbg = p.dbg != nullptr;
+        long long t7 = 0, tq = 0;
+        uint32_t sw = 0, pw = 0;
+        for (int it = blockIdx.x; it < total; it += gridDim.x)
+          for (int i = 0; i < nslice; ++i) {
+            if (dbg) tq = clock64();
             ptx::mbar_wait(w_empty + 8 * sw, pw ^ 1);
+            if (dbg) t7 += clock64() - tq;
             ptx::mbar_expect_tx(w_full + 8 * sw, C::W_SLICE);
-            ptx::bulk_load(w_stage0 + sw * C::W_SLICE, p.wpack + (size_t)(c * 9 + t) * C::W_SLICE, C::W_SLICE,
-                           w_full + 8 * sw);
+            ptx::bulk_load(w_stage0 + sw * C::W_SLICE, p.wpack + (size_t)i * C::W_SLICE, C::W_SLICE, w_full + 8 * sw);
             if (++sw == C::SW) { sw = 0; pw ^= 1; }
           }
-        }
+        if (dbg) p.dbg[blockIdx.x * 8 + 7] = t7;
       }
     }
   } else if (warp == 1) {
@@ -151,15 +194,25 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
     if (ptx::elect_one()) {
       constexpr uint32_t idesc = idesc_f16_f32(128, BN);
       uint32_t sa = 0, pa = 0, sw = 0, pw = 0, kk = 0;
+      const bool dbg = p.dbg != nullptr;
+      long long t1 = 0, t2 = 0, t3 = 0, tq = 0;
+      const long long tm0 = dbg ? clock64() : 0;
       for (int it = blockIdx.x; it < total; it += gridDim.x, ++kk) {
         const uint32_t slot = kk & 1, pacc = (kk >> 1) & 1;
+        if (dbg) tq = clock64();
         ptx::mbar_wait(acc_empty + 8 * slot, pacc ^ 1);   // the epilogue has drained this slot (first use passes at once)
+        if (dbg) t1 += clock64() - tq;
         ptx::tc_fence_after();
         for (int c = 0; c < p.NC; ++c) {
+          if (dbg) tq = clock64();
           ptx::mbar_wait(a_full + 8 * sa, pa);
+          if (dbg) t2 += clock64() - tq;
           const uint32_t abase = a_stage0 + sa * C::A_STAGE;
           for (int t = 0; t < 9; ++t) {
+            if (resident) { sw = c * 9 + t; pw = 0; }   // loaded once: phase 0 of its barrier stays complete
+            if (dbg) tq = clock64();
             ptx::mbar_wait(w_full + 8 * sw, pw);
+            if (dbg) t3 += clock64() - tq;
             ptx::tc_fence_after();
             const uint32_t tap_off = ((t / 3) * PITCH + (t % 3)) * 128;
             const uint64_t ad0 = ptx::smem_desc_sw128(abase + tap_off, 0);
@@ -173,14 +226,17 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
                 ptx::mma_bf16_ss(tmem + (slot * APS + a) * BN, ad, bd, idesc, (c | t | k) != 0);
               }
             }
-            ptx::tc_commit(w_empty + 8 * sw);
-            if (++sw == C::SW) { sw = 0; pw ^= 1; }
+            if (!resident) {
+              ptx::tc_commit(w_empty + 8 * sw);
+              if (++sw == C::SW) { sw = 0; pw ^= 1; }
+            }
           }
           ptx::tc_commit(a_empty + 8 * sa);
           if (++sa == SA) { sa = 0; pa ^= 1; }
         }
         ptx::tc_commit(acc_full + 8 * slot);
       }
+      if (dbg) { long long* d = p.dbg + blockIdx.x * 8; d[0] = clock64() - tm0; d[1] = t1; d[2] = t2; d[3] = t3; }
     }
   } else {
     // ============================== epilogue ==================================
@@ -202,6 +258,7 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
     }
     const int oh = p.ups2 ? 2 * p.H : p.H, ow = p.ups2 ? 2 * p.W : p.W;
     uint32_t kk = 0;
+    pdl_wait();                                         // residuals are read and the output buffer is written below
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++kk) {
       const uint32_t slot = kk & 1, pacc = (kk >> 1) & 1;
       const int txi = it % p.tiles_x, r = it / p.tiles_x;
@@ -211,7 +268,10 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
       bool pxok[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) pxok[i] = (8 * i + cpx < TILE_W) && (x0 + 8 * i + cpx < p.W);
+      const bool dbg = p.dbg != nullptr && warp == 2 && lane == 0;
+      const long long te0 = dbg ? clock64() : 0;
       ptx::mbar_wait(acc_full + 8 * slot, pacc);
+      const long long te1 = dbg ? clock64() : 0;
       ptx::tc_fence_after();
 #pragma unroll 1
       for (int u = 0; u < APS * GROUPS; ++u) {
@@ -302,6 +362,7 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(acc_empty + 8 * slot);
+      if (dbg) { p.dbg[blockIdx.x * 8 + 4] += te1 - te0; p.dbg[blockIdx.x * 8 + 5] += clock64() - te1; }
     }
   }
 

@@ -45,7 +45,8 @@ constexpr int MODE_FIRST64 = 3;
 // K layout: window row ky at k = 10 ky + (3 kx + c) (9 used of 10, so no operand pair straddles two rows), k = 30, 31 bias.
 // Per pixel: 9 aligned 32-bit loads + 9 funnel shifts + 15 PRMT instead of 27 byte loads + 27 I2F + 14 F2FP.
 constexpr int MODE_CONV1_H = 4;
-constexpr int I27_THREADS = 544;       // warps 0-3 / 4-7 two A-builder groups, warp 8 MMA, warps 9-12 / 13-16 two drain groups
+constexpr int I27_NDG = 3;             // drain groups (4 warps each) taking items k % 3: the drain is the longest role
+constexpr int I27_THREADS = 32 * (9 + 4 * I27_NDG);   // warps 0-3 / 4-7 two A-builder groups, warp 8 MMA, warps 9-12 / 13-16 / 17-20 drain groups
 constexpr int I27_SA = 4;              // A stages (128 rows x 128 B each); item sequence k uses stage k & 3
 constexpr int I27_MMA_WARP = 8;
 constexpr int I27_EPI_WARP0 = 9;
@@ -59,7 +60,7 @@ struct I27Cfg {
   static constexpr int W_BYTES = BN * 128;
   static constexpr int W_OFF = I27_SA * A_STAGE;
   static constexpr int STG_OFF = W_OFF + W_BYTES;
-  static constexpr int BAR_OFF = STG_OFF + 8 * I27_STG;
+  static constexpr int BAR_OFF = STG_OFF + 4 * I27_NDG * I27_STG;
   static constexpr int BIAS_OFF = BAR_OFF + 256;
   static constexpr int SMEM = BIAS_OFF + BN * 4 + 1024;
 };
@@ -129,42 +130,58 @@ im2col27_kernel(const I27Params p) {
     const bool dbg = p.dbg != nullptr && threadIdx.x == 0;
     long long tbw = 0;
     const long long tb0 = dbg ? clock64() : 0;
+    // ---- MODE_CONV1_H: the 3 x 9 window bytes of a pixel as 9 aligned 32-bit words (3 per row), fetched one item ahead
+    const uintptr_t lo = reinterpret_cast<uintptr_t>(p.in), hi = lo + (uintptr_t)p.npix * 3;
+    auto fetch_h = [&](long long pix, uint32_t (&raw)[9]) {
+#pragma unroll
+      for (int j = 0; j < 9; ++j) raw[j] = 0u;
+      if (pix >= p.npix) return;
+      const int y = (int)((pix / p.W) % p.H);
+      const uintptr_t a0 = lo + (uintptr_t)((pix - 1) * 3);               // byte address of pixel (y, x-1), channel 0
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky) {
+        const int yy = y + ky - 1;
+        if (yy < 0 || yy >= p.H) continue;                                // rows of padding stay zero
+        const uintptr_t wa = (a0 + (uintptr_t)((long long)(ky - 1) * p.W * 3)) & ~(uintptr_t)3;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) raw[3 * ky + j] = ldg_word_clipped(wa + 4 * j, lo, hi);
+      }
+    };
+    auto pack_h = [&](long long pix, const uint32_t (&raw)[9], uint32_t (&w)[16]) {
+      if (pix >= p.npix) return;
+      const int x = (int)(pix % p.W);
+      const uintptr_t a0 = lo + (uintptr_t)((pix - 1) * 3);
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky) {
+        const uint32_t sh = (uint32_t)((a0 + (uintptr_t)((long long)(ky - 1) * p.W * 3)) & 3) * 8;
+        uint32_t A0 = __funnelshift_r(raw[3 * ky], raw[3 * ky + 1], sh);   // the row's 9 window bytes, aligned
+        uint32_t A1 = __funnelshift_r(raw[3 * ky + 1], raw[3 * ky + 2], sh);
+        uint32_t A2 = raw[3 * ky + 2] >> sh;
+        if (x == 0) A0 &= 0xFF000000u;                                     // left neighbour is padding (bytes 0-2)
+        if (x == p.W - 1) { A1 &= 0x0000FFFFu; A2 = 0u; }                  // right neighbour is padding (bytes 6-8)
+        constexpr uint32_t C64 = 0x64646464u;
+        w[5 * ky + 0] = __byte_perm(A0, C64, 0x4140);
+        w[5 * ky + 1] = __byte_perm(A0, C64, 0x4342);
+        w[5 * ky + 2] = __byte_perm(A1, C64, 0x4140);
+        w[5 * ky + 3] = __byte_perm(A1, C64, 0x4342);
+        w[5 * ky + 4] = __byte_perm(A2, C64, 0x4440);                      // k = 10 ky + 9 is unused (zero weight)
+      }
+      w[15] = 0x3C003C00u;                                                 // k = 30, 31: 1.0 against the bias halves
+    };
+    uint32_t raw[9];
+    if (MODE == MODE_CONV1_H) {
+      const long long it0 = blockIdx.x + (long long)gi * gridDim.x;
+      if (it0 < items) fetch_h(it0 * 128 + r, raw);
+    }
     for (long long it = blockIdx.x + (long long)gi * gridDim.x; it < items; it += 2LL * gridDim.x) {
       const long long pix = it * 128 + r;
       uint32_t w[16], wlo[16];
 #pragma unroll
       for (int j = 0; j < 16; ++j) w[j] = wlo[j] = 0u;
       if (MODE == MODE_CONV1_H) {
-        if (pix < p.npix) {
-          const int x = (int)(pix % p.W);
-          const int y = (int)((pix / p.W) % p.H);
-          const uintptr_t lo = reinterpret_cast<uintptr_t>(p.in), hi = lo + (uintptr_t)p.npix * 3;
-          const uintptr_t a0 = lo + (uintptr_t)((pix - 1) * 3);           // byte address of pixel (y, x-1), channel 0
-#pragma unroll
-          for (int ky = 0; ky < 3; ++ky) {
-            const int yy = y + ky - 1;
-            uint32_t A0 = 0, A1 = 0, A2 = 0;                               // the row's 9 window bytes, aligned
-            if (yy >= 0 && yy < p.H) {
-              const uintptr_t a = a0 + (uintptr_t)((long long)(ky - 1) * p.W * 3);
-              const uintptr_t wa = a & ~(uintptr_t)3;
-              const uint32_t sh = (uint32_t)(a & 3) * 8;
-              const uint32_t w0 = ldg_word_clipped(wa, lo, hi), w1 = ldg_word_clipped(wa + 4, lo, hi),
-                             w2 = ldg_word_clipped(wa + 8, lo, hi);
-              A0 = __funnelshift_r(w0, w1, sh);
-              A1 = __funnelshift_r(w1, w2, sh);
-              A2 = w2 >> sh;
-              if (x == 0) A0 &= 0xFF000000u;                               // left neighbour is padding (bytes 0-2)
-              if (x == p.W - 1) { A1 &= 0x0000FFFFu; A2 = 0u; }            // right neighbour is padding (bytes 6-8)
-            }
-            constexpr uint32_t C64 = 0x64646464u;
-            w[5 * ky + 0] = __byte_perm(A0, C64, 0x4140);
-            w[5 * ky + 1] = __byte_perm(A0, C64, 0x4342);
-            w[5 * ky + 2] = __byte_perm(A1, C64, 0x4140);
-            w[5 * ky + 3] = __byte_perm(A1, C64, 0x4342);
-            w[5 * ky + 4] = __byte_perm(A2, C64, 0x4440);                  // k = 10 ky + 9 is unused (zero weight)
-          }
-          w[15] = 0x3C003C00u;                                             // k = 30, 31: 1.0 against the bias halves
-        }
+        pack_h(pix, raw, w);
+        const long long itn = it + 2LL * gridDim.x;          // the raw words are consumed: the next item's loads fly during the hand-off
+        if (itn < items) fetch_h(itn * 128 + r, raw);
       } else if (pix < p.npix && !(p.probe & 4)) {
         const int x = (int)(pix % p.W);
         const long long t = pix / p.W;
@@ -285,7 +302,12 @@ im2col27_kernel(const I27Params p) {
     const bool dbg = p.dbg != nullptr && ew == 0 && lane == 0;
     long long t5 = 0, t6 = 0;
     const long long td0 = dbg ? clock64() : 0;
-    for (long long it = blockIdx.x + (long long)ge * gridDim.x; it < items; it += 2LL * gridDim.x, k += 2) {
+    // A parity wait is only safe for a waiter that is at most one phase behind its barrier, so the groups that take items
+    // in turn must not outnumber the accumulators: with 2 accumulators (BN = 256) a third group's first item would be the
+    // SECOND use of accumulator 0, its wait for parity 1 would pass on the untouched barrier and it would drain garbage.
+    constexpr int NDG = C::NACC < I27_NDG ? C::NACC : I27_NDG;
+    for (long long it = ge < NDG ? blockIdx.x + (long long)ge * gridDim.x : items; it < items;
+         it += (long long)NDG * gridDim.x, k += NDG) {
       const uint32_t b = (uint32_t)(k % C::NACC), pb = (uint32_t)((k / C::NACC) & 1);
       const long long pix = it * 128 + q * 32 + lane;
       const bool valid = pix < p.npix;

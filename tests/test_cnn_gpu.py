@@ -499,3 +499,25 @@ def test_conv1_operand_builders_agree(enhancers, models, h, w):
         enhancers["seed0"].set_option("ws_budget_mb", prev)
     b = enhancers["seed0"].cnn_debug_f32(dev(frames), tap=1).cpu().numpy()
     assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("h,w", [(1, 1), (2, 3), (3, 15), (4, 16), (37, 53), (130, 70), (45, 16), (360, 480)])
+def test_fused_tail_generations_bit_identical(enhancers, h, w):
+    """option fuse_tail: 1 = default (relu(upconv1) written to shared memory in PixelShuffle order as the A operand of the
+    second GEMM), 3 = the variant that keeps it in TENSOR memory (the PixelShuffle becomes four phase planes indexed by the
+    low-res pixel, the second GEMM reads its A operand from TMEM).  Same products, same K order per accumulator, same tap order in the gather: the uint8
+    frames and the pre-quantisation fp32 output must be bit-identical, on ragged tiles and image borders too."""
+    rng = np.random.default_rng(55)
+    frames = [synth.random_frame(h, w, rng), synth.edges_frame(h, w, rng), synth.random_frame(h, w, rng)]
+    for key in ("seed0", "stress"):
+        enh = enhancers[key]
+        a8 = enh.upscale_device(dev(frames), mode="cnn", out_bgr=True).cpu().numpy()
+        a = enh.cnn_debug_f32(dev(frames), tap=0).cpu().numpy()
+        prev = enh.set_option("fuse_tail", 3)
+        try:
+            b8 = enh.upscale_device(dev(frames), mode="cnn", out_bgr=True).cpu().numpy()
+            b = enh.cnn_debug_f32(dev(frames), tap=0).cpu().numpy()
+        finally:
+            enh.set_option("fuse_tail", prev)
+        assert np.array_equal(a, b), (key, h, w, float(np.abs(a - b).max()))
+        assert np.array_equal(a8, b8), (key, h, w)

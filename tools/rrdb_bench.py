@@ -13,6 +13,9 @@ peaks = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_P
     os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")) else {"bf16_tflops": 1646.9}
 hd = B200RealESRGAN(device="cuda:0", scale=4, seed=0, num_block=nb)
 hd._ensure_model_loaded()
+for kv in sys.argv[2:]:
+    k, v = kv.split("=")
+    print("option", k, v, "was", hd._lib.vex_set_option(hd._ctx, k.encode(), int(v)), file=sys.stderr)
 flop_px = R.flops_per_input_pixel(4, nb)
 rng = np.random.default_rng(0)
 res = {"num_block": nb, "flop_per_input_pixel": flop_px}

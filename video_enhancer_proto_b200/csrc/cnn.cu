@@ -19,6 +19,7 @@
 #include "conv_tc3.cuh"
 #include "thin_tc.cuh"
 #include "tail_tc.cuh"
+#include "tail_tc2.cuh"
 #include "vex_internal.cuh"
 
 namespace vex {
@@ -418,9 +419,15 @@ int launch_g27(vex_ctx* ctx, unsigned abit, const __nv_bfloat16* in, int C, cons
 // x5 [n][H][W] -> uint8 [n][2H][2W][3]: upconv1 + relu + upconv2 + clamp + quantise in one kernel (tail_tc.cuh)
 int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_t* w2, const float* b2,
                   uint8_t* out_u8, float* out_nchw, int n, int H, int W, int out_bgr, cudaStream_t s) {
+  // fuse_tail: 1 = default (relu(upconv1) handed to the second GEMM through shared memory, tail_tc.cuh); 3 = the variant
+  // that keeps it in tensor memory (tail_tc2.cuh: bit-identical, 40 % less shared-memory traffic, but with TMEM full its
+  // stages cannot be double-buffered and it measures 2287 against 1961 cycles per item)
+  const bool v2 = ctx->opt_fuse_tail == 3;
   if (!(ctx->attr_mask & 0x400u)) {
     VEX_CUDA(ctx, cudaFuncSetAttribute(thin::uptail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        thin::UTCfg::SMEM));
+    VEX_CUDA(ctx, cudaFuncSetAttribute(thin::uptail2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       thin::UT2Cfg::SMEM));
     ctx->attr_mask |= 0x400u;
   }
   thin::UTParams p;
@@ -450,7 +457,8 @@ int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_
         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(ctx, VEX_ERR_CUDA, "cuTensorMapEncodeTiled (x5) failed (" + std::to_string((int)r) + ")");
   }
-  thin::uptail_kernel<<<grid, thin::UT_THREADS, thin::UTCfg::SMEM, s>>>(xmap, p);
+  if (v2) thin::uptail2_kernel<<<grid, thin::UT_THREADS, thin::UT2Cfg::SMEM, s>>>(xmap, p);
+  else thin::uptail_kernel<<<grid, thin::UT_THREADS, thin::UTCfg::SMEM, s>>>(xmap, p);
   ctx->launches++;
   VEX_CUDA(ctx, cudaGetLastError());
   if (p.dbg) {

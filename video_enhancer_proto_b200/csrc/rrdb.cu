@@ -146,6 +146,7 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, const __half* in, int in_cs, cons
   p.tiles_y = (H + rrdb::ROWS - 1) / rrdb::ROWS;
   p.n_img = n;
   p.dbg = nullptr;
+  p.force_ring = ctx->opt_rrdb_ring;
   const long long total = (long long)p.tiles_x * p.tiles_y * n;
   if (total > 0x7fffffffLL) return fail(ctx, VEX_ERR_INVALID, "rrdb conv: too many tiles");
   if (ctx->opt_conv_dbg) {

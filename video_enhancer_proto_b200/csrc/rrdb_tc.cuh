@@ -73,6 +73,7 @@ struct Params {
   int ups2;               // store every pixel to the 2 x 2 block of a twice as large output (nearest-neighbour upsample)
   int H, W, NC;           // NC = 64-channel chunks of the input that are read
   int tiles_x, tiles_y, n_img;
+  int force_ring;         // A/B switch (option rrdb_ring): stream the weights through the slice buffer even when they would fit
   long long* dbg;         // optional [gridDim.x][8] cycle counters (option conv_dbg): MMA thread 0 total, 1 wait acc_empty, 2 wait a_full,
                           // 3 wait w_full; epilogue warp 2: 4 wait acc_full, 5 work; producer: 6 wait a_empty, 7 wait w_empty
 };
@@ -138,7 +139,7 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot_p;
-  const bool resident = p.NC * 9 <= C::SW;              // every weight slice of the layer fits the slice buffer
+  const bool resident = p.NC * 9 <= C::SW && !p.force_ring;   // every weight slice of the layer fits the slice buffer
   pdl_launch_dependents();                              // the next layer may begin its prologue
 
   if (warp == 0) {
@@ -211,7 +212,9 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
           for (int t = 0; t < 9; ++t) {
             if (resident) { sw = c * 9 + t; pw = 0; }   // loaded once: phase 0 of its barrier stays complete
             if (dbg) tq = clock64();
-            ptx::mbar_wait(w_full + 8 * sw, pw);
+            // even an already-complete mbarrier wait costs ~100 clocks of this one issuing thread (measured: 16 % of an item),
+            // so resident slices are waited for during the first item only
+            if (!resident || kk == 0) ptx::mbar_wait(w_full + 8 * sw, pw);
             if (dbg) t3 += clock64() - tq;
             ptx::tc_fence_after();
             const uint32_t tap_off = ((t / 3) * PITCH + (t % 3)) * 128;

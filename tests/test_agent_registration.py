@@ -185,3 +185,31 @@ def test_agent_dispatch_runs_the_b200_handler(tmp_path):
         assert info["scale"] == 2 and "name" in info and "description" in info
     finally:
         handler.close()
+
+
+@pytest.mark.gpu
+def test_agent_realesrgan_branch_runs_the_b200_handler(tmp_path):
+    """The agent's own 'realesrgan' branch (video_enhancer_sota.py:353-356) served by the GPU twin of RealESRGANHandler:
+    `restore_video(input_path=, output_path=)` -> the statistics dictionary of realesrgan_handler.py:265-273."""
+    cv2 = pytest.importorskip("cv2")
+    from video_enhancer_proto_b200 import B200RealESRGAN, synth
+    src = tmp_path / "in.mp4"
+    wr = cv2.VideoWriter(str(src), cv2.VideoWriter_fourcc(*"mp4v"), 24.0, (64, 48))
+    if not wr.isOpened():
+        pytest.skip("OpenCV cannot write mp4v here")
+    rng = np.random.default_rng(0)
+    for i in range(5):
+        wr.write(synth.demo_frame(i, size=(64, 48), rng=rng, bgr=True))
+    wr.release()
+    handler = B200RealESRGAN(device="cuda:0", scale=4, seed=0, num_block=1)
+    try:
+        agent = A.AgentRef({"realesrgan": handler})
+        task = types.SimpleNamespace(task_id="job-8", task_type="video_enhancement",
+                                     input_data={"video_path": str(src), "analysis_result": {"task_type": "super_resolution"}})
+        r = agent.handle_video_enhancement(task)                        # _select_model picks 'realesrgan' (:297-299)
+        assert r.status is A.TaskStatus.COMPLETED
+        assert r.metadata == {"model_used": "realesrgan", "enhancement_type": "2025_sota", "frames_processed": 5}
+        assert r.output_data["output_resolution"] == (192, 256) and r.output_data["scale_factor"] == 4
+        assert (tmp_path / "in_sota_enhanced.mp4").exists()
+    finally:
+        handler.close()

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark of the per-frame 2x upscaler hot path on B200.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cnn|bicubic|stream|wide] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cnn|bicubic|stream|wide|rrdb] [--impl reference]
 
 One JSON line on stdout (rank 0).  Metric (BASELINE.json): 2x-SR frames/sec at 1080p->2160p.
 
@@ -48,6 +48,7 @@ def load_peaks():
 
 PROFILE_CNN_CSV = ("profiles/r2_ncu_full_cnn.csv", "profiles/r1_v7_ncu_full_cnn.csv")        # newest first
 PROFILE_BIC_CSV = ("profiles/r2_ncu_full_bicubic.csv", "profiles/r1_v7_ncu_full_bicubic.csv")
+PROFILE_WIDE_CSV = ("profiles/r2_ncu_full_wide.csv",)          # conv3x3_tc launches of ONE 2160p frame of the configs[4] plan
 _UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
 
 
@@ -610,6 +611,8 @@ def gpu_wide(args, world, rank, local, warmup, peaks, torch, dist, synth, _lib):
     enh.close()
     if rank != 0:
         return
+    tr, wide_src, wide_n, _ = ncu_traffic(PROFILE_WIDE_CSV, r"conv3x3_tc_kernel")   # mean DRAM bytes per conv3x3_tc launch, one frame
+    wide_traffic = int(tr) if tr else None
     print(json.dumps({
         "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": steps, "warmup": warmup,
         "ms_per_step": total_ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -627,11 +630,103 @@ def gpu_wide(args, world, rank, local, warmup, peaks, torch, dist, synth, _lib):
                 "d2h_bytes_per_step": fps_step * fin * 4, "frames_per_step": fps_step, "steps": e2e_steps,
                 "api": "vex_upscale_host (pinned host in/out, one frame per chunk)"},
         "roofline": {"bound": "tensor", "kernel": "conv3x3_tc_kernel (conv2, conv3 + 2 extra blocks, conv4: 5 launches/frame)",
-                     "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                     "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                     "traffic": wide_traffic, "traffic_source": wide_src, "traffic_launches": wide_n,
+                     "frac_of_burst_peak": achieved / peaks["bf16_tflops"],
                      "peak_source": peaks["source"] + " (sustained cuBLAS bf16)",
                      "algorithmic_flop_per_step": tc_flop, "kernel_ms_per_step": tc_ms,
                      "kernel_share_of_step": tc_ms / (total_ms / steps), "layer_ms": prof,
                      "whole_net_tflops": all_flop / (total_ms / steps / 1e3) / 1e12}}), flush=True)
+
+
+def gpu_rrdb(args, world, rank, local, warmup, peaks, torch, dist, synth):
+    """Real-ESRGAN RRDBNet (23 blocks, x4, seeded random weights - the handler's own fallback when no
+    checkpoint is found, realesrgan_handler.py:153-156) on 1080p frames -> 4320p, each frame through the reference's tile
+    loop (tile 512, pad 10: 12 tiles, :324-372), frames sharded over the ranks.  value: frames resident in HBM; e2e: the
+    handler method `_enhance_frame` (host ndarray in, host ndarray out).  The CPU baseline is the oracle on ONE padded tile,
+    scaled to a frame by pixel count (stated in `sample`)."""
+    from oracle import realesrgan_ref as R
+    from video_enhancer_proto_b200 import B200RealESRGAN
+    hd = B200RealESRGAN(device=f"cuda:{local}", scale=4, seed=0, num_block=23)
+    hd._ensure_model_loaded()
+    fps_step = args.frames or 2
+    steps = max(2, min(args.steps, 5))
+    rng = np.random.default_rng(1234 + rank)
+    frames = [synth.random_frame(H, W, rng) if i % 2 == 0 else synth.edges_frame(H, W, rng) for i in range(fps_step)]
+    dev = [torch.from_numpy(f).cuda() for f in frames]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        for d in dev:
+            hd.frame_device(d, in_bgr=True, out_bgr=True)
+    for _ in range(max(1, warmup // 3)):
+        step()
+    barrier()
+    l0 = hd.kernel_launches()
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    launches = hd.kernel_launches() - l0
+    t = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    value = world * fps_step * steps / (total_ms / 1e3)
+    plan = R.tile_plan(H, W, 512, 10)
+    px = sum((py1 - py0) * (px1 - px0) for (py0, py1, px0, px1, *_r) in plan)       # what the reference's loop computes on
+    flop = R.flops_per_input_pixel(4, 23) * px
+    achieved = flop * fps_step * steps / (total_ms / 1e3) / 1e12
+    hd._enhance_frame(frames[0])
+    barrier()
+    t0 = time.perf_counter()
+    n_e2e = max(2, fps_step)
+    for i in range(n_e2e):
+        out = hd._enhance_frame(frames[i % fps_step])
+    dt = torch.tensor([time.perf_counter() - t0], device="cuda")
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    assert out.shape == (4 * H, 4 * W, 3)
+    line = {"metric": "Real-ESRGAN x4 frames/sec at 1080p->4320p (reference tile loop)", "value": value, "unit": "frames/s",
+            "n_gpus": world, "steps": steps, "warmup": max(1, warmup // 3), "ms_per_step": total_ms / steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+            "config": {"workload": "Real-ESRGAN RRDBNet 23 blocks x4, 1080p->4320p, tile 512 pad 10 (SURVEY 8(f)4)",
+                       "frames_per_step_per_gpu": fps_step, "tiles_per_frame": len(plan), "pixels_per_frame_incl_padding": px,
+                       "weights": "random-init (torch default Conv2d init, seed 0)", "flop_per_frame": flop,
+                       "l2": "2.2 GB of activations per tile > 126 MB L2, no flush"},
+            "clocks": clocks, "gpu_launches": int(launches),
+            "e2e": {"value": world * n_e2e / float(dt.item()), "unit": "frames/s", "h2d_bytes_per_step": H * W * 3,
+                    "d2h_bytes_per_step": H * W * 3 * 16, "api": "B200RealESRGAN._enhance_frame(ndarray BGR) -> ndarray BGR"},
+            "roofline": {"bound": "tensor", "kernel": "rconv3x3_kernel (345 of the 351 launches per tile)", "achieved": achieved,
+                         "peak": peaks["bf16_tflops"], "unit": "TFLOP/s", "frac": achieved / peaks["bf16_tflops"],
+                         "traffic": None, "peak_source": peaks["source"] + " (burst cuBLAS bf16; fp16 has the same dense rate)",
+                         "algorithmic_flop_per_step": flop * fps_step,
+                         "note": "whole pass incl. the 6 thin launches per tile; N = 32 / 64 MMAs are shared-memory bound (DESIGN.md 4)"}}
+    if world == 1 and not args.no_cpu_baseline:
+        model = R.make_network(0, 4, 23)
+        torch.set_num_threads(os.cpu_count() or 1)
+        py0, py1, px0, px1 = plan[5][:4]                                  # an interior tile: 532 x 532 with padding
+        tile = np.ascontiguousarray(frames[0][py0:py1, px0:px1])
+        t0 = time.perf_counter()
+        R.process_single(model, tile)
+        dtc = time.perf_counter() - t0
+        tpx = (py1 - py0) * (px1 - px0)
+        line["cpu_baseline"] = {"value": 1.0 / (dtc * px / tpx), "unit": "frames/s", "cores": os.cpu_count() or 1, "kind": "port",
+                                "sample": f"one padded tile {py1 - py0}x{px1 - px0} of the 12 ({tpx / px:.3f} of a frame's pixels) "
+                                          f"through the oracle in {dtc:.1f} s, torch CPU fp32, scaled by pixel count"}
+    hd.close()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
 
 
 def main():
@@ -640,7 +735,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=["cnn", "bicubic", "stream", "wide"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=["cnn", "bicubic", "stream", "wide", "rrdb"])
     ap.add_argument("--frames", type=int, default=0, help="frames per step per GPU (0 = workload default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the secondary objects (bicubic, e2e_plugin, stream, demo480, e2e_file)")
@@ -678,6 +773,12 @@ def main():
             os.close(saved)
     warmup = max(args.warmup, 3)
     peaks = load_peaks()
+    if workload == "rrdb":                                  # SURVEY 8(f)4; a reporting workload, not the driver's default
+        gpu_rrdb(args, world, rank, local, warmup, peaks, torch, dist, synth)
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
     if workload == "wide":                                  # configs[4]; a reporting workload, not the driver's default
         gpu_wide(args, world, rank, local, warmup, peaks, torch, dist, synth, _lib)
         if world > 1:

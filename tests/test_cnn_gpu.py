@@ -521,3 +521,20 @@ def test_fused_tail_generations_bit_identical(enhancers, h, w):
             enh.set_option("fuse_tail", prev)
         assert np.array_equal(a, b), (key, h, w, float(np.abs(a - b).max()))
         assert np.array_equal(a8, b8), (key, h, w)
+
+
+def test_nvtx_option_and_unknown_option(enhancers):
+    """option nvtx: one NVTX range per layer launch; without a profiler attached it must be a no-op
+    that changes no pixel.  Unknown option names are errors, not silently ignored."""
+    rng = np.random.default_rng(3)
+    d = dev([synth.random_frame(40, 64, rng)])
+    enh = enhancers["seed0"]
+    a = enh.upscale_device(d, mode="cnn").cpu().numpy()
+    prev = enh.set_option("nvtx", 1)
+    try:
+        b = enh.upscale_device(d, mode="cnn").cpu().numpy()
+        c = enh.cnn_debug_f32(d, tap=3).cpu().numpy()                   # early-return path closes its ranges too
+    finally:
+        enh.set_option("nvtx", prev)
+    assert np.array_equal(a, b) and np.isfinite(c).all()
+    assert enh.set_option("no_such_option", 1) == -1

@@ -84,11 +84,26 @@ class B200BasicUpscaler:
                    "vex_filter3x3_u8")
         return out
 
-    def enhance_frames(self, frames: Sequence[np.ndarray]) -> List[np.ndarray]:
-        B200VideoEnhancer._check_frames(frames)
-        x = torch.from_numpy(np.stack(frames)).to(self._enh.device if self._enh.device != "cuda" else "cuda:0")
-        y = self.upscale_device(x).cpu().numpy()
-        return [y[i] for i in range(y.shape[0])]
+    def enhance_frames(self, frames: Sequence[np.ndarray], slot: int = 0) -> List[np.ndarray]:
+        """Host frames through the pipeline: pinned staging on both sides (asynchronous H2D / D2H on the current stream,
+        one synchronisation at the end).  The returned arrays are views of the pinned result buffer of `slot`: valid until
+        the next call with that slot (the video loop rotates slots, other callers copy what they keep)."""
+        h, w = B200VideoEnhancer._check_frames(frames)
+        n, fin = len(frames), h * w * 3
+        e = self._enh
+        pin_in = e._pinned_buf("b_in", n * fin)
+        pin_out = e._pinned_buf(f"b_out{slot}", n * fin * 4)
+        vin = pin_in.numpy()[: n * fin].reshape(n, h, w, 3)
+        for i, f in enumerate(frames):
+            vin[i] = f
+        dev = torch.device(e.device if e.device != "cuda" else "cuda:0")
+        x = e._device_buf("b_in", n * fin)[: n * fin].view(n, h, w, 3)
+        x.copy_(pin_in[: n * fin].view(n, h, w, 3), non_blocking=True)
+        y = self.upscale_device(x)
+        pin_out[: n * fin * 4].view(n, 2 * h, 2 * w, 3).copy_(y, non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        res = pin_out.numpy()[: n * fin * 4].reshape(n, 2 * h, 2 * w, 3)
+        return [res[i] for i in range(n)]
 
     # ------------------------------------------------------------------ handler protocol
     def enhance_video(self, input_path: str, output_path: str) -> Dict:
@@ -118,7 +133,7 @@ class B200BasicUpscaler:
                 return batch or None
 
             def process(batch, slot):
-                return self.enhance_frames(batch)
+                return self.enhance_frames(batch, slot=slot)
 
             def write(res):
                 nonlocal processed

@@ -420,8 +420,8 @@ int launch_g27(vex_ctx* ctx, unsigned abit, const __nv_bfloat16* in, int C, cons
 int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_t* w2, const float* b2,
                   uint8_t* out_u8, float* out_nchw, int n, int H, int W, int out_bgr, cudaStream_t s) {
   // fuse_tail: 1 = default (relu(upconv1) handed to the second GEMM through shared memory, tail_tc.cuh); 3 = the variant
-  // that keeps it in tensor memory (tail_tc2.cuh: bit-identical, 40 % less shared-memory traffic, but with TMEM full its
-  // stages cannot be double-buffered and it measures 2287 against 1961 cycles per item)
+  // that keeps it in tensor memory (tail_tc2.cuh: bit-identical, 40 % less shared-memory traffic, two issuing threads; it
+  // measures 2007-2022 against 1960 cycles per item - a tie, the tail is bound by warp-instruction issue)
   const bool v2 = ctx->opt_fuse_tail == 3;
   if (!(ctx->attr_mask & 0x400u)) {
     VEX_CUDA(ctx, cudaFuncSetAttribute(thin::uptail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -472,9 +472,9 @@ int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_
     const double items = (double)total / grid, e_items = std::max(1.0, a[12]);
     fprintf(stderr, "[uptail_dbg] items/cta=%.1f cycles/item: MMA total=%.0f wait_a1_full=%.0f wait_acc1_empty=%.0f wait_acc2_empty=%.0f "
                     "wait_a2_full=%.0f | builder total=%.0f wait_a1_empty=%.0f wait_x_full=%.0f | mid-drain total=%.0f wait_a2_empty=%.0f wait_acc1_full=%.0f "
-                    "tmem_ld=%.0f | epilogue(group 0, per own item) total=%.0f wait_acc2_full=%.0f\n",
+                    "tmem_ld=%.0f tmem_st=%.0f | epilogue(group 0, per own item) total=%.0f wait_acc2_full=%.0f\n",
             items, a[0] / items, a[1] / items, a[2] / items, a[3] / items, a[4] / items, a[6] / items, a[5] / items,
-            a[13] / items, a[9] / items, a[7] / items, a[8] / items, a[14] / items, a[11] / e_items, a[10] / e_items);
+            a[13] / items, a[9] / items, a[7] / items, a[8] / items, a[14] / items, a[15] / items, a[11] / e_items, a[10] / e_items);
   }
   return VEX_OK;
 }

@@ -20,12 +20,23 @@
 // Results are bit-identical to tail_tc.cuh (same products, same K order per accumulator, same tap order in the gather;
 // tests/test_cnn_gpu.py::test_fused_tail_generations_bit_identical).
 //
-// STATUS: a measured variant (option fuse_tail = 3), not the default.  The 512 TMEM columns are all taken (256 + 128 + 128), so
-// neither the first accumulator nor the A2 planes nor Y can be double-buffered, and GEMM #2 of item k-1, GEMM #1 of item k
-// and the mid-drain of item k run strictly one after the other: 2287 cycles per item against 1961 for the shared-memory
-// hand-off of tail_tc.cuh, whose two A2 stages let the mid-drain of item k overlap GEMM #2 of item k-1 (B200, batch 8 at
-// 1080p, option conv_dbg: the MMA thread waits 999 cycles per item for the A2 planes, the mid-drain 611 for the first GEMM).
-// What would make it pay: fp16 accumulators for the first GEMM (half the columns -> room for a second buffer).
+// Pipelining.  The 512 TMEM columns are all taken (256 + 128 + 128), but every buffer exists once PER HALF (phase pair):
+// unit (item k, half h) flows GEMM #1 -> acc1[h] -> mid-drain group h -> A2[h] -> GEMM #2 -> Y[h] -> epilogue, and the two
+// halves are independent pipelines.  The first version issued all four GEMMs of an item from ONE thread in program order
+// (GEMM #2 of item k-1 for both halves, then GEMM #1 of item k): blocked on one half's barrier it could not serve the
+// other, everything ran in series and an item took 2287 cycles against 1961 for tail_tc.cuh (option conv_dbg: the MMA
+// thread waited 999 cycles per item for the A2 planes).  Now each half has its OWN issuing thread (warp 7 / warp 3), the
+// mid-drain hands the accumulator back as soon as it has been read (before the last store), and only 3 builder warps remain
+// (85 live patch rows): 2007-2022 cycles per item.
+//
+// STATUS: a measured variant (option fuse_tail = 3), not the default - it ties with tail_tc.cuh (1960 cycles per item) and
+// does not beat it.  The counters say why: the mid-drain warps are still "busy" ~1360 cycles per item although their
+// tcgen05.ld take 108 and their tcgen05.st 96 of them and they touch no shared memory at all.  What is left is their
+// instruction stream itself (64 conversions + 64 selects + addressing per thread and item) issued at ~0.25 instructions
+// per clock, because 24 warps share four schedulers that are 58 % busy (ncu: issue active 58 %, ALU 48 %).  The tail is
+// bound by warp-instruction issue across its five roles, not by TMEM, not by shared memory alone; the next lever is fewer
+// instructions per output pixel (a 16 x 16 halo tile: 196 instead of 180 outputs for the same work; the 3-tap row sums of
+// the gather by warp shuffles), not another data path.
 #pragma once
 
 #include "tail_tc.cuh"
@@ -73,7 +84,7 @@ uptail2_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
   const uint32_t a2_full = bar0 + 64, a2_empty = bar0 + 80;          // per half of the A2 planes in TMEM
   // Y is single-buffered, but each epilogue group has ITS OWN "full" barrier (completing once per item of that group): a
   // parity wait is only safe for a waiter at most one phase behind, and three groups taking turns on one barrier are not.
-  const uint32_t y_full = bar0 + 96, y_empty = bar0 + 96 + 8 * UT_EPI_GROUPS;
+  const uint32_t y_full = bar0 + 96, y_empty = bar0 + 96 + 16 * UT_EPI_GROUPS;     // y_full[group][half], y_empty[half]
   const uint32_t w_bar = bar0 + 160, tmem_slot = bar0 + 168;
   const uint32_t x_full = bar0 + 176, x_empty = bar0 + 176 + 8 * UT_XS;
   volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(sm + C::BAR_OFF + 168);
@@ -84,14 +95,14 @@ uptail2_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < 2; ++i) {
-      ptx::mbar_init(a1_full + 8 * i, 128); ptx::mbar_init(a1_empty + 8 * i, 1);
+      ptx::mbar_init(a1_full + 8 * i, 96); ptx::mbar_init(a1_empty + 8 * i, 2);      // 3 builder warps; both issuing threads
       ptx::mbar_init(a2_full + 8 * i, 3); ptx::mbar_init(a2_empty + 8 * i, 1);
       ptx::mbar_init(acc1_full + 8 * i, 1); ptx::mbar_init(acc1_empty + 8 * i, 3);
+      ptx::mbar_init(y_empty + 8 * i, 3);
     }
-    for (int i = 0; i < UT_EPI_GROUPS; ++i) ptx::mbar_init(y_full + 8 * i, 1);
-    ptx::mbar_init(y_empty, 3);
+    for (int i = 0; i < 2 * UT_EPI_GROUPS; ++i) ptx::mbar_init(y_full + 8 * i, 1);
     ptx::mbar_init(w_bar, 1);
-    for (int i = 0; i < UT_XS; ++i) { ptx::mbar_init(x_full + 8 * i, 1); ptx::mbar_init(x_empty + 8 * i, 128); }
+    for (int i = 0; i < UT_XS; ++i) { ptx::mbar_init(x_full + 8 * i, 1); ptx::mbar_init(x_empty + 8 * i, 96); }
     ptx::fence_mbar_init();
     ptx::prefetch_tensormap(&xmap);
   }
@@ -104,8 +115,9 @@ uptail2_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot_p;
 
-  if (warp < 4) {
-    // ================================ builders: low-res pixel r of the 5 x 17 patch -> one operand row (as tail_tc.cuh)
+  if (warp < 3) {
+    // ================================ builders: low-res pixel r of the 5 x 17 patch -> one operand row (as tail_tc.cuh);
+    // rows 96-127 of the operand are never written and the accumulator lanes they feed are never read
     const int r = threadIdx.x;
     const int lr = r / UT_LC, lc = r - lr * UT_LC;
     uint32_t k = 0;
@@ -162,62 +174,57 @@ uptail2_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
         ptx::tma_load_4d(sbase + C::X_OFF + xs * UT_X_STAGE, &xmap, x_full + 8 * xs, 0, 15 * txi - 2, 3 * tyi - 2, n);
       }
     }
-  } else if (warp == UT_MMA_WARP) {
-    // ================================ both GEMMs from one thread.  Per item k: GEMM #2 of item k-1 (its A2 planes were
-    // finished by the mid-drain while GEMM #1 of item k-1 drained), then GEMM #1 of item k.
+  } else if (warp == UT_MMA_WARP || warp == 3) {
+    // ================================ one issuing thread per half h (warp 7: phases 0-1, warp 3: phases 2-3).  Per item k:
+    // GEMM #1 of (k, h) into acc1[h], then GEMM #2 of (k-1, h) from the A2 planes of that half into Y[h].
+    const int h = warp == UT_MMA_WARP ? 0 : 1;
     if (ptx::elect_one()) {
-      ptx::mbar_expect_tx(w_bar, 256 * 128 + 4096);
-      ptx::bulk_load(sbase + C::W1_OFF, p.w1pack, 256 * 128, w_bar);
-      ptx::bulk_load(sbase + C::W2_OFF, p.w2pack, 4096, w_bar);
+      if (h == 0) {
+        ptx::mbar_expect_tx(w_bar, 256 * 128 + 4096);
+        ptx::bulk_load(sbase + C::W1_OFF, p.w1pack, 256 * 128, w_bar);
+        ptx::bulk_load(sbase + C::W2_OFF, p.w2pack, 4096, w_bar);
+      }
       ptx::mbar_wait(w_bar, 0);
       constexpr uint32_t idesc1 = ptx::idesc_bf16_f32(128, 128);
       constexpr uint32_t idesc2 = ptx::idesc_bf16_f32(128, 32);
-      const uint64_t a1d0 = ptx::smem_desc_sw128(sbase + C::A1_OFF, 0), w1d = ptx::smem_desc_sw128(sbase + C::W1_OFF, 0);
+      const uint64_t a1d0 = ptx::smem_desc_sw128(sbase + C::A1_OFF, 0);
+      const uint64_t w1d = ptx::smem_desc_sw128(sbase + C::W1_OFF + h * 16384, 0);
       const uint64_t w2d = ptx::smem_desc_sw128(sbase + C::W2_OFF, 0);
-      const bool dbg = p.dbg != nullptr;
+      const bool dbg = p.dbg != nullptr && h == 0;
       long long t1 = 0, t2 = 0, t3 = 0, t4 = 0, tq = 0;
       const long long tm0 = dbg ? clock64() : 0;
-      auto gemm2 = [&](uint32_t j) {                  // item j: 4 phase planes, each [128 x 64] x [64 x 32]
+      auto gemm2 = [&](uint32_t j) {                  // unit (j, h): two phase planes, each [128 x 64] x [64 x 32]
         if (dbg) tq = clock64();
-        ptx::mbar_wait(y_empty, (j & 1) ^ 1);        // the epilogue of item j-1 has drained Y
+        ptx::mbar_wait(y_empty + 8 * h, (j & 1) ^ 1);  // the epilogue of item j-1 has drained this half of Y
         if (dbg) { const long long n = clock64(); t3 += n - tq; tq = n; }
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          ptx::mbar_wait(a2_full + 8 * h, j & 1);
-          ptx::tc_fence_after();
-#pragma unroll
-          for (int pp = 0; pp < 2; ++pp)
-#pragma unroll
-            for (int kk = 0; kk < 4; ++kk)
-              mma_bf16_ts(tmem + TM_Y + (2 * h + pp) * 32, tmem + TM_A2 + (2 * h + pp) * 32 + kk * 8,
-                          ptx::desc_advance(w2d, kk * 32), idesc2, kk != 0);
-          ptx::tc_commit(a2_empty + 8 * h);
-        }
+        ptx::mbar_wait(a2_full + 8 * h, j & 1);
         if (dbg) t4 += clock64() - tq;
-        ptx::tc_commit(y_full + 8 * (j % UT_EPI_GROUPS));
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int pp = 0; pp < 2; ++pp)
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)
+            mma_bf16_ts(tmem + TM_Y + (2 * h + pp) * 32, tmem + TM_A2 + (2 * h + pp) * 32 + kk * 8,
+                        ptx::desc_advance(w2d, kk * 32), idesc2, kk != 0);
+        ptx::tc_commit(a2_empty + 8 * h);
+        ptx::tc_commit(y_full + 8 * (2 * (j % UT_EPI_GROUPS) + h));
       };
       uint32_t k = 0;
       for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
-        if (k > 0) gemm2(k - 1);
         const uint32_t sa = k & 1, pa = (k >> 1) & 1;
         if (dbg) tq = clock64();
         ptx::mbar_wait(a1_full + 8 * sa, pa);
-        if (dbg) t1 += clock64() - tq;
+        if (dbg) { const long long n = clock64(); t1 += n - tq; tq = n; }
+        ptx::mbar_wait(acc1_empty + 8 * h, (k & 1) ^ 1);
+        if (dbg) t2 += clock64() - tq;
+        ptx::tc_fence_after();
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          if (dbg) tq = clock64();
-          ptx::mbar_wait(acc1_empty + 8 * h, (k & 1) ^ 1);
-          if (dbg) t2 += clock64() - tq;
-          ptx::tc_fence_after();
-#pragma unroll
-          for (int kk = 0; kk < 2; ++kk) {
-            const uint64_t ad = ptx::desc_advance(a1d0, sa * C::A1_STAGE + kk * 32);
-            const uint64_t bd = ptx::desc_advance(w1d, h * 16384 + kk * 32);
-            ptx::mma_bf16_ss(tmem + h * 128, ad, bd, idesc1, kk);
-          }
-          ptx::tc_commit(acc1_full + 8 * h);
-        }
-        ptx::tc_commit(a1_empty + 8 * sa);
+        for (int kk = 0; kk < 2; ++kk)
+          ptx::mma_bf16_ss(tmem + h * 128, ptx::desc_advance(a1d0, sa * C::A1_STAGE + kk * 32), ptx::desc_advance(w1d, kk * 32),
+                           idesc1, kk);
+        ptx::tc_commit(acc1_full + 8 * h);
+        ptx::tc_commit(a1_empty + 8 * sa);             // the stage is free when BOTH halves' MMAs have read it (count 2)
+        if (k > 0) gemm2(k - 1);
       }
       if (k > 0) gemm2(k - 1);
       if (dbg) {
@@ -225,7 +232,7 @@ uptail2_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
         d[0] = clock64() - tm0; d[1] = t1; d[2] = t2; d[3] = t3; d[4] = t4;
       }
     }
-  } else if (warp < 11) {   // (warp 7 = MMA was taken above)
+  } else if (warp < 11) {   // warps 4-6 and 8-10 (3 and 7 issue the MMAs)
     // ================================ mid-drain: relu(upconv1) of low-res pixel r, phases 2h and 2h+1 (group h = warps 4-6 /
     // 8-10), back into TMEM as the bf16 A operand of the second GEMM - same lane, no shared memory.
     const int h = warp >> 3;
@@ -235,14 +242,12 @@ uptail2_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
     const uint32_t tl = tmem + ((uint32_t)(q * 32) << 16);
     uint32_t k = 0;
     const bool dbg = p.dbg != nullptr && warp == 4 && lane == 0;
-    long long t7 = 0, t8 = 0, tq = 0;
+    long long t7 = 0, t8 = 0, tq = 0, tld = 0, tst = 0;
     const long long td0 = dbg ? clock64() : 0;
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
       const int txi = it % p.tiles_x, t = it / p.tiles_x;
       const int tyi = t % p.tiles_y;
       if (dbg) tq = clock64();
-      ptx::mbar_wait(a2_empty + 8 * h, (k & 1) ^ 1);   // GEMM #2 of the previous item has consumed these planes
-      if (dbg) { const long long n = clock64(); t7 += n - tq; tq = n; }
       ptx::mbar_wait(acc1_full + 8 * h, k & 1);
       if (dbg) t8 += clock64() - tq;
       ptx::tc_fence_after();
@@ -257,23 +262,34 @@ uptail2_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint32_t v[32];
+          const long long tl0 = dbg ? clock64() : 0;
           ptx::tmem_ld_32x32(tl + h * 128 + pp * 64 + half * 32, v);
           ptx::tmem_ld_wait();
+          if (dbg) tld += clock64() - tl0;
 #pragma unroll
           for (int j = 0; j < 16; ++j)
             o[half * 16 + j] = keep ? ptx::pack_relu_bf16x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1])) : 0u;
         }
+        if (pp == 0) {
+          if (dbg) tq = clock64();
+          ptx::mbar_wait(a2_empty + 8 * h, (k & 1) ^ 1);   // GEMM #2 of the previous item has consumed these planes
+          if (dbg) t7 += clock64() - tq;
+          ptx::tc_fence_after();
+        } else {                                           // the accumulator half has been read completely: hand it back
+          ptx::tc_fence_before();                          // before the last store, GEMM #1 of the next item can start
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(acc1_empty + 8 * h);
+        }
+        const long long ts0 = dbg ? clock64() : 0;
         ptx::tmem_st_32x32(tl + TM_A2 + (2 * h + pp) * 32, o);
+        if (pp == 1) ptx::tmem_st_wait();
+        if (dbg) tst += clock64() - ts0;
       }
-      ptx::tmem_st_wait();
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) {
-        ptx::mbar_arrive(acc1_empty + 8 * h);        // this half of the first accumulator is free
-        ptx::mbar_arrive(a2_full + 8 * h);           // ... and its two A2 planes are in tensor memory
-      }
+      if (lane == 0) ptx::mbar_arrive(a2_full + 8 * h);    // both A2 planes of this half are in tensor memory
     }
-    if (dbg) { long long* d = p.dbg + blockIdx.x * 16; d[7] = t7; d[8] = t8; d[9] = clock64() - td0; }
+    if (dbg) { long long* d = p.dbg + blockIdx.x * 16; d[7] = t7; d[8] = t8; d[9] = clock64() - td0; d[14] = tld; d[15] = tst; }
   } else if (warp >= UT_EPI_WARP0) {
     // ================================ epilogue: Y planes -> Ys, 9-tap gather over the phase planes, clamp, uint8 rows
     const int grp = (warp - UT_EPI_WARP0) >> 2;
@@ -292,7 +308,8 @@ uptail2_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
       const int tyi = t % p.tiles_y, n = t / p.tiles_y;
       const int x0 = txi * G27_TW, y0 = tyi * G27_ROWS;
       const long long tq = dbg ? clock64() : 0;
-      ptx::mbar_wait(y_full + 8 * grp, (k / UT_EPI_GROUPS) & 1);
+      ptx::mbar_wait(y_full + 8 * (2 * grp), (k / UT_EPI_GROUPS) & 1);
+      ptx::mbar_wait(y_full + 8 * (2 * grp + 1), (k / UT_EPI_GROUPS) & 1);
       if (dbg) { t10 += clock64() - tq; ++n_items; }
       ptx::tc_fence_after();
       if (q < 3) {                                   // lanes 96-127 hold no patch pixel
@@ -309,7 +326,7 @@ uptail2_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
         }
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(y_empty);
+        if (lane == 0) { ptx::mbar_arrive(y_empty); ptx::mbar_arrive(y_empty + 8); }
       }
       named_bar_sync(1 + grp, 128);
       const int nvx = min(G27_TW, W2 - x0);

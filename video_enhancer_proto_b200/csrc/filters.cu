@@ -58,6 +58,22 @@ __global__ void filter3x3_kernel(const uint8_t* __restrict__ in, uint8_t* __rest
 // row-major tap order of the generic kernel, one 16-byte store.
 constexpr int FILT_ROWS = 16;
 
+// uint8 <-> fp32 without the conversion pipe (I2F / F2I issue at a quarter of the FMA rate on B200: 16 per clock per SM,
+// tools/ubench/pipes.cu - with 22 + 16 conversions per 16 output bytes they, not the 144 FMAs, bounded this kernel at 0.37
+// of HBM).  In: the float 2^23 + b is the bit pattern 0x4B000000 | b (one byte permute), minus 2^23 (exact).  Out:
+// clamp to [0, 255], add 1.5 * 2^23 - the sum is rounded to nearest even exactly like cvRound and its low mantissa byte
+// IS the integer - and three byte permutes pack four results.  cv::saturate_cast<uchar>(cvRound(v)) clamps after
+// rounding; clamping first gives the same byte for every finite v (-0.5 -> 0, 255.5 -> 256 -> 255 either way).
+__device__ __forceinline__ float byte_to_f32(uint32_t w, int i) {
+  return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7540u | i)) - 8388608.0f;
+}
+__device__ __forceinline__ uint32_t round_sat_bits(float v) {
+  return __float_as_uint(fminf(fmaxf(v, 0.f), 255.f) + 12582912.0f);
+}
+__device__ __forceinline__ uint32_t pack4_low_bytes(uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  return __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
+}
+
 __device__ __forceinline__ void filt_load_row(const uint8_t* __restrict__ rowp, int col, int row_bytes, float (&f)[22]) {
   const uint4 v = *reinterpret_cast<const uint4*>(rowp + col);
   // halo: bytes col-3..col-1 and col+16..col+18; at the row ends REFLECT_101 in x: pixel -1 -> pixel 1, pixel W -> W-2
@@ -68,11 +84,11 @@ __device__ __forceinline__ void filt_load_row(const uint8_t* __restrict__ rowp, 
   else hi = (v.z >> 16) | (v.w << 16);                                                   // bytes 10, 11, 12 (pixel W-2)
   const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-  for (int i = 0; i < 3; ++i) f[i] = (float)((lo >> (8 * i)) & 0xffu);
+  for (int i = 0; i < 3; ++i) f[i] = byte_to_f32(lo, i);
 #pragma unroll
-  for (int i = 0; i < 16; ++i) f[3 + i] = (float)((w[i >> 2] >> (8 * (i & 3))) & 0xffu);
+  for (int i = 0; i < 16; ++i) f[3 + i] = byte_to_f32(w[i >> 2], i & 3);
 #pragma unroll
-  for (int i = 0; i < 3; ++i) f[19 + i] = (float)((hi >> (8 * i)) & 0xffu);
+  for (int i = 0; i < 3; ++i) f[19 + i] = byte_to_f32(hi, i);
 }
 
 __global__ void __launch_bounds__(128)
@@ -95,16 +111,18 @@ filter3x3_rows_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out,
     float (&rb)[22] = r[(t + 1) % 3];
     float (&rc)[22] = r[(t + 2) % 3];
     filt_load_row(base + (size_t)reflect101(y + 1, H) * row_bytes, col, row_bytes, rc);
-    uint32_t o[4] = {0u, 0u, 0u, 0u};
+    uint32_t b[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
       float a = 0.f;
       a = fmaf(kk[0], ra[i], a); a = fmaf(kk[1], ra[i + 3], a); a = fmaf(kk[2], ra[i + 6], a);
       a = fmaf(kk[3], rb[i], a); a = fmaf(kk[4], rb[i + 3], a); a = fmaf(kk[5], rb[i + 6], a);
       a = fmaf(kk[6], rc[i], a); a = fmaf(kk[7], rc[i + 3], a); a = fmaf(kk[8], rc[i + 6], a);
-      o[i >> 2] |= (uint32_t)sat_u8_rn(a) << (8 * (i & 3));
+      b[i] = round_sat_bits(a);
     }
-    *reinterpret_cast<uint4*>(out + fo + (size_t)y * row_bytes + col) = make_uint4(o[0], o[1], o[2], o[3]);
+    *reinterpret_cast<uint4*>(out + fo + (size_t)y * row_bytes + col) =
+        make_uint4(pack4_low_bytes(b[0], b[1], b[2], b[3]), pack4_low_bytes(b[4], b[5], b[6], b[7]),
+                   pack4_low_bytes(b[8], b[9], b[10], b[11]), pack4_low_bytes(b[12], b[13], b[14], b[15]));
   }
 }
 
@@ -145,13 +163,13 @@ bilateral5_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int
     const uint32_t p = tile[threadIdx.y + 2 + BL_DI[k]][threadIdx.x + 2 + BL_DJ[k]];
     const float w = tab.space[k] * cw[__vsadu4(p, c0)];
     ws += w;
-    sb = fmaf((float)(p & 0xffu), w, sb);
-    sg = fmaf((float)((p >> 8) & 0xffu), w, sg);
-    sr = fmaf((float)(p >> 16), w, sr);
+    sb = fmaf(byte_to_f32(p, 0), w, sb);             // byte -> float by permute + subtract: 39 I2F per pixel were the bound
+    sg = fmaf(byte_to_f32(p, 1), w, sg);
+    sr = fmaf(byte_to_f32(p, 2), w, sr);
   }
   const float inv = 1.f / ws;
   uint8_t* o = out + fo + ((size_t)y * W + x) * 3;
-  o[0] = sat_u8_rn(sb * inv); o[1] = sat_u8_rn(sg * inv); o[2] = sat_u8_rn(sr * inv);
+  o[0] = (uint8_t)round_sat_bits(sb * inv); o[1] = (uint8_t)round_sat_bits(sg * inv); o[2] = (uint8_t)round_sat_bits(sr * inv);
 }
 
 // ------------------------------------------------------------------------------------------------ Lanczos4 2x
@@ -197,14 +215,16 @@ lanczos4_2x_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, in
     const int ch = i % 3, g = (i / 3) % (LZ_TW / 4), r = i / (3 * (LZ_TW / 4));
     float v[12];
 #pragma unroll
-    for (int c = 0; c < 12; ++c) v[c] = (float)s_in[r][(4 * g + c) * 3 + ch];
+    for (int c = 0; c < 12; ++c)                              // byte -> float off the conversion pipe: 2^23 + b, minus 2^23
+      v[c] = __uint_as_float(0x4B000000u | (uint32_t)s_in[r][(4 * g + c) * 3 + ch]) - 8388608.0f;
 #pragma unroll
     for (int d = 0; d < 8; ++d) {
       const int j = d >> 1, e = d & 1;
       float acc = 0.f;                                         // |partial sums| <= 255 * 3126 < 2^24: exact in fp32
 #pragma unroll
       for (int k = 0; k < 8; ++k) acc = fmaf(c_lzf[e][k], v[j + e + k], acc);
-      s_h[r][(8 * g + d) * 3 + ch] = __float2int_rn(acc);
+      // acc is an integer of magnitude < 2^22: acc + 1.5 * 2^23 holds it in the low mantissa bits (no F2I)
+      s_h[r][(8 * g + d) * 3 + ch] = (int)(__float_as_uint(acc + 12582912.0f) - 0x4B400000u);
     }
   }
   __syncthreads();

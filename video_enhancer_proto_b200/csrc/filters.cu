@@ -126,6 +126,108 @@ filter3x3_rows_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out,
   }
 }
 
+// Packed variant (row bytes % 32 == 0): one thread owns TWO 16-byte columns, `half` bytes apart, and keeps them in the two
+// lanes of fp32x2 registers, so the nine FMAs of an output byte pair are nine FFMA2 instructions.  The kernel above is bound
+// by warp-instruction issue (ncu: 68 % issue-active at 18.4 instructions per output byte, FMA pipe 46 %), not by the FMA
+// pipe, and FFMA2 has the same FLOP rate with half the instructions: ~10 instructions per byte.  Same fp32 operations in the
+// same order per byte, hence the same bytes (tests/test_filters_gpu.py compares both against cv2).  Measured: 0.41 -> 0.43
+// of HBM only - halving the FMA instructions did not move it, so issue is not the whole story either; left here.
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t f2_pack(float lo, float hi) {
+  f2_t r;
+  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(f2_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f2_t f2_fma(f2_t a, f2_t k, f2_t c) {
+  f2_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(k), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f2_t f2_add(f2_t a, f2_t b) {
+  f2_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
+struct FiltRaw { uint4 v; uint32_t lo, hi; };
+__device__ __forceinline__ FiltRaw filt_load_raw(const uint8_t* __restrict__ rowp, int col, int row_bytes) {
+  FiltRaw r;
+  r.v = *reinterpret_cast<const uint4*>(rowp + col);
+  if (col > 0) r.lo = *reinterpret_cast<const uint32_t*>(rowp + col - 4) >> 8;           // bytes col-3 .. col-1
+  else r.lo = (r.v.x >> 24) | (r.v.y << 8);                                               // REFLECT_101: pixel 1
+  if (col + 16 < row_bytes) r.hi = *reinterpret_cast<const uint32_t*>(rowp + col + 16);   // bytes col+16 .. col+18
+  else r.hi = (r.v.z >> 16) | (r.v.w << 16);                                              // pixel W-2
+  return r;
+}
+__device__ __forceinline__ uint32_t filt_byte(const FiltRaw& r, int i) {                 // window byte i of 22 as 0x4B0000bb
+  const uint32_t w = i < 3 ? r.lo : i < 7 ? r.v.x : i < 11 ? r.v.y : i < 15 ? r.v.z : i < 19 ? r.v.w : r.hi;
+  const int b = i < 3 ? i : i < 19 ? (i - 3) & 3 : i - 19;
+  return __byte_perm(w, 0x4B000000u, 0x7540u | b);
+}
+__device__ __forceinline__ void filt_convert2(const FiltRaw& a, const FiltRaw& b, f2_t (&f)[22]) {
+  const f2_t m = f2_pack(-8388608.0f, -8388608.0f);
+#pragma unroll
+  for (int i = 0; i < 22; ++i)
+    f[i] = f2_add(f2_pack(__uint_as_float(filt_byte(a, i)), __uint_as_float(filt_byte(b, i))), m);
+}
+__device__ __forceinline__ void filt_load_row2(const uint8_t* __restrict__ rowp, int colA, int colB, int row_bytes, f2_t (&f)[22]) {
+  const FiltRaw a = filt_load_raw(rowp, colA, row_bytes), b = filt_load_raw(rowp, colB, row_bytes);
+  const f2_t m = f2_pack(-8388608.0f, -8388608.0f);
+#pragma unroll
+  for (int i = 0; i < 22; ++i)
+    f[i] = f2_add(f2_pack(__uint_as_float(filt_byte(a, i)), __uint_as_float(filt_byte(b, i))), m);
+}
+
+__global__ void __launch_bounds__(128)
+filter3x3_rows2_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int H, int row_bytes,
+                       float k0, float k1, float k2, float k3, float k4, float k5, float k6, float k7, float k8) {
+  const int half = row_bytes / 2;
+  const int colA = (blockIdx.x * blockDim.x + threadIdx.x) * 16;
+  if (colA >= half) return;
+  const int colB = colA + half;
+  const int y0 = blockIdx.y * FILT_ROWS, y1 = min(y0 + FILT_ROWS, H);
+  const size_t fo = (size_t)blockIdx.z * H * row_bytes;
+  const uint8_t* base = in + fo;
+  const f2_t kk[9] = {f2_pack(k0, k0), f2_pack(k1, k1), f2_pack(k2, k2), f2_pack(k3, k3), f2_pack(k4, k4),
+                      f2_pack(k5, k5), f2_pack(k6, k6), f2_pack(k7, k7), f2_pack(k8, k8)};
+  const f2_t zero = f2_pack(0.f, 0.f);
+  f2_t r[3][22];
+  filt_load_row2(base + (size_t)reflect101(y0 - 1, H) * row_bytes, colA, colB, row_bytes, r[0]);
+  filt_load_row2(base + (size_t)y0 * row_bytes, colA, colB, row_bytes, r[1]);
+  // (Requesting the raw words of row y + 2 one iteration early was tried: 166 registers, 3 blocks per SM, 0.43 -> 0.30 of HBM.)
+#pragma unroll
+  for (int t = 0; t < FILT_ROWS; ++t) {
+    const int y = y0 + t;
+    if (y >= y1) break;
+    f2_t (&ra)[22] = r[t % 3];
+    f2_t (&rb)[22] = r[(t + 1) % 3];
+    f2_t (&rc)[22] = r[(t + 2) % 3];
+    filt_load_row2(base + (size_t)reflect101(y + 1, H) * row_bytes, colA, colB, row_bytes, rc);
+    uint32_t bA[16], bB[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      f2_t a = zero;
+      a = f2_fma(kk[0], ra[i], a); a = f2_fma(kk[1], ra[i + 3], a); a = f2_fma(kk[2], ra[i + 6], a);
+      a = f2_fma(kk[3], rb[i], a); a = f2_fma(kk[4], rb[i + 3], a); a = f2_fma(kk[5], rb[i + 6], a);
+      a = f2_fma(kk[6], rc[i], a); a = f2_fma(kk[7], rc[i + 3], a); a = f2_fma(kk[8], rc[i + 6], a);
+      float lo, hi;
+      f2_unpack(a, lo, hi);
+      bA[i] = round_sat_bits(lo);
+      bB[i] = round_sat_bits(hi);
+    }
+    uint8_t* orow = out + fo + (size_t)y * row_bytes;
+    *reinterpret_cast<uint4*>(orow + colA) =
+        make_uint4(pack4_low_bytes(bA[0], bA[1], bA[2], bA[3]), pack4_low_bytes(bA[4], bA[5], bA[6], bA[7]),
+                   pack4_low_bytes(bA[8], bA[9], bA[10], bA[11]), pack4_low_bytes(bA[12], bA[13], bA[14], bA[15]));
+    *reinterpret_cast<uint4*>(orow + colB) =
+        make_uint4(pack4_low_bytes(bB[0], bB[1], bB[2], bB[3]), pack4_low_bytes(bB[4], bB[5], bB[6], bB[7]),
+                   pack4_low_bytes(bB[8], bB[9], bB[10], bB[11]), pack4_low_bytes(bB[12], bB[13], bB[14], bB[15]));
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ bilateral 5x5
 struct BilateralTab {
   float space[13];
@@ -276,6 +378,15 @@ int launch_filter3x3(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h
     return fail(ctx, VEX_ERR_INVALID, "vex_filter3x3_u8: bad argument");
   const int row_bytes = w * 3;
   const bool aligned = ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  if (row_bytes % 32 == 0 && aligned && w >= 16 && !ctx->opt_force_generic_bicubic && !ctx->opt_force_generic_resize) {
+    dim3 grid((row_bytes / 32 + 127) / 128, (h + FILT_ROWS - 1) / FILT_ROWS, n);   // two 16-byte columns per thread, fp32x2
+    if (grid.y > 65535 || grid.z > 65535) return fail(ctx, VEX_ERR_INVALID, "vex_filter3x3_u8: frame or batch too large");
+    filter3x3_rows2_kernel<<<grid, 128, 0, s>>>(in, out, h, row_bytes, k9[0], k9[1], k9[2], k9[3], k9[4], k9[5], k9[6], k9[7],
+                                                k9[8]);
+    ctx->launches++;
+    VEX_CUDA(ctx, cudaGetLastError());
+    return VEX_OK;
+  }
   if (row_bytes % 16 == 0 && aligned && w >= 8 && !ctx->opt_force_generic_bicubic) {
     dim3 grid((row_bytes / 16 + 127) / 128, (h + FILT_ROWS - 1) / FILT_ROWS, n);
     if (grid.y > 65535 || grid.z > 65535) return fail(ctx, VEX_ERR_INVALID, "vex_filter3x3_u8: frame or batch too large");

@@ -12,6 +12,11 @@ What it restates (all citations relative to ``/root/reference``):
 * single-frame pre/post-processing                app.py:334-346
 * bicubic CPU fallback                            app.py:364-376
 * OpenCV bicubic twin                             models/enhancement/frame/basic_upscaler_fallback.py:142
+* BasicUpscalerFallback per-frame body            models/enhancement/frame/basic_upscaler_fallback.py:113-128
+* Real-ESRGAN network and handler frame path      models/enhancement/vsr/realesrgan_handler.py:23-100, 286-372
+                                                  (oracle/realesrgan_ref.py, pinned by oracle/make_golden_rrdb.py)
+* the agent's dispatch to the handlers            agents/enhancer/video_enhancer_sota.py:155-210, 275-371
+                                                  (oracle/agent_ref.py, pinned by tests/test_agent_registration.py)
 
 Parity pinning status: the reference's own tests hold NO golden vectors, known-answer
 tests or tolerances for this path, so the restatement is pinned

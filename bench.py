@@ -158,10 +158,46 @@ def cpu_reference(workload: str, budget_s: float):
             "sample": f"{n} frame(s) 1080p->2160p, {workload}, torch {torch.__version__} CPU fp32, {torch.get_num_threads()} threads, {dt:.1f}s"}
 
 
+def run_reference_rrdb(args):
+    """--impl reference --workload rrdb: the oracle's Real-ESRGAN (the reference's network on torch CPU, all host threads) on
+    padded tiles of a 1080p frame, one tile per step, scaled to frames by pixel count."""
+    import torch
+    from oracle import realesrgan_ref as R
+    from video_enhancer_proto_b200 import synth
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    model = R.make_network(0, 4, 23)
+    frame = synth.random_frame(H, W, np.random.default_rng(1234))
+    plan = R.tile_plan(H, W, 512, 10)
+    px = sum((py1 - py0) * (px1 - px0) for (py0, py1, px0, px1, *_r) in plan)
+    vals, tpx_total, t_total = [], 0, 0.0
+    for k in range(max(1, min(args.steps, 3))):
+        py0, py1, px0, px1 = plan[(5 + k) % len(plan)][:4]
+        tile = np.ascontiguousarray(frame[py0:py1, px0:px1])
+        t0 = time.perf_counter()
+        R.process_single(model, tile)
+        dt = time.perf_counter() - t0
+        tpx = (py1 - py0) * (px1 - px0)
+        vals.append(1.0 / (dt * px / tpx)); tpx_total += tpx; t_total += dt
+    v = float(np.mean(vals))
+    base = {"value": v, "unit": "frames/s", "cores": cores, "kind": "port",
+            "sample": f"{len(vals)} padded tile(s) of the 12 of a 1080p frame ({tpx_total / px:.2f} frames' worth of pixels) in {t_total:.1f} s, "
+                      f"torch {torch.__version__} CPU fp32, {torch.get_num_threads()} threads, scaled by pixel count"}
+    print(json.dumps({"impl": "reference", "metric": "Real-ESRGAN x4 frames/sec at 1080p->4320p (reference tile loop)", "value": v,
+                      "unit": "frames/s", "n_gpus": args.gpus, "steps": len(vals), "warmup": 0, "ms_per_step": 1000.0 / v,
+                      "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                      "config": {"workload": "Real-ESRGAN RRDBNet 23 blocks x4, 1080p->4320p, tile 512 pad 10 (SURVEY 8(f)4)",
+                                 "note": "reference CPU path (oracle port), one padded tile per step"},
+                      "cpu_baseline": base,
+                      "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
+
+
 def run_reference(args, workload):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    if workload == "rrdb":
+        return run_reference_rrdb(args)
     if workload not in ("cnn", "bicubic"):                  # stream / wide: the reference arm is the CNN at configs[2]
         workload = "cnn"
     per_step = 4.0 if workload == "bicubic" else 30.0

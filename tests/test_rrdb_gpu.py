@@ -15,6 +15,7 @@ import pytest
 import torch
 
 from oracle import realesrgan_ref as R
+import rrdb_emulation as E
 from video_enhancer_proto_b200 import B200RealESRGAN, synth
 
 pytestmark = pytest.mark.gpu
@@ -185,5 +186,50 @@ def test_restore_video_file_to_file(tmp_path):
         cap.release()
         with pytest.raises(ValueError, match="Could not open video"):
             hd.restore_video(str(tmp_path / "missing.mp4"), str(tmp_path / "o.mp4"))
+    finally:
+        hd.close()
+
+
+def test_full_size_1080p_frame_through_the_tile_loop():
+    """The reference configuration at the bench's size: a 1080p frame, 23 blocks, x4, tile 512 / pad 10 (12 tiles -> 4320p).
+    The CPU oracle needs minutes for a whole frame, so one INTERIOR tile (532 x 532 with padding) is checked against the
+    oracle's `_process_single` on the same padded crop (what `_tile_process` computes for it, :351), and every tile core of
+    the frame against the same tile run alone on the GPU (bit for bit)."""
+    model = R.make_network(2, 4, 23, 6.0)
+    hd = handler(model)
+    try:
+        rng = np.random.default_rng(5)
+        img = synth.edges_frame(1080, 1920, rng)
+        out = hd._tile_process(img)
+        assert out.shape == (4320, 7680, 3) and out.dtype == np.uint8
+        plan = R.tile_plan(1080, 1920, 512, 10)
+        assert len(plan) == 12
+        for (py0, py1, px0, px1, y0, y1, x0, x1) in (plan[0], plan[5], plan[11]):      # corner, interior, ragged last tile
+            alone = hd._process_single(np.ascontiguousarray(img[py0:py1, px0:px1]))
+            core = alone[(y0 - py0) * 4:(y0 - py0) * 4 + (y1 - y0) * 4, (x0 - px0) * 4:(x0 - px0) * 4 + (x1 - x0) * 4]
+            assert np.array_equal(out[y0 * 4:y1 * 4, x0 * 4:x1 * 4], core), (y0, x0)
+        py0, py1, px0, px1, y0, y1, x0, x1 = plan[5]
+        ref = R.process_single(model, np.ascontiguousarray(img[py0:py1, px0:px1]))
+        want = ref[(y0 - py0) * 4:(y0 - py0) * 4 + (y1 - y0) * 4, (x0 - px0) * 4:(x0 - px0) * 4 + (x1 - x0) * 4]
+        got = out[y0 * 4:y1 * 4, x0 * 4:x1 * 4]
+        d = np.abs(got.astype(int) - want.astype(int))
+        assert want.max() - want.min() > 100                                 # full-range output
+        # 23 blocks x gain 6: what the fp16 number format itself costs against fp32 is measured here, on the same tile, by
+        # the CPU emulation of the GPU's rounding points (tests/rrdb_emulation.py); the GPU may not be further from the
+        # oracle than that, up to the summation-order freedom (1 LSB).  At gain 1 (test_23_block_network_meets_the_bar)
+        # the same error is 0.5 LSB and the <= 2 LSB bar holds outright.
+        emu = E.process_single(model, np.ascontiguousarray(img[py0:py1, px0:px1]))
+        emu = emu[(y0 - py0) * 4:(y0 - py0) * 4 + (y1 - y0) * 4, (x0 - px0) * 4:(x0 - px0) * 4 + (x1 - x0) * 4]
+        de = np.abs(emu.astype(int) - want.astype(int))
+        dg = np.abs(got.astype(int) - emu.astype(int))
+
+        def psnr(x):
+            return 10 * np.log10(255.0 ** 2 / max(float((x.astype(np.float64) ** 2).mean()), 1e-12))
+
+        print(f"[rrdb_1080p] gpu-fp32 max {int(d.max())} mean {d.mean():.4f} psnr {psnr(d):.1f} | emu-fp32 max {int(de.max())} "
+              f"mean {de.mean():.4f} psnr {psnr(de):.1f} | gpu-emu max {int(dg.max())} mean {dg.mean():.4f} psnr {psnr(dg):.1f}")
+        assert d.max() <= de.max() + 1, (int(d.max()), int(de.max()))
+        assert d.mean() <= 1.1 * de.mean() + 0.01, (float(d.mean()), float(de.mean()))
+        assert psnr(d) >= psnr(de) - 0.5 and psnr(d) >= 45.0, (psnr(d), psnr(de))
     finally:
         hd.close()

@@ -8,6 +8,7 @@ import numpy as np
 import pytest
 
 from oracle import realesrgan_ref as R
+import rrdb_emulation as E
 from video_enhancer_proto_b200 import realesrgan as RG
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -71,3 +72,15 @@ def test_no_cpu_fallback_without_device():
     h = RG.B200RealESRGAN(seed=0, num_block=1)
     with pytest.raises(_lib.VexError):
         h._enhance_frame(np.zeros((8, 8, 3), np.uint8))
+
+
+def test_fp16_rounding_points_keep_the_23_block_network_inside_the_bar():
+    """Why the GPU trunk is fp16 and what bar it can meet: the emulation of its rounding points (tests/rrdb_emulation.py)
+    against the fp32 oracle on the reference configuration (23 blocks, scale 4).  Gain 1: within the 2 LSB bar with room;
+    gain 6 (full-range output): the same relative error, a few LSB - the bound the full-size GPU test is judged against."""
+    img = np.random.default_rng(5).integers(0, 256, (48, 56, 3), dtype=np.uint8)
+    for gain, bound in ((1.0, 1), (6.0, 6)):
+        model = R.make_network(2, 4, 23, gain)
+        d = np.abs(E.process_single(model, img).astype(int) - R.process_single(model, img).astype(int))
+        assert d.max() <= bound, (gain, int(d.max()))
+        assert d.mean() < 0.1 * gain, (gain, float(d.mean()))

@@ -126,6 +126,24 @@ int vex_cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch,
 int vex_cnn2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc,
                  int n, int h, int w, int in_bgr, int out_bgr, void* stream);
 
+/* vex_cnn2x_u8 for callers that may not allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same kernels and the same output bytes as vex_cnn2x_u8; the activation workspace is a static device
+ * array inside the library instead of a cudaMalloc'd one, and the call makes no cudaMalloc / cudaFree / event creation.
+ *   limit:    one frame's workspace (vex_workspace_bytes(ctx, 1, h, w)) must fit VEX_NOALLOC_SCRATCH_BYTES = 176 MiB,
+ *             i.e. up to 480 x 360 (BASELINE configs[0]) with the reference widths (1040 B per input pixel); larger
+ *             frames return VEX_ERR_NOMEM with the two byte counts in vex_last_error.  n frames run in sub-batches
+ *             of as many as fit.  Every GPU whose context loads the library holds the 176 MiB until process exit.
+ *   set-up:   vex_cnn_load_weights (which allocates) must have run on this ctx; it also resolves the scratch address.
+ *             Options "profile" and "conv_dbg" allocate and are refused here (VEX_ERR_UNSUPPORTED).
+ *   sharing:  ONE array per device, shared by every call and every ctx of the process, holding the last call's
+ *             contents (nothing needs clearing: each layer writes its output before it is read).  Calls are ordered
+ *             only by `stream`; two calls that overlap on the GPU race on the scratch.  It is independent of the
+ *             workspace of vex_cnn2x_u8, so a no-alloc call and an ordinary call may overlap. */
+#define VEX_NOALLOC_SCRATCH_BYTES (176u << 20)
+int vex_cnn2x_u8_noalloc(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc,
+                         int n, int h, int w, int in_bgr, int out_bgr, void* stream);
+
 /* fp32 input form of vex_cnn2x_u8 for the tensor branch of the single-frame entry (app.py:337-338: a caller may hand
  * `_enhance_frame_with_gpu` an fp32 NCHW tensor already in [0,1], which the reference feeds to conv1 unquantised).
  * in_nchw: n*[3][h][w] fp32 device, any real values; conv1 takes each value as a hi + lo bf16 pair (relative input error

@@ -36,6 +36,7 @@ SIGNATURES = {
     "vex_filter3x3_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float), C.c_void_p]),
     "vex_cnn_load_weights": (C.c_int, [C.c_void_p, C.POINTER(VexCnnDesc), C.POINTER(C.c_void_p), C.c_int]),
     "vex_cnn2x_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "vex_cnn2x_u8_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "vex_cnn2x_f32_debug": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "vex_cnn_profile_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "vex_workspace_bytes": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)]),

@@ -55,7 +55,16 @@ struct CnnPlan {
   double prof_sum[7] = {0, 0, 0, 0, 0, 0, 0};
   float prof_min[7] = {0, 0, 0, 0, 0, 0, 0}, prof_max[7] = {0, 0, 0, 0, 0, 0, 0};
   int prof_n = 0;
+  // vex_cnn2x_u8_noalloc: this device's address of g_noalloc_ws (resolved once, at weight load), or null + the reason
+  uint8_t* noalloc_ws = nullptr;
+  cudaError_t noalloc_err = cudaSuccess;
 };
+
+// Scratch of the no-allocation entry point (vex_cnn2x_u8_noalloc, include/vex.h): the activation workspace of the CNN for
+// callers that may not allocate (CUDA graph capture, serving loops).  File-scope device storage: every GPU whose context
+// loads this library holds VEX_NOALLOC_SCRATCH_BYTES of it until the process exits.  In HOST code this name is only a
+// stand-in for the symbol; the device address comes from cudaGetSymbolAddress (cnn_noalloc_setup), once per device.
+static __device__ __align__(256) unsigned char g_noalloc_ws[VEX_NOALLOC_SCRATCH_BYTES];
 
 namespace {
 
@@ -910,6 +919,59 @@ int cnn_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f32
     int rc = forward_chunk(ctx, in + (size_t)f0 * h * w * 3 * (in_bgr == IN_F32_NCHW ? 4 : 1), out_u8 ? out_u8 + (size_t)f0 * h * w * 12 : nullptr,
                            out_f32 ? out_f32 + (size_t)f0 * out_ch[tap] * out_px : nullptr, tap, nf, h, w, in_bgr,
                            out_bgr, s);
+    if (rc) return rc;
+  }
+  return VEX_OK;
+}
+
+// ------------------------------------------------------------------------------------------- no-allocation entry
+
+// Set-up half (called from vex_cnn_load_weights with the ctx's device current): resolve this device's copy of the
+// static scratch.  A failure is kept and reported by the entry point; weight loading itself is not affected.
+void cnn_noalloc_setup(vex_ctx* ctx) {
+  CnnPlan* P = ctx->cnn;
+  if (!P || P->noalloc_ws) return;
+  void* ptr = nullptr;
+  P->noalloc_err = cudaGetSymbolAddress(&ptr, g_noalloc_ws);
+  if (P->noalloc_err != cudaSuccess) { cudaGetLastError(); ptr = nullptr; }
+  P->noalloc_ws = static_cast<uint8_t*>(ptr);
+}
+
+// The forward of cnn_forward with the static scratch as the activation workspace: same kernels, same launch order, so the
+// output is the existing entry point's bit for bit.  No cudaMalloc / cudaFree / event creation on this path: the options
+// that would allocate (profile events, conv_dbg counters) are refused.  Every layer writes its output before the next
+// one reads it and image borders come from the tensor maps' out-of-bounds fill, so nothing in the scratch has to start
+// at zero and the previous call's contents are harmless.  All calls on a device share the one array: calls that overlap
+// on the GPU (different streams without an ordering between them, or two contexts of one process) race.
+int cnn_forward_noalloc(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, int n, int h, int w, int in_bgr, int out_bgr,
+                        cudaStream_t s) {
+  CnnPlan* P = ctx->cnn;
+  if (!P || !P->w1g) return fail(ctx, VEX_ERR_NO_WEIGHTS, "vex_cnn_load_weights has not been called");
+  if (!P->noalloc_ws)
+    return fail(ctx, VEX_ERR_CUDA, std::string("vex_cnn2x_u8_noalloc: cudaGetSymbolAddress of the static scratch failed: ") +
+                                       cudaGetErrorString(P->noalloc_err));
+  if (ctx->opt_profile || ctx->opt_conv_dbg)
+    return fail(ctx, VEX_ERR_UNSUPPORTED, "vex_cnn2x_u8_noalloc: options profile / conv_dbg allocate; switch them off");
+  if ((long long)h * w > (1LL << 28)) return fail(ctx, VEX_ERR_INVALID, "frame too large");
+  const size_t per_frame = ws_layout(P->arch, (size_t)h * w).total;
+  if (per_frame > (size_t)VEX_NOALLOC_SCRATCH_BYTES)
+    return fail(ctx, VEX_ERR_NOMEM, "vex_cnn2x_u8_noalloc: a " + std::to_string(h) + " x " + std::to_string(w) + " frame needs " +
+                                        std::to_string(per_frame) + " bytes of scratch, the built-in scratch holds " +
+                                        std::to_string((size_t)VEX_NOALLOC_SCRATCH_BYTES) +
+                                        " (VEX_NOALLOC_SCRATCH_BYTES); use vex_cnn2x_u8");
+  // frames that fit the scratch together go as one sub-batch; forward_chunk finds ws_bytes large enough and allocates nothing
+  int sub = (int)std::min<size_t>((size_t)n, (size_t)VEX_NOALLOC_SCRATCH_BYTES / per_frame);
+  while (sub > 1 && ws_layout(P->arch, (size_t)sub * h * w).total > (size_t)VEX_NOALLOC_SCRATCH_BYTES) --sub;
+  struct Swap {                               // the ctx's own workspace comes back on every exit path
+    CnnPlan* p; uint8_t* ws; size_t bytes;
+    ~Swap() { p->ws = ws; p->ws_bytes = bytes; }
+  } swap{P, P->ws, P->ws_bytes};
+  P->ws = P->noalloc_ws;
+  P->ws_bytes = (size_t)VEX_NOALLOC_SCRATCH_BYTES;
+  for (int f0 = 0; f0 < n; f0 += sub) {
+    const int nf = std::min(sub, n - f0);
+    const int rc = forward_chunk(ctx, in + (size_t)f0 * h * w * 3, out_u8 + (size_t)f0 * h * w * 12, nullptr, 0, nf, h, w,
+                                 in_bgr, out_bgr, s);
     if (rc) return rc;
   }
   return VEX_OK;

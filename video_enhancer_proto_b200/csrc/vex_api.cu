@@ -246,7 +246,18 @@ int vex_cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* co
                          int n_tensors) {
   if (!ctx) return VEX_ERR_INVALID;
   VEX_ON_DEVICE(ctx);
-  return vex::cnn_load_weights(ctx, arch, tensors, n_tensors);
+  const int rc = vex::cnn_load_weights(ctx, arch, tensors, n_tensors);
+  if (rc == VEX_OK) vex::cnn_noalloc_setup(ctx);    // resolves the static scratch of vex_cnn2x_u8_noalloc; cannot fail the load
+  return rc;
+}
+
+int vex_cnn2x_u8_noalloc(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w,
+                         int in_bgr, int out_bgr, void* stream) {
+  if (!ctx) return VEX_ERR_INVALID;
+  if (!in_hwc || !out_hwc || n <= 0 || h <= 0 || w <= 0)
+    return vex::fail(ctx, VEX_ERR_INVALID, "vex_cnn2x_u8_noalloc: bad argument");
+  VEX_ON_DEVICE(ctx);
+  return vex::cnn_forward_noalloc(ctx, in_hwc, out_hwc, n, h, w, in_bgr != 0, out_bgr != 0, (cudaStream_t)stream);
 }
 
 int vex_cnn2x_u8(vex_ctx* ctx, const uint8_t* in_hwc, uint8_t* out_hwc, int n, int h, int w,

@@ -123,6 +123,10 @@ int launch_bicubic2x(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h
 
 int launch_bicubic2x_f32in(vex_ctx* ctx, const float* in_nchw, uint8_t* out, int n, int h, int w, cudaStream_t s);
 
+// cnn.cu: the no-allocation entry (static device scratch)
+void cnn_noalloc_setup(vex_ctx* ctx);
+int cnn_forward_noalloc(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, int n, int h, int w, int in_bgr, int out_bgr,
+                        cudaStream_t s);
 // rrdb.cu
 int rrdb_load_weights(vex_ctx* ctx, const vex_rrdb_desc* arch, const float* const* tensors, int n);
 int rrdb_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f32, int tap, int n, int h, int w,

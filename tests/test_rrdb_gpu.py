@@ -129,6 +129,35 @@ def test_tiled_equals_tiles_run_alone_and_rgb_methods():
         hd.close()
 
 
+@pytest.mark.parametrize("scale,h,w,tile,pad,budget_mb", [(2, 150, 200, 64, 10, 0), (4, 150, 200, 32, 6, 0), (4, 97, 131, 48, 10, 64),
+                                                          (2, 128, 192, 64, 0, 0)])
+def test_batched_tile_loop_equals_the_sequential_one(scale, h, w, tile, pad, budget_mb):
+    """The tiles of a frame run as ONE batch of canvases per layer (csrc/rrdb.cu: rrdb_frame; option rrdb_batch, default
+    on), each tile in the corner of a canvas as large as the largest tile with everything outside its own size kept
+    zero.  That must be the reference's sequential loop (:342-370) bit for bit: ragged last row / column, more tiles than
+    one batch holds (35 > 16), a workspace budget that cuts batches short, and pad 0 (all canvases but the last equal)."""
+    model = R.make_network(7, scale, 2, 6.0)
+    hd = handler(model, scale=scale, tile_size=tile, tile_pad=pad)
+    try:
+        img = synth.edges_frame(h, w, np.random.default_rng(h + w))
+        if budget_mb:
+            hd.set_option("ws_budget_mb", budget_mb)
+        n0 = hd.kernel_launches()
+        batched = hd._tile_process(img).copy()
+        n_batched = hd.kernel_launches() - n0
+        assert hd.set_option("rrdb_batch", 0) == 1
+        n0 = hd.kernel_launches()
+        sequential = hd._tile_process(img).copy()
+        n_seq = hd.kernel_launches() - n0
+        assert np.array_equal(batched, sequential)
+        assert n_batched < n_seq                                           # it really was batched
+        assert int(batched.max()) - int(batched.min()) > 100
+        hd.set_option("rrdb_batch", 1)
+        assert np.array_equal(hd._tile_process(img), batched)              # and again, over the stale workspace
+    finally:
+        hd.close()
+
+
 def test_23_block_network_meets_the_bar():
     """The reference's configuration (num_block 23, scale 4) with seeded random weights: 347 conv layers deep."""
     model = R.make_network(2, 4, 23)

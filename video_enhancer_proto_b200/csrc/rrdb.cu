@@ -44,6 +44,9 @@ struct RrdbPlan {
   uint8_t* tile_in = nullptr;
   uint8_t* tile_out = nullptr;
   size_t tile_in_bytes = 0, tile_out_bytes = 0;
+  // canvas batching: valid (h, w) of every image of the forward that is being enqueued (empty = all images fill the canvas)
+  std::vector<int> canvas_dims;
+  int canvas_h0 = 0;                      // the canvas height at the network's input resolution (layers at 2x / 4x scale the table)
 };
 
 namespace {
@@ -142,12 +145,28 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, const __half* in, int in_cs, cons
   p.r1 = e.r1; p.r1_cs = e.r1_cs; p.a1 = e.a1; p.r2 = e.r2; p.r2_cs = e.r2_cs; p.a2 = e.a2;
   p.lrelu = e.lrelu; p.ups2 = e.ups2;
   p.H = H; p.W = W; p.NC = L.nc;
+  p.klast = L.cin % 64 == 32 ? 2 : 4;
   p.tiles_x = (W + rrdb::TILE_W - 1) / rrdb::TILE_W;
   p.tiles_y = (H + rrdb::ROWS - 1) / rrdb::ROWS;
   p.n_img = n;
   p.dbg = nullptr;
   p.force_ring = ctx->opt_rrdb_ring;
-  const long long total = (long long)p.tiles_x * p.tiles_y * n;
+  long long total = (long long)p.tiles_x * p.tiles_y * n;
+  p.n_tab = 0;
+  memset(p.vh, 0, sizeof(p.vh)); memset(p.vw, 0, sizeof(p.vw)); memset(p.item0, 0, sizeof(p.item0));
+  if (!P->canvas_dims.empty()) {
+    if ((int)P->canvas_dims.size() != 2 * n || n > rrdb::MAXB || P->canvas_h0 <= 0 || H % P->canvas_h0 || H > 32767 || W > 32767)
+      return fail(ctx, VEX_ERR_INVALID, "rrdb conv: inconsistent canvas table");
+    const int f = H / P->canvas_h0;
+    p.n_tab = n;
+    total = 0;
+    for (int i = 0; i < n; ++i) {
+      p.vh[i] = (short)(P->canvas_dims[2 * i] * f); p.vw[i] = (short)(P->canvas_dims[2 * i + 1] * f);
+      p.item0[i] = (int)total;
+      total += (long long)rrdb::items_x(p.vw[i], W) * rrdb::items_y(p.vh[i], H);
+    }
+    p.item0[n] = (int)total;
+  }
   if (total > 0x7fffffffLL) return fail(ctx, VEX_ERR_INVALID, "rrdb conv: too many tiles");
   if (ctx->opt_conv_dbg) {
     VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&p.dbg), (size_t)ctx->sm_count * 64));
@@ -205,6 +224,17 @@ __global__ void slice_f16_to_nchw_f32_kernel(const __half* __restrict__ in, floa
   const size_t pix = i / C;
   const size_t n = pix / HW, hw = pix % HW;
   out[(n * C + c) * (size_t)HW + hw] = __half2float(in[pix * cs + c0 + c]);
+}
+
+// canvas batching: conv_first runs over whole canvases, so what it wrote outside an image's valid part (its bias) is
+// cleared before the trunk reads it as padding.  One thread per (pixel, 16-byte chunk of the 64 fp16 channels).
+struct CanvasTab { short vh[rrdb::MAXB], vw[rrdb::MAXB]; };
+__global__ void zero_outside_kernel(__half* __restrict__ buf, size_t nchunk, int H, int W, CanvasTab t) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nchunk) return;
+  const size_t pix = i >> 3;
+  const int x = (int)(pix % W), y = (int)((pix / W) % H), n = (int)(pix / ((size_t)W * H));
+  if (y >= t.vh[n] || x >= t.vw[n]) reinterpret_cast<uint4*>(buf)[i] = make_uint4(0, 0, 0, 0);
 }
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -321,6 +351,7 @@ int rrdb_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f3
   const vex_rrdb_desc& a = P->arch;
   const size_t npix = (size_t)n * H * W;
   const Layout L = ws_layout(a, npix);
+  P->canvas_h0 = H;
   if (L.total > P->ws_bytes) {
     VEX_CUDA(ctx, cudaDeviceSynchronize());
     if (P->ws) cudaFree(P->ws);
@@ -367,6 +398,15 @@ int rrdb_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f3
                                                     C::SMEM, s>>>(p);
     ctx->launches++;
     VEX_CUDA(ctx, cudaGetLastError());
+    if (!P->canvas_dims.empty()) {
+      if ((int)P->canvas_dims.size() != 2 * n || n > rrdb::MAXB) return fail(ctx, VEX_ERR_INVALID, "rrdb: inconsistent canvas table");
+      CanvasTab t{};
+      for (int i = 0; i < n; ++i) { t.vh[i] = (short)P->canvas_dims[2 * i]; t.vw[i] = (short)P->canvas_dims[2 * i + 1]; }
+      const size_t nchunk = npix * 8;
+      zero_outside_kernel<<<(unsigned)((nchunk + 255) / 256), 256, 0, s>>>(feat, nchunk, H, W, t);
+      ctx->launches++;
+      VEX_CUDA(ctx, cudaGetLastError());
+    }
     VEX_CUDA(ctx, cudaMemcpy2DAsync(D[0], 384, feat, 128, 128, npix, cudaMemcpyDeviceToDevice, s));
   }
   if (out_f32 && tap == 1) return emit(feat, 64, 0, 64, npix, HW);
@@ -441,8 +481,15 @@ int rrdb_forward(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float* out_f3
 }
 
 // `_enhance_frame` (:286-306) on the device: one frame, tiled like `_tile_process` (:324-372) when either side exceeds
-// tile_size, else `_process_single`.  Tiles are cropped with padding by a strided device copy, run through the network,
-// and their un-padded cores pasted into the output frame.  in / out are packed u8 HWC device buffers.
+// tile_size, else `_process_single`.  in / out are packed u8 HWC device buffers.
+//
+// The reference runs its tiles one after the other.  Here the tiles of a frame are independent images of one BATCH: each
+// is cropped (with its padding) to the top-left corner of its own Hc x Wc canvas, where Hc x Wc is the largest padded tile,
+// and every layer is launched once for all of them (option rrdb_batch, default on).  The conv kernel knows each canvas's
+// valid size and keeps everything outside it zero, so a tile sees the same zero padding as when it runs alone and the
+// result is bit-identical (tests/test_rrdb_gpu.py) - but a layer launch now has ~12x the work items: the fill/drain of the
+// per-CTA pipelines, the launch gap and the rounding-up of items to whole waves of 148 CTAs are paid once per layer
+// instead of once per layer AND tile.  Batches hold at most MAXB tiles and ws_budget_mb of activations.
 int rrdb_frame(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int h, int w, int tile_size, int tile_pad, int in_bgr,
                int out_bgr, cudaStream_t s) {
   RrdbPlan* P = ctx->rrdb;
@@ -450,35 +497,70 @@ int rrdb_frame(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int h, int w, int 
   if (tile_size <= 0 || tile_pad < 0) return fail(ctx, VEX_ERR_INVALID, "vex_rrdb_frame_u8: bad tile geometry");
   const int S = P->arch.scale;
   if (h <= tile_size && w <= tile_size) return rrdb_forward(ctx, in, out, nullptr, 0, 1, h, w, in_bgr, out_bgr, s);
-  const size_t side = (size_t)std::min(tile_size + 2 * tile_pad, std::max(h, w));
-  const size_t need_in = side * side * 3, need_out = need_in * S * S;
-  if (need_in > P->tile_in_bytes || need_out > P->tile_out_bytes) {
-    VEX_CUDA(ctx, cudaDeviceSynchronize());
-    if (P->tile_in) cudaFree(P->tile_in);
-    if (P->tile_out) cudaFree(P->tile_out);
-    P->tile_in = P->tile_out = nullptr;
-    P->tile_in_bytes = P->tile_out_bytes = 0;
-    VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&P->tile_in), need_in));
-    VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&P->tile_out), need_out));
-    P->tile_in_bytes = need_in; P->tile_out_bytes = need_out;
-  }
+
+  struct Tile { int sx, sy, ex, ey, px0, py0, tw, th; };
+  std::vector<Tile> tiles;
   const int tiles_x = (w + tile_size - 1) / tile_size, tiles_y = (h + tile_size - 1) / tile_size;
   for (int ty = 0; ty < tiles_y; ++ty)
     for (int tx = 0; tx < tiles_x; ++tx) {
-      const int sx = tx * tile_size, sy = ty * tile_size;
-      const int ex = std::min(sx + tile_size, w), ey = std::min(sy + tile_size, h);
-      const int px0 = std::max(sx - tile_pad, 0), px1 = std::min(ex + tile_pad, w);
-      const int py0 = std::max(sy - tile_pad, 0), py1 = std::min(ey + tile_pad, h);
-      const int tw = px1 - px0, th = py1 - py0;
-      VEX_CUDA(ctx, cudaMemcpy2DAsync(P->tile_in, (size_t)tw * 3, in + ((size_t)py0 * w + px0) * 3, (size_t)w * 3,
-                                      (size_t)tw * 3, th, cudaMemcpyDeviceToDevice, s));
-      int rc = rrdb_forward(ctx, P->tile_in, P->tile_out, nullptr, 0, 1, th, tw, in_bgr, out_bgr, s);
-      if (rc) return rc;
-      const size_t pl = (size_t)(sx - px0) * S, pt = (size_t)(sy - py0) * S;
-      VEX_CUDA(ctx, cudaMemcpy2DAsync(out + ((size_t)sy * S * w * S + (size_t)sx * S) * 3, (size_t)w * S * 3,
-                                      P->tile_out + (pt * tw * S + pl) * 3, (size_t)tw * S * 3,
-                                      (size_t)(ex - sx) * S * 3, (size_t)(ey - sy) * S, cudaMemcpyDeviceToDevice, s));
+      Tile t;
+      t.sx = tx * tile_size; t.sy = ty * tile_size;
+      t.ex = std::min(t.sx + tile_size, w); t.ey = std::min(t.sy + tile_size, h);
+      t.px0 = std::max(t.sx - tile_pad, 0); t.py0 = std::max(t.sy - tile_pad, 0);
+      t.tw = std::min(t.ex + tile_pad, w) - t.px0; t.th = std::min(t.ey + tile_pad, h) - t.py0;
+      tiles.push_back(t);
     }
+  const size_t per_px = ws_layout(P->arch, 1 << 20).total >> 20;            // workspace bytes per input pixel
+  const size_t budget_px = std::max<size_t>(((size_t)ctx->opt_ws_budget_mb << 20) / std::max<size_t>(per_px, 1), 1);
+  const int max_batch = ctx->opt_rrdb_batch ? rrdb::MAXB : 1;
+
+  size_t first = 0;
+  while (first < tiles.size()) {
+    // greedy batch of consecutive tiles: at most MAXB canvases, n * Hc * Wc within the workspace budget
+    int Hc = tiles[first].th, Wc = tiles[first].tw;
+    size_t last = first + 1;
+    while (last < tiles.size() && (int)(last - first) < max_batch) {
+      const int nh = std::max(Hc, tiles[last].th), nw = std::max(Wc, tiles[last].tw);
+      if ((last - first + 1) * (size_t)nh * nw > budget_px) break;
+      Hc = nh; Wc = nw; ++last;
+    }
+    const int n = (int)(last - first);
+    const size_t canvas_in = (size_t)Hc * Wc * 3, canvas_out = canvas_in * S * S;
+    const size_t need_in = canvas_in * n, need_out = canvas_out * n;
+    if (need_in > P->tile_in_bytes || need_out > P->tile_out_bytes) {
+      VEX_CUDA(ctx, cudaDeviceSynchronize());
+      if (P->tile_in) cudaFree(P->tile_in);
+      if (P->tile_out) cudaFree(P->tile_out);
+      P->tile_in = P->tile_out = nullptr;
+      P->tile_in_bytes = P->tile_out_bytes = 0;
+      VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&P->tile_in), need_in));
+      VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&P->tile_out), need_out));
+      P->tile_in_bytes = need_in; P->tile_out_bytes = need_out;
+    }
+    bool uniform = true;
+    for (size_t i = first; i < last; ++i) uniform = uniform && tiles[i].th == Hc && tiles[i].tw == Wc;
+    if (!uniform) VEX_CUDA(ctx, cudaMemsetAsync(P->tile_in, 0, need_in, s));   // zero = what a smaller tile has beyond its edge
+    std::vector<int> dims;
+    for (size_t i = first; i < last; ++i) {
+      const Tile& t = tiles[i];
+      VEX_CUDA(ctx, cudaMemcpy2DAsync(P->tile_in + (i - first) * canvas_in, (size_t)Wc * 3,
+                                      in + ((size_t)t.py0 * w + t.px0) * 3, (size_t)w * 3, (size_t)t.tw * 3, t.th,
+                                      cudaMemcpyDeviceToDevice, s));
+      dims.push_back(t.th); dims.push_back(t.tw);
+    }
+    if (!uniform) P->canvas_dims = dims;
+    const int rc = rrdb_forward(ctx, P->tile_in, P->tile_out, nullptr, 0, n, Hc, Wc, in_bgr, out_bgr, s);
+    P->canvas_dims.clear();
+    if (rc) return rc;
+    for (size_t i = first; i < last; ++i) {
+      const Tile& t = tiles[i];
+      const size_t pl = (size_t)(t.sx - t.px0) * S, pt = (size_t)(t.sy - t.py0) * S;
+      VEX_CUDA(ctx, cudaMemcpy2DAsync(out + ((size_t)t.sy * S * w * S + (size_t)t.sx * S) * 3, (size_t)w * S * 3,
+                                      P->tile_out + (i - first) * canvas_out + (pt * Wc * S + pl) * 3, (size_t)Wc * S * 3,
+                                      (size_t)(t.ex - t.sx) * S * 3, (size_t)(t.ey - t.sy) * S, cudaMemcpyDeviceToDevice, s));
+    }
+    first = last;
+  }
   return VEX_OK;
 }
 

@@ -47,6 +47,12 @@ constexpr int SA = 2;
 constexpr int NTHREADS = 224;    // warp 0 TMA (activations), warp 1 MMA, warps 2-5 epilogue (TMEM lane quarter = warp & 3), warp 6 weights
 constexpr int APS = 2;           // accumulators (128 pixels each) per work item
 constexpr int ROWS = APS * 4;
+constexpr int MAXB = 16;         // images of different valid sizes per launch (canvas batching)
+
+// work items of a vh x vw image on an H x W canvas: the valid part and, where the canvas has room, one more row / column
+// (stored as zeros: the conv padding of the next layer)
+__host__ __device__ constexpr int items_x(int vw, int W) { return ((vw + 1 < W ? vw + 1 : W) + TILE_W - 1) / TILE_W; }
+__host__ __device__ constexpr int items_y(int vh, int H) { return ((vh + 1 < H ? vh + 1 : H) + ROWS - 1) / ROWS; }
 
 template <int BN>
 struct Cfg {
@@ -72,7 +78,16 @@ struct Params {
   int lrelu;              // LeakyReLU(0.2) after the bias
   int ups2;               // store every pixel to the 2 x 2 block of a twice as large output (nearest-neighbour upsample)
   int H, W, NC;           // NC = 64-channel chunks of the input that are read
+  int klast;              // K = 16 steps of the LAST chunk: 2 when Cin % 64 == 32 (conv2 / conv4 of a dense block), else 4
   int tiles_x, tiles_y, n_img;
+  // Canvas batching (the tile loop of `_tile_process`, realesrgan_handler.py:324-372, in ONE launch per layer): the n_tab
+  // images of the batch share the H x W canvas but image i is only vh[i] x vw[i] large, anchored at (0, 0).  Work items
+  // cover the valid part plus one more row / column, and every store outside the valid part writes ZERO, so the next
+  // layer sees exactly the zero padding a tile run alone gets from the tensor map's out-of-bounds fill.  n_tab == 0: all
+  // n_img images are H x W (tiles_x / tiles_y above).
+  int n_tab;
+  short vh[MAXB], vw[MAXB];
+  int item0[MAXB + 1];    // first work item of image i; item0[n_tab] = total
   int force_ring;         // A/B switch (option rrdb_ring): stream the weights through the slice buffer even when they would fit
   long long* dbg;         // optional [gridDim.x][8] cycle counters (option conv_dbg): MMA thread 0 total, 1 wait acc_empty, 2 wait a_full,
                           // 3 wait w_full; epilogue warp 2: 4 wait acc_full, 5 work; producer: 6 wait a_empty, 7 wait w_empty
@@ -95,6 +110,24 @@ __device__ __forceinline__ uint32_t pack_f16x2_sat(float lo, float hi) {
 __device__ __forceinline__ float2 unpack_f16x2(uint32_t w) {
   return __half22float2(*reinterpret_cast<const __half2*>(&w));
 }
+struct Item { int n, x0, y0, vh, vw; };
+// work item -> image, tile origin and the image's valid size
+template <class P>
+__device__ __forceinline__ Item decode_item(const P& p, int it) {
+  Item r;
+  if (p.n_tab == 0) {
+    const int q = it / p.tiles_x;
+    r.n = q / p.tiles_y; r.x0 = (it % p.tiles_x) * TILE_W; r.y0 = (q % p.tiles_y) * ROWS; r.vh = p.H; r.vw = p.W;
+  } else {
+    int n = 0;
+    while (n + 1 < p.n_tab && it >= p.item0[n + 1]) ++n;
+    r.vh = p.vh[n]; r.vw = p.vw[n];
+    const int tx = items_x(r.vw, p.W), l = it - p.item0[n];
+    r.n = n; r.x0 = (l % tx) * TILE_W; r.y0 = (l / tx) * ROWS;
+  }
+  return r;
+}
+
 // instruction descriptor for kind::f16 with fp16 A/B (format 0), fp32 D, both K-major
 __host__ __device__ constexpr uint32_t idesc_f16_f32(int m, int n) {
   return (1u << 4) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
@@ -102,7 +135,7 @@ __host__ __device__ constexpr uint32_t idesc_f16_f32(int m, int n) {
 
 template <int BN>
 __global__ void __launch_bounds__(NTHREADS, 1)
-rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
+rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ Params p) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -121,7 +154,7 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
   float* bias_s = reinterpret_cast<float*>(sm + C::BIAS_OFF);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int total = p.tiles_x * p.tiles_y * p.n_img;
+  const int total = p.n_tab ? p.item0[p.n_tab] : p.tiles_x * p.tiles_y * p.n_img;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < SA; ++i) { ptx::mbar_init(a_full + 8 * i, 1); ptx::mbar_init(a_empty + 8 * i, 1); }
@@ -150,9 +183,8 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
       long long t6 = 0, tq = 0;
       pdl_wait();                                       // activations of the previous layer
       for (int it = blockIdx.x; it < total; it += gridDim.x) {
-        const int txi = it % p.tiles_x, r = it / p.tiles_x;
-        const int tyi = r % p.tiles_y, n = r / p.tiles_y;
-        const int x0 = txi * TILE_W, y0 = tyi * ROWS;
+        const Item im = decode_item(p, it);
+        const int x0 = im.x0, y0 = im.y0, n = im.n;
         for (int c = 0; c < p.NC; ++c) {
           if (dbg) tq = clock64();
           ptx::mbar_wait(a_empty + 8 * sa, pa ^ 1);
@@ -209,6 +241,7 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
           ptx::mbar_wait(a_full + 8 * sa, pa);
           if (dbg) t2 += clock64() - tq;
           const uint32_t abase = a_stage0 + sa * C::A_STAGE;
+          const int ksteps = c == p.NC - 1 ? p.klast : KC / 16;   // the upper half of a 96 / 160-channel input's last chunk is not read
           for (int t = 0; t < 9; ++t) {
             if (resident) { sw = c * 9 + t; pw = 0; }   // loaded once: phase 0 of its barrier stays complete
             if (dbg) tq = clock64();
@@ -224,6 +257,7 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
             for (int a = 0; a < APS; ++a) {
 #pragma unroll
               for (int k = 0; k < KC / 16; ++k) {
+                if (k >= ksteps) break;
                 const uint64_t ad = ptx::desc_advance(ad0, a * (128 * 128) + k * 32);
                 const uint64_t bd = ptx::desc_advance(bd0, k * 32);
                 ptx::mma_bf16_ss(tmem + (slot * APS + a) * BN, ad, bd, idesc, (c | t | k) != 0);
@@ -264,13 +298,15 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
     pdl_wait();                                         // residuals are read and the output buffer is written below
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++kk) {
       const uint32_t slot = kk & 1, pacc = (kk >> 1) & 1;
-      const int txi = it % p.tiles_x, r = it / p.tiles_x;
-      const int tyi = r % p.tiles_y, n = r / p.tiles_y;
-      const int x0 = txi * TILE_W;
-      const int ybase = tyi * ROWS + q;                 // accumulator row m = a*128 + q*32 + lane -> y = ybase + 4a
-      bool pxok[4];
+      const Item im = decode_item(p, it);
+      const int x0 = im.x0, n = im.n;
+      const int ybase = im.y0 + q;                      // accumulator row m = a*128 + q*32 + lane -> y = ybase + 4a
+      bool pxok[4], pxval[4];                           // inside the canvas (stored) / inside the image (else stored as zero)
 #pragma unroll
-      for (int i = 0; i < 4; ++i) pxok[i] = (8 * i + cpx < TILE_W) && (x0 + 8 * i + cpx < p.W);
+      for (int i = 0; i < 4; ++i) {
+        pxok[i] = (8 * i + cpx < TILE_W) && (x0 + 8 * i + cpx < p.W);
+        pxval[i] = x0 + 8 * i + cpx < im.vw;
+      }
       const bool dbg = p.dbg != nullptr && warp == 2 && lane == 0;
       const long long te0 = dbg ? clock64() : 0;
       ptx::mbar_wait(acc_full + 8 * slot, pacc);
@@ -280,7 +316,7 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
       for (int u = 0; u < APS * GROUPS; ++u) {
         const int a = u / GROUPS, g = u % GROUPS;
         const int y = ybase + 4 * a;
-        const bool yok = y < p.H;
+        const bool yok = y < p.H, yval = y < im.vh;
         uint32_t v[32];
         ptx::tmem_ld_32x32(tq + (slot * APS + a) * BN + g * 32, v);
         // residual rows in the co-pattern (pixel 8i + cpx, chunk cch), issued before the TMEM wait
@@ -289,13 +325,13 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
         if (p.r1) {
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            s1[i] = (yok && pxok[i]) ? __ldg(reinterpret_cast<const uint4*>(p.r1 + (pix0 + 8 * i) * p.r1_cs + g * 32 + cch * 8))
+            s1[i] = (yval && pxok[i] && pxval[i]) ? __ldg(reinterpret_cast<const uint4*>(p.r1 + (pix0 + 8 * i) * p.r1_cs + g * 32 + cch * 8))
                                      : make_uint4(0, 0, 0, 0);
         }
         if (p.r2) {
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            s2[i] = (yok && pxok[i]) ? __ldg(reinterpret_cast<const uint4*>(p.r2 + (pix0 + 8 * i) * p.r2_cs + g * 32 + cch * 8))
+            s2[i] = (yval && pxok[i] && pxval[i]) ? __ldg(reinterpret_cast<const uint4*>(p.r2 + (pix0 + 8 * i) * p.r2_cs + g * 32 + cch * 8))
                                      : make_uint4(0, 0, 0, 0);
         }
         ptx::tmem_ld_wait();
@@ -348,8 +384,9 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
         __syncwarp();
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const uint4 o = *reinterpret_cast<const uint4*>(stage + co_off[i]);
+          uint4 o = *reinterpret_cast<const uint4*>(stage + co_off[i]);
           if (!(yok && pxok[i])) continue;
+          if (!(yval && pxval[i])) o = make_uint4(0, 0, 0, 0);
           const int x = x0 + 8 * i + cpx;
           if (!p.ups2) {
             *reinterpret_cast<uint4*>(p.out + (((size_t)n * oh + y) * ow + x) * p.out_cs + p.out_c0 + g * 32 + cch * 8) = o;

@@ -245,6 +245,11 @@ class B200RealESRGAN:
         self._lib.vex_kernel_launches(self._ctx, C.byref(v))
         return int(v.value)
 
+    def set_option(self, name: str, value: int) -> int:
+        """`vex_set_option` on this handler's context (e.g. ``rrdb_batch``, ``pdl``); returns the previous value."""
+        self._ensure_ctx()
+        return self._lib.vex_set_option(self._ctx, name.encode(), int(value))
+
     # ------------------------------------------------------------------ RealESRGANHandler frame path
     def _host_frame(self, frame: np.ndarray, in_bgr: bool, out_bgr: bool, tiled: Optional[bool] = None, slot: int = 0) -> np.ndarray:
         """One host frame through the GPU: pinned H2D, the (tiled) network, pinned D2H.  Returns a view of the pinned

@@ -9,5 +9,6 @@ hd = B200RealESRGAN(device="cuda:0", scale=4, seed=0, num_block=1); hd._ensure_m
 x = torch.from_numpy(synth.random_frame(H, W, np.random.default_rng(0))).cuda()[None]
 for _ in range(2): hd.upscale_device(x)
 torch.cuda.synchronize()
+if len(sys.argv) > 3: print("probe", sys.argv[3], hd._lib.vex_set_option(hd._ctx, b"thin_probe", int(sys.argv[3])), file=sys.stderr)
 hd._lib.vex_set_option(hd._ctx, b"conv_dbg", 1)
 hd.upscale_device(x); torch.cuda.synchronize()

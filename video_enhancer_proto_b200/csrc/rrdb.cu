@@ -151,6 +151,7 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, const __half* in, int in_cs, cons
   p.n_img = n;
   p.dbg = nullptr;
   p.force_ring = ctx->opt_rrdb_ring;
+  p.probe = ctx->opt_thin_probe;
   long long total = (long long)p.tiles_x * p.tiles_y * n;
   p.n_tab = 0;
   memset(p.vh, 0, sizeof(p.vh)); memset(p.vw, 0, sizeof(p.vw)); memset(p.item0, 0, sizeof(p.item0));

@@ -22,10 +22,11 @@
 // by zero weights (the buffer only ever holds finite values, see above): 10 % more MMAs over a block, no second code path.
 //
 // N = 32 / 64 makes the SS-mode MMA shared-memory bound (4 KB of A per 128 x N x 16 MMA at 128 B/clk: 40 / 48 clocks
-// against 16 / 32 of math), so unlike conv_tc3 there is nothing to win from CTA pairs and this kernel is single-CTA:
-// warp 0 activation (TMA) producer, warp 1 MMA issuer + TMEM owner, warps 2-5 epilogue, warp 6 weight producer; two TMEM
-// slots of APS accumulators so the epilogue of item k overlaps the MMAs of item k+1.  Persistent grid; work item = (image,
-// 8-row x 30-column tile).
+// against 16 / 32 of math; measured alone 44.7 / 48.1, tools/ubench/mma_rate.cu), so unlike conv_tc3 there is little to win
+// from CTA pairs and this kernel is single-CTA: warp 0 activation (TMA) producer, warps 1 and 7 MMA issuers (one
+// accumulator each; warp 1 owns the TMEM allocation), warps 2-5 epilogue, warp 6 weight producer; two TMEM slots of APS
+// accumulators so the epilogue of item k overlaps the MMAs of item k+1.  Persistent grid; work item = (image, 8-row x
+// 30-column tile).
 // Weights: when all (chunk, tap) slices of the layer fit the slice buffer (every Cout = 32 layer: <= 27 x 4 KB; the
 // 64 -> 64 layers: 9 x 8 KB) they are loaded ONCE per CTA and stay resident; only conv5 (192 -> 64, 216 KB) streams them
 // through the buffer as a ring.  The first version had one producer thread issue activations and weights in program order;
@@ -44,7 +45,7 @@ constexpr int PITCH = 32;
 constexpr int TILE_W = 30;
 constexpr int KC = 64;
 constexpr int SA = 2;
-constexpr int NTHREADS = 224;    // warp 0 TMA (activations), warp 1 MMA, warps 2-5 epilogue (TMEM lane quarter = warp & 3), warp 6 weights
+constexpr int NTHREADS = 256;    // warp 0 TMA (activations), warps 1 and 7 MMA (one accumulator each), warps 2-5 epilogue (TMEM lane quarter = warp & 3), warp 6 weights
 constexpr int APS = 2;           // accumulators (128 pixels each) per work item
 constexpr int ROWS = APS * 4;
 constexpr int MAXB = 16;         // images of different valid sizes per launch (canvas batching)
@@ -88,6 +89,8 @@ struct Params {
   int n_tab;
   short vh[MAXB], vw[MAXB];
   int item0[MAXB + 1];    // first work item of image i; item0[n_tab] = total
+  int probe;              // -DVEX_DEBUG_PROBES builds only (wrong pixels, timing experiments): 256 = the activation producer loads the
+                          // first SA stages and then only signals; 512 = the epilogue only waits and releases; 2048 = no MMAs
   int force_ring;         // A/B switch (option rrdb_ring): stream the weights through the slice buffer even when they would fit
   long long* dbg;         // optional [gridDim.x][8] cycle counters (option conv_dbg): MMA thread 0 total, 1 wait acc_empty, 2 wait a_full,
                           // 3 wait w_full; epilogue warp 2: 4 wait acc_full, 5 work; producer: 6 wait a_empty, 7 wait w_empty
@@ -157,9 +160,10 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
   const int total = p.n_tab ? p.item0[p.n_tab] : p.tiles_x * p.tiles_y * p.n_img;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < SA; ++i) { ptx::mbar_init(a_full + 8 * i, 1); ptx::mbar_init(a_empty + 8 * i, 1); }
-    for (int i = 0; i < C::SW; ++i) { ptx::mbar_init(w_full + 8 * i, 1); ptx::mbar_init(w_empty + 8 * i, 1); }
-    for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full + 8 * i, 1); ptx::mbar_init(acc_empty + 8 * i, 4); }
+    // consumer-side barriers count APS arrivals: each of the two MMA threads commits its own MMAs
+    for (int i = 0; i < SA; ++i) { ptx::mbar_init(a_full + 8 * i, 1); ptx::mbar_init(a_empty + 8 * i, APS); }
+    for (int i = 0; i < C::SW; ++i) { ptx::mbar_init(w_full + 8 * i, 1); ptx::mbar_init(w_empty + 8 * i, APS); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full + 8 * i, APS); ptx::mbar_init(acc_empty + 8 * i, 4); }
     ptx::fence_mbar_init();
     ptx::prefetch_tensormap(&amap);
   }
@@ -181,6 +185,9 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
       uint32_t sa = 0, pa = 0;
       const bool dbg = p.dbg != nullptr;
       long long t6 = 0, tq = 0;
+#ifdef VEX_DEBUG_PROBES
+      int nload = 0;
+#endif
       pdl_wait();                                       // activations of the previous layer
       for (int it = blockIdx.x; it < total; it += gridDim.x) {
         const Item im = decode_item(p, it);
@@ -189,6 +196,10 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
           if (dbg) tq = clock64();
           ptx::mbar_wait(a_empty + 8 * sa, pa ^ 1);
           if (dbg) t6 += clock64() - tq;
+#ifdef VEX_DEBUG_PROBES
+          if ((p.probe & 256) && nload >= SA) { ptx::mbar_arrive(a_full + 8 * sa); if (++sa == SA) { sa = 0; pa ^= 1; } continue; }
+          ++nload;
+#endif
           ptx::mbar_expect_tx(a_full + 8 * sa, C::A_STAGE);
           ptx::tma_load_4d(a_stage0 + sa * C::A_STAGE, &amap, a_full + 8 * sa, c * KC, x0 - 1, y0 - 1, n);
           if (++sa == SA) { sa = 0; pa ^= 1; }
@@ -222,12 +233,18 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
         if (dbg) p.dbg[blockIdx.x * 8 + 7] = t7;
       }
     }
-  } else if (warp == 1) {
-    // ============================== MMA issuer ================================
+  } else if (warp == 1 || warp == 7) {
+    // ============================== MMA issuers ===============================
+    // TWO issuing threads, one per accumulator of an item.  A single thread needs ~65 clocks of its own instruction
+    // stream per tcgen05.mma here (descriptor arithmetic, uniform-register moves, branches: measured with the MMAs
+    // themselves switched off, tools/rconv_probe.py) while the tensor pipe can take an N = 32 MMA every 45 clocks
+    // (tools/ubench/mma_rate.cu): with one issuer the kernel was bound by that thread, not by the pipe.
+    static_assert(APS == 2, "one MMA warp per accumulator");
+    const int a = warp == 1 ? 0 : 1;
     if (ptx::elect_one()) {
       constexpr uint32_t idesc = idesc_f16_f32(128, BN);
       uint32_t sa = 0, pa = 0, sw = 0, pw = 0, kk = 0;
-      const bool dbg = p.dbg != nullptr;
+      const bool dbg = p.dbg != nullptr && a == 0;
       long long t1 = 0, t2 = 0, t3 = 0, tq = 0;
       const long long tm0 = dbg ? clock64() : 0;
       for (int it = blockIdx.x; it < total; it += gridDim.x, ++kk) {
@@ -253,13 +270,15 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
             const uint32_t tap_off = ((t / 3) * PITCH + (t % 3)) * 128;
             const uint64_t ad0 = ptx::smem_desc_sw128(abase + tap_off, 0);
             const uint64_t bd0 = ptx::smem_desc_sw128(w_stage0 + sw * C::W_SLICE, 0);
-#pragma unroll
-            for (int a = 0; a < APS; ++a) {
+            {
 #pragma unroll
               for (int k = 0; k < KC / 16; ++k) {
                 if (k >= ksteps) break;
                 const uint64_t ad = ptx::desc_advance(ad0, a * (128 * 128) + k * 32);
                 const uint64_t bd = ptx::desc_advance(bd0, k * 32);
+#ifdef VEX_DEBUG_PROBES
+                if (p.probe & 2048) continue;               // no MMAs at all: what the other roles cost on their own
+#endif
                 ptx::mma_bf16_ss(tmem + (slot * APS + a) * BN, ad, bd, idesc, (c | t | k) != 0);
               }
             }
@@ -312,8 +331,13 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
       ptx::mbar_wait(acc_full + 8 * slot, pacc);
       const long long te1 = dbg ? clock64() : 0;
       ptx::tc_fence_after();
+#ifdef VEX_DEBUG_PROBES
+      const int nunits = (p.probe & 512) ? 0 : APS * GROUPS;
+#else
+      constexpr int nunits = APS * GROUPS;
+#endif
 #pragma unroll 1
-      for (int u = 0; u < APS * GROUPS; ++u) {
+      for (int u = 0; u < nunits; ++u) {
         const int a = u / GROUPS, g = u % GROUPS;
         const int y = ybase + 4 * a;
         const bool yok = y < p.H, yval = y < im.vh;

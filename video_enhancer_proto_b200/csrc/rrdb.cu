@@ -84,21 +84,24 @@ int upload(vex_ctx* ctx, T** dst, const void* src, size_t bytes) {
   return VEX_OK;
 }
 
-// nn.Conv2d weight [cout][cin][3][3] -> [chunk][tap] slices of cout rows x 64 fp16 in the SWIZZLE_128B K-major image
-// (16-byte chunk j of row r at j ^ (r & 7)); input channels beyond cin are zero columns.
+// nn.Conv2d weight [cout][cin][3][3] -> per block of 32 output channels [chunk][dy] slices of 96 rows x 64 fp16 in the
+// SWIZZLE_128B K-major image (16-byte chunk j of row r at j ^ (r & 7)): row dx*32 + co holds W[co][ci][dy][dx], the three
+// horizontal taps side by side in the MMA's N (rrdb_tc.cuh); input channels beyond cin are zero columns.
 int pack_rconv(vex_ctx* ctx, RConv& L, const float* w, const float* b) {
   L.nc = (L.cin + 63) / 64;
-  std::vector<uint16_t> img((size_t)L.nc * 9 * L.cout * 64, 0);
-  for (int c = 0; c < L.nc; ++c)
-    for (int t = 0; t < 9; ++t) {
-      uint16_t* slice = img.data() + ((size_t)c * 9 + t) * L.cout * 64;
-      for (int r = 0; r < L.cout; ++r)
-        for (int k = 0; k < 64; ++k) {
-          const int ci = c * 64 + k;
-          const float v = ci < L.cin ? w[((size_t)r * L.cin + ci) * 9 + t] : 0.f;
-          slice[(size_t)r * 64 + (((k >> 3) ^ (r & 7)) << 3) + (k & 7)] = f32_to_f16(v);
-        }
-    }
+  const int nblk = L.cout / rrdb::CO;
+  std::vector<uint16_t> img((size_t)nblk * L.nc * 3 * rrdb::NB * 64, 0);
+  for (int blk = 0; blk < nblk; ++blk)
+    for (int c = 0; c < L.nc; ++c)
+      for (int dy = 0; dy < 3; ++dy) {
+        uint16_t* slice = img.data() + (((size_t)blk * L.nc + c) * 3 + dy) * rrdb::NB * 64;
+        for (int r = 0; r < rrdb::NB; ++r)
+          for (int k = 0; k < 64; ++k) {
+            const int ci = c * 64 + k, dx = r / rrdb::CO, co = blk * rrdb::CO + r % rrdb::CO;
+            const float v = ci < L.cin ? w[((size_t)co * L.cin + ci) * 9 + dy * 3 + dx] : 0.f;
+            slice[(size_t)r * 64 + (((k >> 3) ^ (r & 7)) << 3) + (k & 7)] = f32_to_f16(v);
+          }
+      }
   int rc = upload(ctx, &L.wpack, img.data(), img.size() * 2);
   if (rc) return rc;
   return upload(ctx, &L.bias, b, (size_t)L.cout * 4);
@@ -126,23 +129,24 @@ struct Epi {
   int lrelu = 0, ups2 = 0;
 };
 
-template <int BN>
-int launch_rconv(vex_ctx* ctx, const RConv& L, const __half* in, int in_cs, const Epi& e, int n, int H, int W,
+// one launch = one block of 32 output channels (blk) of the layer
+int launch_rconv(vex_ctx* ctx, const RConv& L, int blk, const __half* in, int in_cs, const Epi& e, int n, int H, int W,
                  cudaStream_t s) {
-  using C = rrdb::Cfg<BN>;
+  using C = rrdb::Cfg;
   RrdbPlan* P = ctx->rrdb;
   CUtensorMap amap;
   int rc = make_map(ctx, &amap, in, n, H, W, in_cs, rrdb::ROWS + 2);
   if (rc) return rc;
-  const unsigned abit = BN == 32 ? 1u : 2u;
+  const unsigned abit = 1u;
   if (!(P->attr_mask & abit)) {
-    VEX_CUDA(ctx, cudaFuncSetAttribute(rrdb::rconv3x3_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+    VEX_CUDA(ctx, cudaFuncSetAttribute(rrdb::rconv3x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
     P->attr_mask |= abit;
   }
   rrdb::Params p;
-  p.wpack = L.wpack; p.bias = L.bias;
-  p.out = e.out; p.out_cs = e.out_cs; p.out_c0 = e.out_c0;
-  p.r1 = e.r1; p.r1_cs = e.r1_cs; p.a1 = e.a1; p.r2 = e.r2; p.r2_cs = e.r2_cs; p.a2 = e.a2;
+  p.wpack = L.wpack + (size_t)blk * L.nc * 3 * C::W_SLICE; p.bias = L.bias + blk * rrdb::CO;
+  p.out = e.out; p.out_cs = e.out_cs; p.out_c0 = e.out_c0 + blk * rrdb::CO;
+  p.r1 = e.r1 ? e.r1 + blk * rrdb::CO : nullptr; p.r1_cs = e.r1_cs; p.a1 = e.a1;
+  p.r2 = e.r2 ? e.r2 + blk * rrdb::CO : nullptr; p.r2_cs = e.r2_cs; p.a2 = e.a2;
   p.lrelu = e.lrelu; p.ups2 = e.ups2;
   p.H = H; p.W = W; p.NC = L.nc;
   p.klast = L.cin % 64 == 32 ? 2 : 4;
@@ -150,7 +154,6 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, const __half* in, int in_cs, cons
   p.tiles_y = (H + rrdb::ROWS - 1) / rrdb::ROWS;
   p.n_img = n;
   p.dbg = nullptr;
-  p.force_ring = ctx->opt_rrdb_ring;
   p.probe = ctx->opt_thin_probe;
   long long total = (long long)p.tiles_x * p.tiles_y * n;
   p.n_tab = 0;
@@ -184,7 +187,7 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, const __half* in, int in_cs, cons
   cfg.attrs = attr; cfg.numAttrs = 1;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (p.dbg) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, s); }
-  VEX_CUDA(ctx, cudaLaunchKernelEx(&cfg, rrdb::rconv3x3_kernel<BN>, amap, p));
+  VEX_CUDA(ctx, cudaLaunchKernelEx(&cfg, rrdb::rconv3x3_kernel, amap, p));
   ctx->launches++;
   VEX_CUDA(ctx, cudaGetLastError());
   if (p.dbg) {
@@ -201,19 +204,22 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, const __half* in, int in_cs, cons
     for (unsigned b = 0; b < grid; ++b)
       for (int i = 0; i < 8; ++i) a[i] += (double)h[(size_t)b * 8 + i] / grid;
     const double items = (double)total / grid;
-    const double mma_clk = (double)L.nc * 9 * rrdb::APS * 4;          // MMAs per item
-    fprintf(stderr, "[rconv_dbg cin=%d cout=%d %dx%d] %.1f us, items/cta=%.2f, cycles/item: MMA total=%.0f (%.1f clk/MMA) wait_acc_empty=%.0f "
-                    "wait_a_full=%.0f wait_w_full=%.0f | epilogue wait_acc_full=%.0f work=%.0f | producer wait_a_empty=%.0f wait_w_empty=%.0f\n",
-            L.cin, L.cout, H, W, ms * 1e3, items, a[0] / items, a[0] / items / mma_clk, a[1] / items, a[2] / items, a[3] / items,
-            a[4] / items, a[5] / items, a[6] / items, a[7] / items);
+    const double mma_clk = ((double)(L.nc - 1) * 4 + p.klast) * 3 * rrdb::APS;   // MMAs (N = 96) per item
+    fprintf(stderr, "[rconv_dbg cin=%d cout=%d blk=%d %dx%d] %.1f us, items/cta=%.2f, cycles/item: MMA total=%.0f (%.1f clk/MMA) wait_acc_empty=%.0f "
+                    "wait_a_full=%.0f wait_w_full=%.0f | epilogue wait_acc_full=%.0f work=%.0f | producer wait_a_empty=%.0f\n",
+            L.cin, L.cout, blk, H, W, ms * 1e3, items, a[0] / items, a[0] / items / mma_clk, a[1] / items, a[2] / items, a[3] / items,
+            a[4] / items, a[5] / items, a[6] / items);
   }
   return VEX_OK;
 }
 
 int run_rconv(vex_ctx* ctx, const RConv& L, const __half* in, int in_cs, const Epi& e, int n, int H, int W,
               cudaStream_t s) {
-  return L.cout == 32 ? launch_rconv<32>(ctx, L, in, in_cs, e, n, H, W, s)
-                      : launch_rconv<64>(ctx, L, in, in_cs, e, n, H, W, s);
+  for (int blk = 0; blk < L.cout / rrdb::CO; ++blk) {
+    const int rc = launch_rconv(ctx, L, blk, in, in_cs, e, n, H, W, s);
+    if (rc) return rc;
+  }
+  return VEX_OK;
 }
 
 // fp16 NHWC channel slice -> fp32 NCHW (parity taps).  One thread per (pixel, channel).

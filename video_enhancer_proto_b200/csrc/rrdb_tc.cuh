@@ -1,6 +1,7 @@
 // conv3x3 (pad 1, stride 1) of the Real-ESRGAN RRDB network (reference models/enhancement/vsr/realesrgan_handler.py:23-100)
 // as an implicit GEMM on the sm_100a tensor cores: tcgen05.mma (fp16 x fp16 -> fp32 in TMEM), TMA-staged activation halo
-// tiles, mbarrier rings.  One kernel serves every conv3x3 of the network except the 3-channel ends:
+// tiles, mbarrier rings.  One kernel serves every conv3x3 of the network except the 3-channel ends, 32 output channels
+// per launch (the 64-channel layers are two launches):
 //
 //   ResidualDenseBlock.conv1..conv4 (:41-44, 50-53)  Cin = 64/96/128/160 -> 32, LeakyReLU(0.2), written into the channel
 //        SLICE [64+32k, 96+32k) of the block's 192-channel NHWC "dense" buffer, so torch.cat((x, x1, ...), 1) costs nothing;
@@ -15,23 +16,26 @@
 // points on the CPU gives 0.5 LSB of max error with fp16 against 4.8 LSB with bf16), fp32 accumulation, fp32
 // epilogue arithmetic, saturating fp16 stores (a stale or overflowing value can never become Inf/NaN in a buffer).
 //
-// GEMM view: M = output pixels, N = Cout (BN = 32 or 64), K = 9 taps x Cin.  As in conv_tc3.cuh one TMA box load brings a
-// halo tile [ROWS+2][PITCH=32 px][64 ch] (128 B per pixel, SWIZZLE_128B, out-of-bounds = 0 = conv padding) and tap (dy,dx)
-// is the same buffer with the descriptor start advanced by (dy*32+dx) rows; 30 of 32 columns are valid outputs.
-// Cin is consumed in 64-channel chunks; Cin = 96 / 160 read the next 32 channels of the dense buffer too and multiply them
-// by zero weights (the buffer only ever holds finite values, see above): 10 % more MMAs over a block, no second code path.
+// GEMM view.  One TMA box load brings a halo tile [ROWS+2][PITCH = 32 px][64 ch] (128 B per pixel, SWIZZLE_128B,
+// out-of-bounds = 0 = conv padding).  An accumulator covers 4 tile rows x 32 tile columns = 128 GEMM rows, one warp-wide
+// TMEM lane quarter per tile row.  The first version ran one MMA of N = 32 per tap (the A descriptor advanced by
+// dy*32+dx rows): an N = 32 MMA reads 4 KB of A and 1 KB of B from shared memory and is bound by that read, 44.7 clocks
+// against 16 of math (tools/ubench/mma_rate.cu), so the tensor pipe could never be more than a third busy.  Now the three
+// HORIZONTAL taps sit side by side in N:
+//        D[pixel m][dx*32 + co] = sum over dy, ci of  X[m + 32*dy][ci] * W[co][ci][dy][dx]
+// - only the vertical tap moves the A descriptor (by whole tile rows, which also keeps it on the 1 KB swizzle atom) - and
+// the epilogue finishes the convolution with two lane shuffles: the 32 lanes of a warp ARE the 32 columns of one tile row,
+// so   out[x] = D[x-1][0:32] + D[x][32:64] + D[x+1][64:96].   A K = 16 step of an accumulator is 3 MMAs of N = 96 (56 clocks
+// each, measured) instead of 9 of N = 32 (45 each): 168 clocks instead of 402.  30 of the 32 columns are valid outputs.
+// Cin is consumed in 64-channel chunks; Cin = 96 / 160 issue only the two K = 16 steps of their last chunk that exist.
 //
-// N = 32 / 64 makes the SS-mode MMA shared-memory bound (4 KB of A per 128 x N x 16 MMA at 128 B/clk: 40 / 48 clocks
-// against 16 / 32 of math; measured alone 44.7 / 48.1, tools/ubench/mma_rate.cu), so unlike conv_tc3 there is little to win
-// from CTA pairs and this kernel is single-CTA: warp 0 activation (TMA) producer, warps 1 and 7 MMA issuers (one
-// accumulator each; warp 1 owns the TMEM allocation), warps 2-5 epilogue, warp 6 weight producer; two TMEM slots of APS
-// accumulators so the epilogue of item k overlaps the MMAs of item k+1.  Persistent grid; work item = (image, 8-row x
-// 30-column tile).
-// Weights: when all (chunk, tap) slices of the layer fit the slice buffer (every Cout = 32 layer: <= 27 x 4 KB; the
-// 64 -> 64 layers: 9 x 8 KB) they are loaded ONCE per CTA and stay resident; only conv5 (192 -> 64, 216 KB) streams them
-// through the buffer as a ring.  The first version had one producer thread issue activations and weights in program order;
-// blocked on a free activation stage it could not run ahead with the weights, and the per-role cycle counters (option
-// conv_dbg) showed the MMA thread waiting 13-19 % of its time for weight slices (67-75 clocks per MMA against ~48).
+// Roles (256 threads, one CTA per SM, persistent over work items = (image, 8-row x 30-column tile)): warp 0 activation
+// (TMA) producer; warps 1 and 7 MMA issuers, one accumulator each - a single thread needs ~65 clocks of its own
+// instruction stream per tcgen05.mma here, more than the pipe needs for the MMA (measured with the MMAs switched off,
+// tools/rconv_probe.py); warps 2-5 epilogue (TMEM lane quarter = warp & 3); warp 6 loads the layer's weights, which always
+// fit (<= 3 chunks x 3 vertical taps x 12 KB) and stay resident: once per CTA, waited for during the first item only (even
+// an already-complete mbarrier wait costs ~100 clocks of the issuing thread).  Two TMEM slots of two accumulators: the
+// epilogue of item k overlaps the MMAs of item k+1.
 #pragma once
 
 #include <cuda_fp16.h>
@@ -45,34 +49,37 @@ constexpr int PITCH = 32;
 constexpr int TILE_W = 30;
 constexpr int KC = 64;
 constexpr int SA = 2;
-constexpr int NTHREADS = 256;    // warp 0 TMA (activations), warps 1 and 7 MMA (one accumulator each), warps 2-5 epilogue (TMEM lane quarter = warp & 3), warp 6 weights
+constexpr int NTHREADS = 256;
 constexpr int APS = 2;           // accumulators (128 pixels each) per work item
 constexpr int ROWS = APS * 4;
+constexpr int CO = 32;           // output channels per launch
+constexpr int NB = 3 * CO;       // MMA N: the three horizontal taps of CO channels side by side
+constexpr int ACC_COLS = 128;    // TMEM columns reserved per accumulator (NB used)
 constexpr int MAXB = 16;         // images of different valid sizes per launch (canvas batching)
+constexpr int MAX_NC = 3;        // 64-channel chunks of the widest input (192)
 
 // work items of a vh x vw image on an H x W canvas: the valid part and, where the canvas has room, one more row / column
 // (stored as zeros: the conv padding of the next layer)
 __host__ __device__ constexpr int items_x(int vw, int W) { return ((vw + 1 < W ? vw + 1 : W) + TILE_W - 1) / TILE_W; }
 __host__ __device__ constexpr int items_y(int vh, int H) { return ((vh + 1 < H ? vh + 1 : H) + ROWS - 1) / ROWS; }
 
-template <int BN>
 struct Cfg {
-  static_assert(BN == 32 || BN == 64, "BN");
   static constexpr int A_STAGE = (ROWS + 2) * PITCH * 128;
-  static constexpr int W_SLICE = BN * 128;              // one (chunk, tap) slice: BN rows x 64 fp16
-  static constexpr int SW = BN == 32 ? 27 : 9;          // slice buffer: a whole Cout = 32 layer / one chunk's worth of taps
+  static constexpr int W_SLICE = NB * 128;              // one (chunk, vertical tap) slice: 96 rows (dx*32 + co) x 64 fp16
+  static constexpr int SW = MAX_NC * 3;                 // every slice of the widest layer
   static constexpr int BAR_OFF = SA * A_STAGE + SW * W_SLICE;
   static constexpr int BIAS_OFF = BAR_OFF + 512;
   static constexpr int STAGE_OFF = BIAS_OFF + 256;
   static constexpr int SMEM = STAGE_OFF + 4 * 2048 + 1024;
-  static constexpr int TMEM_COLS = 2 * APS * BN;        // 128 / 256: a power of two >= 32
+  static constexpr int TMEM_COLS = 2 * APS * ACC_COLS;  // 512
 };
+static_assert(Cfg::SMEM <= 227 * 1024, "shared memory");
 
 struct Params {
-  const uint8_t* wpack;   // [chunk][tap] slices of BN x 128 B, SWIZZLE_128B image, fp16
-  const float* bias;      // [BN]
-  __half* out;            // NHWC [n][H][W][out_cs] (ups2: [n][2H][2W][out_cs]); channels [out_c0, out_c0 + BN) are written
-  const __half* r1;       // optional residual, NHWC with channel stride r1_cs, channels [0, BN):  v = v * a1 + r1
+  const uint8_t* wpack;   // [chunk][dy] slices of NB x 128 B (row dx*32 + co), SWIZZLE_128B image, fp16: this launch's 32 output channels
+  const float* bias;      // [CO]
+  __half* out;            // NHWC [n][H][W][out_cs] (ups2: [n][2H][2W][out_cs]); channels [out_c0, out_c0 + CO) are written
+  const __half* r1;       // optional residual, NHWC with channel stride r1_cs, channels [0, CO):  v = v * a1 + r1
   const __half* r2;       // optional second residual:                                             v = v * a2 + r2
   float a1, a2;
   int out_cs, out_c0, r1_cs, r2_cs;
@@ -91,15 +98,14 @@ struct Params {
   int item0[MAXB + 1];    // first work item of image i; item0[n_tab] = total
   int probe;              // -DVEX_DEBUG_PROBES builds only (wrong pixels, timing experiments): 256 = the activation producer loads the
                           // first SA stages and then only signals; 512 = the epilogue only waits and releases; 2048 = no MMAs
-  int force_ring;         // A/B switch (option rrdb_ring): stream the weights through the slice buffer even when they would fit
   long long* dbg;         // optional [gridDim.x][8] cycle counters (option conv_dbg): MMA thread 0 total, 1 wait acc_empty, 2 wait a_full,
-                          // 3 wait w_full; epilogue warp 2: 4 wait acc_full, 5 work; producer: 6 wait a_empty, 7 wait w_empty
+                          // 3 wait w_full; epilogue warp 2: 4 wait acc_full, 5 work; producer: 6 wait a_empty
 };
 
-// Programmatic dependent launch: the ~350 layer kernels of one pass form a chain on one stream.  A kernel launched with
+// Programmatic dependent launch: the ~420 layer kernels of one pass form a chain on one stream.  A kernel launched with
 // the programmatic-serialisation attribute may start while its predecessor's last CTAs are still running; its prologue
-// (barrier init, TMEM allocation, bias, tensor-map prefetch) then overlaps the predecessor's tail, and `pdl_wait` holds
-// every access to activations until the predecessor has completed and flushed.  `pdl_launch_dependents` lets the
+// (barrier init, TMEM allocation, bias, tensor-map prefetch, weights) then overlaps the predecessor's tail, and `pdl_wait`
+// holds every access to activations until the predecessor has completed and flushed.  `pdl_launch_dependents` lets the
 // successor start as early as possible.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
@@ -136,10 +142,9 @@ __host__ __device__ constexpr uint32_t idesc_f16_f32(int m, int n) {
   return (1u << 4) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
 }
 
-template <int BN>
 __global__ void __launch_bounds__(NTHREADS, 1)
 rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ Params p) {
-  using C = Cfg<BN>;
+  using C = Cfg;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
   const uint32_t sbase = (raw + 1023u) & ~1023u;
@@ -148,10 +153,10 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
   const uint32_t a_stage0 = sbase;
   const uint32_t w_stage0 = sbase + SA * C::A_STAGE;
   const uint32_t bar0 = sbase + C::BAR_OFF;
-  // barrier map (8 B each): a_full[SA] a_empty[SA] w_full[SW] w_empty[SW] acc_full[2] acc_empty[2] | tmem slot
+  // barrier map (8 B each): a_full[SA] a_empty[SA] w_full[SW] acc_full[2] acc_empty[2] | tmem slot
   const uint32_t a_full = bar0, a_empty = bar0 + 8 * SA;
-  const uint32_t w_full = a_empty + 8 * SA, w_empty = w_full + 8 * C::SW;
-  const uint32_t acc_full = w_empty + 8 * C::SW, acc_empty = acc_full + 16;
+  const uint32_t w_full = a_empty + 8 * SA;
+  const uint32_t acc_full = w_full + 8 * C::SW, acc_empty = acc_full + 16;
   const uint32_t tmem_slot = acc_empty + 16;
   volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(sm + C::BAR_OFF + (tmem_slot - bar0));
   float* bias_s = reinterpret_cast<float*>(sm + C::BIAS_OFF);
@@ -162,12 +167,12 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
   if (threadIdx.x == 0) {
     // consumer-side barriers count APS arrivals: each of the two MMA threads commits its own MMAs
     for (int i = 0; i < SA; ++i) { ptx::mbar_init(a_full + 8 * i, 1); ptx::mbar_init(a_empty + 8 * i, APS); }
-    for (int i = 0; i < C::SW; ++i) { ptx::mbar_init(w_full + 8 * i, 1); ptx::mbar_init(w_empty + 8 * i, APS); }
+    for (int i = 0; i < C::SW; ++i) ptx::mbar_init(w_full + 8 * i, 1);
     for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full + 8 * i, APS); ptx::mbar_init(acc_empty + 8 * i, 4); }
     ptx::fence_mbar_init();
     ptx::prefetch_tensormap(&amap);
   }
-  if (threadIdx.x < BN) bias_s[threadIdx.x] = p.bias[threadIdx.x];
+  if (threadIdx.x < CO) bias_s[threadIdx.x] = p.bias[threadIdx.x];
   if (warp == 1) {
     ptx::tmem_alloc(tmem_slot, C::TMEM_COLS);
     ptx::tmem_relinquish();
@@ -176,7 +181,6 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot_p;
-  const bool resident = p.NC * 9 <= C::SW && !p.force_ring;   // every weight slice of the layer fits the slice buffer
   pdl_launch_dependents();                              // the next layer may begin its prologue
 
   if (warp == 0) {
@@ -209,46 +213,27 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
     }
   } else if (warp == 6) {
     // ============================== weight producer ===========================
-    // Weights do not depend on the previous layer: no pdl_wait here, the first slices land while the predecessor drains.
+    // Weights do not depend on the previous layer: no pdl_wait here, the slices land while the predecessor drains.
     if (ptx::elect_one()) {
-      const int nslice = p.NC * 9;
-      if (resident) {
-        for (int i = 0; i < nslice; ++i) {
-          ptx::mbar_expect_tx(w_full + 8 * i, C::W_SLICE);
-          ptx::bulk_load(w_stage0 + i * C::W_SLICE, p.wpack + (size_t)i * C::W_SLICE, C::W_SLICE, w_full + 8 * i);
-        }
-      } else {
-        const bool dbg = p.dbg != nullptr;
-        long long t7 = 0, tq = 0;
-        uint32_t sw = 0, pw = 0;
-        for (int it = blockIdx.x; it < total; it += gridDim.x)
-          for (int i = 0; i < nslice; ++i) {
-            if (dbg) tq = clock64();
-            ptx::mbar_wait(w_empty + 8 * sw, pw ^ 1);
-            if (dbg) t7 += clock64() - tq;
-            ptx::mbar_expect_tx(w_full + 8 * sw, C::W_SLICE);
-            ptx::bulk_load(w_stage0 + sw * C::W_SLICE, p.wpack + (size_t)i * C::W_SLICE, C::W_SLICE, w_full + 8 * sw);
-            if (++sw == C::SW) { sw = 0; pw ^= 1; }
-          }
-        if (dbg) p.dbg[blockIdx.x * 8 + 7] = t7;
+      const int nslice = p.NC * 3;
+      for (int i = 0; i < nslice; ++i) {
+        ptx::mbar_expect_tx(w_full + 8 * i, C::W_SLICE);
+        ptx::bulk_load(w_stage0 + i * C::W_SLICE, p.wpack + (size_t)i * C::W_SLICE, C::W_SLICE, w_full + 8 * i);
       }
     }
   } else if (warp == 1 || warp == 7) {
     // ============================== MMA issuers ===============================
-    // TWO issuing threads, one per accumulator of an item.  A single thread needs ~65 clocks of its own instruction
-    // stream per tcgen05.mma here (descriptor arithmetic, uniform-register moves, branches: measured with the MMAs
-    // themselves switched off, tools/rconv_probe.py) while the tensor pipe can take an N = 32 MMA every 45 clocks
-    // (tools/ubench/mma_rate.cu): with one issuer the kernel was bound by that thread, not by the pipe.
     static_assert(APS == 2, "one MMA warp per accumulator");
     const int a = warp == 1 ? 0 : 1;
     if (ptx::elect_one()) {
-      constexpr uint32_t idesc = idesc_f16_f32(128, BN);
-      uint32_t sa = 0, pa = 0, sw = 0, pw = 0, kk = 0;
+      constexpr uint32_t idesc = idesc_f16_f32(128, NB);
+      uint32_t sa = 0, pa = 0, kk = 0;
       const bool dbg = p.dbg != nullptr && a == 0;
       long long t1 = 0, t2 = 0, t3 = 0, tq = 0;
       const long long tm0 = dbg ? clock64() : 0;
       for (int it = blockIdx.x; it < total; it += gridDim.x, ++kk) {
         const uint32_t slot = kk & 1, pacc = (kk >> 1) & 1;
+        const uint32_t dcol = tmem + (slot * APS + a) * ACC_COLS;
         if (dbg) tq = clock64();
         ptx::mbar_wait(acc_empty + 8 * slot, pacc ^ 1);   // the epilogue has drained this slot (first use passes at once)
         if (dbg) t1 += clock64() - tq;
@@ -257,34 +242,27 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
           if (dbg) tq = clock64();
           ptx::mbar_wait(a_full + 8 * sa, pa);
           if (dbg) t2 += clock64() - tq;
-          const uint32_t abase = a_stage0 + sa * C::A_STAGE;
-          const int ksteps = c == p.NC - 1 ? p.klast : KC / 16;   // the upper half of a 96 / 160-channel input's last chunk is not read
-          for (int t = 0; t < 9; ++t) {
-            if (resident) { sw = c * 9 + t; pw = 0; }   // loaded once: phase 0 of its barrier stays complete
-            if (dbg) tq = clock64();
-            // even an already-complete mbarrier wait costs ~100 clocks of this one issuing thread (measured: 16 % of an item),
-            // so resident slices are waited for during the first item only
-            if (!resident || kk == 0) ptx::mbar_wait(w_full + 8 * sw, pw);
-            if (dbg) t3 += clock64() - tq;
-            ptx::tc_fence_after();
-            const uint32_t tap_off = ((t / 3) * PITCH + (t % 3)) * 128;
-            const uint64_t ad0 = ptx::smem_desc_sw128(abase + tap_off, 0);
-            const uint64_t bd0 = ptx::smem_desc_sw128(w_stage0 + sw * C::W_SLICE, 0);
-            {
+          // accumulator a = tile rows 4a .. 4a+3; vertical tap dy reads tile rows 4a+dy .. 4a+dy+3 (the box starts at y0 - 1)
+          const uint32_t abase = a_stage0 + sa * C::A_STAGE + (4 * a) * PITCH * 128;
+          const int ksteps = c == p.NC - 1 ? p.klast : KC / 16;
 #pragma unroll
-              for (int k = 0; k < KC / 16; ++k) {
-                if (k >= ksteps) break;
-                const uint64_t ad = ptx::desc_advance(ad0, a * (128 * 128) + k * 32);
-                const uint64_t bd = ptx::desc_advance(bd0, k * 32);
-#ifdef VEX_DEBUG_PROBES
-                if (p.probe & 2048) continue;               // no MMAs at all: what the other roles cost on their own
-#endif
-                ptx::mma_bf16_ss(tmem + (slot * APS + a) * BN, ad, bd, idesc, (c | t | k) != 0);
-              }
+          for (int dy = 0; dy < 3; ++dy) {
+            const uint32_t sl = c * 3 + dy;
+            if (kk == 0) {                                // resident weights: phase 0 of the slice's barrier stays complete
+              if (dbg) tq = clock64();
+              ptx::mbar_wait(w_full + 8 * sl, 0);
+              if (dbg) t3 += clock64() - tq;
             }
-            if (!resident) {
-              ptx::tc_commit(w_empty + 8 * sw);
-              if (++sw == C::SW) { sw = 0; pw ^= 1; }
+            ptx::tc_fence_after();
+            const uint64_t ad0 = ptx::smem_desc_sw128(abase + dy * PITCH * 128, 0);
+            const uint64_t bd0 = ptx::smem_desc_sw128(w_stage0 + sl * C::W_SLICE, 0);
+#pragma unroll
+            for (int k = 0; k < KC / 16; ++k) {
+              if (k >= ksteps) break;
+#ifdef VEX_DEBUG_PROBES
+              if (p.probe & 2048) continue;               // no MMAs at all: what the other roles cost on their own
+#endif
+              ptx::mma_bf16_ss(dcol, ptx::desc_advance(ad0, k * 32), ptx::desc_advance(bd0, k * 32), idesc, (c | dy | k) != 0);
             }
           }
           ptx::tc_commit(a_empty + 8 * sa);
@@ -296,13 +274,14 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
     }
   } else {
     // ============================== epilogue ==================================
-    // 4 warps, TMEM lane quarter q = warp & 3 (hardware rule).  A lane owns the pixel of its accumulator row; a unit is
-    // (accumulator a, 32-column group g): 32 fp32 per lane -> bias, LeakyReLU, residuals (fp32) -> 64 bytes of fp16.
-    // Global accesses go through a 2 KB per-warp stage so that one instruction covers 8 pixels x 64 B (lane l <-> pixel
-    // 8i + (l >> 2), 16-byte chunk l & 3).  Stage layout: pixel px at px*64, chunk j at (j ^ ((px >> 1) & 3)) * 16.
+    // 4 warps, TMEM lane quarter q = warp & 3 = tile row 4a + q of accumulator a; lane = tile column (pixel x0 - 1 + lane).
+    // Per accumulator a lane reads its three 32-column groups and finishes the horizontal taps with its neighbours:
+    //   out(lane) = D[lane-1][0:32] + D[lane][32:64] + D[lane+1][64:96]          (lanes 1..30 are outputs)
+    // then bias, LeakyReLU, residuals (fp32) -> 64 bytes of fp16.  Global accesses go through a 2 KB per-warp stage so
+    // that one instruction covers 8 pixels x 64 B (lane l <-> pixel 8i + (l >> 2), 16-byte chunk l & 3).  Stage layout:
+    // pixel px at px*64, chunk j at (j ^ ((px >> 1) & 3)) * 16.
     const int q = warp & 3;
     uint8_t* stage = sm + C::STAGE_OFF + (warp - 2) * 2048;
-    constexpr int GROUPS = BN / 32;
     const uint32_t tq = tmem + ((uint32_t)(q * 32) << 16);
     const int cpx = lane >> 2, cch = lane & 3;
     int own_off[4], co_off[4];
@@ -318,13 +297,14 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++kk) {
       const uint32_t slot = kk & 1, pacc = (kk >> 1) & 1;
       const Item im = decode_item(p, it);
-      const int x0 = im.x0, n = im.n;
-      const int ybase = im.y0 + q;                      // accumulator row m = a*128 + q*32 + lane -> y = ybase + 4a
-      bool pxok[4], pxval[4];                           // inside the canvas (stored) / inside the image (else stored as zero)
+      const int xl = im.x0 - 1, n = im.n;               // x of tile column 0
+      const int ybase = im.y0 + q;                      // accumulator row m = q*32 + lane of accumulator a -> y = ybase + 4a
+      bool pxok[4], pxval[4];                           // an output inside the canvas (stored) / inside the image (else stored as zero)
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        pxok[i] = (8 * i + cpx < TILE_W) && (x0 + 8 * i + cpx < p.W);
-        pxval[i] = x0 + 8 * i + cpx < im.vw;
+        const int px = 8 * i + cpx;
+        pxok[i] = px >= 1 && px <= TILE_W && xl + px < p.W;
+        pxval[i] = xl + px < im.vw;
       }
       const bool dbg = p.dbg != nullptr && warp == 2 && lane == 0;
       const long long te0 = dbg ? clock64() : 0;
@@ -332,37 +312,41 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
       const long long te1 = dbg ? clock64() : 0;
       ptx::tc_fence_after();
 #ifdef VEX_DEBUG_PROBES
-      const int nunits = (p.probe & 512) ? 0 : APS * GROUPS;
+      const int nunits = (p.probe & 512) ? 0 : APS;
 #else
-      constexpr int nunits = APS * GROUPS;
+      constexpr int nunits = APS;
 #endif
 #pragma unroll 1
-      for (int u = 0; u < nunits; ++u) {
-        const int a = u / GROUPS, g = u % GROUPS;
+      for (int a = 0; a < nunits; ++a) {
         const int y = ybase + 4 * a;
         const bool yok = y < p.H, yval = y < im.vh;
-        uint32_t v[32];
-        ptx::tmem_ld_32x32(tq + (slot * APS + a) * BN + g * 32, v);
+        uint32_t v0[32], v1[32], v2[32];
+        const uint32_t dcol = tq + (slot * APS + a) * ACC_COLS;
+        ptx::tmem_ld_32x32(dcol, v0);
+        ptx::tmem_ld_32x32(dcol + CO, v1);
+        ptx::tmem_ld_32x32(dcol + 2 * CO, v2);
         // residual rows in the co-pattern (pixel 8i + cpx, chunk cch), issued before the TMEM wait
         uint4 s1[4], s2[4];
-        const size_t pix0 = ((size_t)n * p.H + y) * p.W + x0 + cpx;
+        const long long pix0 = ((long long)n * p.H + y) * p.W + xl + cpx;
         if (p.r1) {
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            s1[i] = (yval && pxok[i] && pxval[i]) ? __ldg(reinterpret_cast<const uint4*>(p.r1 + (pix0 + 8 * i) * p.r1_cs + g * 32 + cch * 8))
-                                     : make_uint4(0, 0, 0, 0);
+            s1[i] = (yval && pxok[i] && pxval[i]) ? __ldg(reinterpret_cast<const uint4*>(p.r1 + (pix0 + 8 * i) * p.r1_cs + cch * 8))
+                                                  : make_uint4(0, 0, 0, 0);
         }
         if (p.r2) {
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            s2[i] = (yval && pxok[i] && pxval[i]) ? __ldg(reinterpret_cast<const uint4*>(p.r2 + (pix0 + 8 * i) * p.r2_cs + g * 32 + cch * 8))
-                                     : make_uint4(0, 0, 0, 0);
+            s2[i] = (yval && pxok[i] && pxval[i]) ? __ldg(reinterpret_cast<const uint4*>(p.r2 + (pix0 + 8 * i) * p.r2_cs + cch * 8))
+                                                  : make_uint4(0, 0, 0, 0);
         }
         ptx::tmem_ld_wait();
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-          float t = __uint_as_float(v[j]) + bias_s[g * 32 + j];
+          const float left = __shfl_up_sync(0xffffffffu, __uint_as_float(v0[j]), 1);      // D[lane-1][j]       (tap dx = 0)
+          const float right = __shfl_down_sync(0xffffffffu, __uint_as_float(v2[j]), 1);   // D[lane+1][64 + j]  (tap dx = 2)
+          float t = (left + __uint_as_float(v1[j])) + right + bias_s[j];
           if (p.lrelu) t = t > 0.f ? t : 0.2f * t;        // nn.LeakyReLU(negative_slope=0.2)
           f[j] = t;
         }
@@ -411,14 +395,14 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
           uint4 o = *reinterpret_cast<const uint4*>(stage + co_off[i]);
           if (!(yok && pxok[i])) continue;
           if (!(yval && pxval[i])) o = make_uint4(0, 0, 0, 0);
-          const int x = x0 + 8 * i + cpx;
+          const int x = xl + 8 * i + cpx;
           if (!p.ups2) {
-            *reinterpret_cast<uint4*>(p.out + (((size_t)n * oh + y) * ow + x) * p.out_cs + p.out_c0 + g * 32 + cch * 8) = o;
+            *reinterpret_cast<uint4*>(p.out + (((size_t)n * oh + y) * ow + x) * p.out_cs + p.out_c0 + cch * 8) = o;
           } else {
 #pragma unroll
             for (int d = 0; d < 4; ++d)
               *reinterpret_cast<uint4*>(p.out + (((size_t)n * oh + 2 * y + (d >> 1)) * ow + 2 * x + (d & 1)) * p.out_cs +
-                                        p.out_c0 + g * 32 + cch * 8) = o;
+                                        p.out_c0 + cch * 8) = o;
           }
         }
         __syncwarp();

@@ -481,7 +481,6 @@ int vex_set_option(vex_ctx* ctx, const char* name, int value) {
   else if (!strcmp(name, "nvtx")) slot = &ctx->opt_nvtx;
   else if (!strcmp(name, "conv1_variant")) slot = &ctx->opt_conv1_variant;
   else if (!strcmp(name, "pdl")) slot = &ctx->opt_pdl;
-  else if (!strcmp(name, "rrdb_ring")) slot = &ctx->opt_rrdb_ring;
   else if (!strcmp(name, "rrdb_batch")) slot = &ctx->opt_rrdb_batch;
   if (!slot) return vex::fail(ctx, VEX_ERR_INVALID, std::string("vex_set_option: unknown ") + name);
 #ifndef VEX_DEBUG_PROBES

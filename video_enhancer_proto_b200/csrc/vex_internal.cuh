@@ -78,7 +78,6 @@ struct vex_ctx {
   int opt_profile = 0;            // record per-layer events in cnn_forward (vex_cnn_profile_ms / vex_cnn_profile_stats)
   int opt_nvtx = 0;               // one NVTX range per layer launch
   int opt_rrdb_batch = 1;         // Real-ESRGAN tile loop: tiles of a frame as one batch of canvases (1) or one after the other (0)
-  int opt_rrdb_ring = 0;          // A/B: RRDB conv weights always streamed through the ring (1) instead of resident when they fit
   int opt_pdl = 1;                // RRDB layer chain: programmatic dependent launch (a layer's prologue overlaps its predecessor's tail)
   int opt_conv1_variant = 0;      // 0 = fp16 offset-1024 operand builder (MODE_CONV1_H), 1 = bf16 builder with I2F conversions
   int opt_ws_budget_mb = 49152;   // CNN activation workspace cap; larger batches run in sub-batches

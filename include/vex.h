@@ -265,8 +265,8 @@ int vex_kernel_launches(const vex_ctx* ctx, unsigned long long* out);
  *   product:   "profile" (0/1: per-layer events; setting 1 clears the statistics of vex_cnn_profile_stats), "nvtx" (0/1:
  *              one NVTX range per layer launch), "ws_budget_mb" (activation workspace cap; larger
  *              batches run as sub-batches), "conv3_bn" (128/256: Cout block of conv3), "pdl" (0/1: programmatic dependent launch of the
- *              Real-ESRGAN layer chain), "rrdb_batch" (1 = the tiles of a Real-ESRGAN frame run as one batch of canvases,
- *              0 = one after the other as in realesrgan_handler.py:342-370; bit-identical).
+ *              Real-ESRGAN layer chain), "rrdb_batch" (how many tiles of a Real-ESRGAN frame run as one batch of canvases;
+ *              1 = one after the other as in realesrgan_handler.py:342-370; bit-identical for every value).
  *   variants kept as bit-identity cross-checks (tests/test_cnn_gpu.py): "conv_variant" (0 = default v3 cta_group::2,
  *              1 = single-CTA, 2 = multicast pairs), "conv1_variant" (0 = fp16 offset-1024 operand builder, 1 = bf16 builder), "thin_tc" (0 = fp32 CUDA-core thin layers), "fuse_tail" (0 = upconv1 /
  *              upconv2 as two kernels with `up` in HBM, 3 = fused with `up` kept in tensor memory), "force_generic_bicubic", "force_generic_resize", "bicubic_rows".

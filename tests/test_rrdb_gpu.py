@@ -145,15 +145,18 @@ def test_batched_tile_loop_equals_the_sequential_one(scale, h, w, tile, pad, bud
         n0 = hd.kernel_launches()
         batched = hd._tile_process(img).copy()
         n_batched = hd.kernel_launches() - n0
-        assert hd.set_option("rrdb_batch", 0) == 1
+        prev = hd.set_option("rrdb_batch", 1)                              # one tile after the other
+        assert prev > 1
         n0 = hd.kernel_launches()
         sequential = hd._tile_process(img).copy()
         n_seq = hd.kernel_launches() - n0
         assert np.array_equal(batched, sequential)
         assert n_batched < n_seq                                           # it really was batched
         assert int(batched.max()) - int(batched.min()) > 100
-        hd.set_option("rrdb_batch", 1)
-        assert np.array_equal(hd._tile_process(img), batched)              # and again, over the stale workspace
+        hd.set_option("rrdb_batch", 3)                                     # batches of three, over the stale workspace
+        assert np.array_equal(hd._tile_process(img), batched)
+        hd.set_option("rrdb_batch", prev)
+        assert np.array_equal(hd._tile_process(img), batched)
     finally:
         hd.close()
 

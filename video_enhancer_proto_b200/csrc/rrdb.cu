@@ -46,6 +46,7 @@ struct RrdbPlan {
   size_t tile_in_bytes = 0, tile_out_bytes = 0;
   // canvas batching: valid (h, w) of every image of the forward that is being enqueued (empty = all images fill the canvas)
   std::vector<int> canvas_dims;
+  unsigned launch_parity = 0;             // alternates the sweep direction of consecutive conv launches (Params::reverse)
   int canvas_h0 = 0;                      // the canvas height at the network's input resolution (layers at 2x / 4x scale the table)
 };
 
@@ -139,7 +140,7 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, int blk, const __half* in, int in
   if (rc) return rc;
   const unsigned abit = 1u;
   if (!(P->attr_mask & abit)) {
-    VEX_CUDA(ctx, cudaFuncSetAttribute(rrdb::rconv3x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+    VEX_CUDA(ctx, cudaFuncSetAttribute(rrdb::rconv3x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_MAX));
     P->attr_mask |= abit;
   }
   rrdb::Params p;
@@ -149,12 +150,15 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, int blk, const __half* in, int in
   p.r2 = e.r2 ? e.r2 + blk * rrdb::CO : nullptr; p.r2_cs = e.r2_cs; p.a2 = e.a2;
   p.lrelu = e.lrelu; p.ups2 = e.ups2;
   p.H = H; p.W = W; p.NC = L.nc;
+  p.sa = C::stages(L.nc * 3);                           // what the layer's weights leave of the 227 KB
+  if (ctx->opt_rrdb_stages >= 2 && ctx->opt_rrdb_stages < p.sa) p.sa = ctx->opt_rrdb_stages;   // A/B against fewer
   p.klast = L.cin % 64 == 32 ? 2 : 4;
   p.tiles_x = (W + rrdb::TILE_W - 1) / rrdb::TILE_W;
   p.tiles_y = (H + rrdb::ROWS - 1) / rrdb::ROWS;
   p.n_img = n;
   p.dbg = nullptr;
   p.probe = ctx->opt_thin_probe;
+  p.reverse = ctx->opt_rrdb_zigzag ? (int)(P->launch_parity++ & 1u) : 0;
   long long total = (long long)p.tiles_x * p.tiles_y * n;
   p.n_tab = 0;
   memset(p.vh, 0, sizeof(p.vh)); memset(p.vw, 0, sizeof(p.vw)); memset(p.item0, 0, sizeof(p.item0));
@@ -182,7 +186,7 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, int blk, const __half* in, int in
   attr[0].val.programmaticStreamSerializationAllowed = ctx->opt_pdl ? 1 : 0;
   cfg.gridDim = dim3((unsigned)std::min<long long>(total, ctx->sm_count));
   cfg.blockDim = dim3(rrdb::NTHREADS);
-  cfg.dynamicSmemBytes = C::SMEM;
+  cfg.dynamicSmemBytes = (size_t)C::smem(p.sa, L.nc * 3);
   cfg.stream = s;
   cfg.attrs = attr; cfg.numAttrs = 1;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -519,7 +523,7 @@ int rrdb_frame(vex_ctx* ctx, const uint8_t* in, uint8_t* out, int h, int w, int 
     }
   const size_t per_px = ws_layout(P->arch, 1 << 20).total >> 20;            // workspace bytes per input pixel
   const size_t budget_px = std::max<size_t>(((size_t)ctx->opt_ws_budget_mb << 20) / std::max<size_t>(per_px, 1), 1);
-  const int max_batch = ctx->opt_rrdb_batch ? rrdb::MAXB : 1;
+  const int max_batch = std::min(std::max(ctx->opt_rrdb_batch, 1), rrdb::MAXB);
 
   size_t first = 0;
   while (first < tiles.size()) {

@@ -29,10 +29,11 @@
 // each, measured) instead of 9 of N = 32 (45 each): 168 clocks instead of 402.  30 of the 32 columns are valid outputs.
 // Cin is consumed in 64-channel chunks; Cin = 96 / 160 issue only the two K = 16 steps of their last chunk that exist.
 //
-// Roles (256 threads, one CTA per SM, persistent over work items = (image, 8-row x 30-column tile)): warp 0 activation
+// Roles (384 threads, one CTA per SM, persistent over work items = (image, 8-row x 30-column tile)): warp 0 activation
 // (TMA) producer; warps 1 and 7 MMA issuers, one accumulator each - a single thread needs ~65 clocks of its own
 // instruction stream per tcgen05.mma here, more than the pipe needs for the MMA (measured with the MMAs switched off,
-// tools/rconv_probe.py); warps 2-5 epilogue (TMEM lane quarter = warp & 3); warp 6 loads the layer's weights, which always
+// tools/rconv_probe.py); warps 2-5 and 8-11 epilogue, one accumulator per group of four (TMEM lane quarter = warp & 3);
+// warp 6 loads the layer's weights, which always
 // fit (<= 3 chunks x 3 vertical taps x 12 KB) and stay resident: once per CTA, waited for during the first item only (even
 // an already-complete mbarrier wait costs ~100 clocks of the issuing thread).  Two TMEM slots of two accumulators: the
 // epilogue of item k overlaps the MMAs of item k+1.
@@ -48,8 +49,8 @@ namespace rrdb {
 constexpr int PITCH = 32;
 constexpr int TILE_W = 30;
 constexpr int KC = 64;
-constexpr int SA = 2;
-constexpr int NTHREADS = 256;
+constexpr int SA_MAX = 4;        // activation stages: as many as fit beside the layer's weights (Params::sa), 2..4
+constexpr int NTHREADS = 384;
 constexpr int APS = 2;           // accumulators (128 pixels each) per work item
 constexpr int ROWS = APS * 4;
 constexpr int CO = 32;           // output channels per launch
@@ -67,13 +68,20 @@ struct Cfg {
   static constexpr int A_STAGE = (ROWS + 2) * PITCH * 128;
   static constexpr int W_SLICE = NB * 128;              // one (chunk, vertical tap) slice: 96 rows (dx*32 + co) x 64 fp16
   static constexpr int SW = MAX_NC * 3;                 // every slice of the widest layer
-  static constexpr int BAR_OFF = SA * A_STAGE + SW * W_SLICE;
-  static constexpr int BIAS_OFF = BAR_OFF + 512;
-  static constexpr int STAGE_OFF = BIAS_OFF + 256;
-  static constexpr int SMEM = STAGE_OFF + 4 * 2048 + 1024;
+  static constexpr int BAR_BYTES = 512;                 // a_full/a_empty[SA_MAX], w_full[SW], acc_full/acc_empty[2], TMEM slot
+  static constexpr int TAIL_BYTES = BAR_BYTES + 256 + 8 * 2048;   // barriers, bias, the 8 epilogue warps' transpose stages
+  static constexpr int SMEM_MAX = 227 * 1024;
   static constexpr int TMEM_COLS = 2 * APS * ACC_COLS;  // 512
+  // shared memory of a launch: [sa activation stages][NC*3 weight slices][barriers][bias][stages], + 1 KB for the 1024-byte
+  // alignment of the base.  More activation stages = more bytes in flight per SM: a layer's input comes from HBM (796 MB
+  // per dense buffer at 1080p) and since the MMAs got 2.4x shorter the loads are what the wide layers wait for.
+  __host__ __device__ static constexpr int stages(int nslice) {
+    const int room = (SMEM_MAX - 1024 - TAIL_BYTES - nslice * W_SLICE) / A_STAGE;
+    return room > SA_MAX ? SA_MAX : room;
+  }
+  __host__ __device__ static constexpr int smem(int sa, int nslice) { return 1024 + sa * A_STAGE + nslice * W_SLICE + TAIL_BYTES; }
 };
-static_assert(Cfg::SMEM <= 227 * 1024, "shared memory");
+static_assert(Cfg::stages(Cfg::SW) >= 2, "shared memory");
 
 struct Params {
   const uint8_t* wpack;   // [chunk][dy] slices of NB x 128 B (row dx*32 + co), SWIZZLE_128B image, fp16: this launch's 32 output channels
@@ -85,9 +93,12 @@ struct Params {
   int out_cs, out_c0, r1_cs, r2_cs;
   int lrelu;              // LeakyReLU(0.2) after the bias
   int ups2;               // store every pixel to the 2 x 2 block of a twice as large output (nearest-neighbour upsample)
+  int sa;                 // activation stages of this launch (Cfg::stages(NC * 3), or fewer: option rrdb_stages)
   int H, W, NC;           // NC = 64-channel chunks of the input that are read
   int klast;              // K = 16 steps of the LAST chunk: 2 when Cin % 64 == 32 (conv2 / conv4 of a dense block), else 4
   int tiles_x, tiles_y, n_img;
+  int reverse;            // sweep the work items from the last to the first: consecutive layers alternate, so a layer starts on the
+                          // ~100 MB its predecessor touched last, which are still in L2 (a dense buffer is 0.8 GB at 1080p)
   // Canvas batching (the tile loop of `_tile_process`, realesrgan_handler.py:324-372, in ONE launch per layer): the n_tab
   // images of the batch share the H x W canvas but image i is only vh[i] x vw[i] large, anchored at (0, 0).  Work items
   // cover the valid part plus one more row / column, and every store outside the valid part writes ZERO, so the next
@@ -122,8 +133,9 @@ __device__ __forceinline__ float2 unpack_f16x2(uint32_t w) {
 struct Item { int n, x0, y0, vh, vw; };
 // work item -> image, tile origin and the image's valid size
 template <class P>
-__device__ __forceinline__ Item decode_item(const P& p, int it) {
+__device__ __forceinline__ Item decode_item(const P& p, int total, int it) {
   Item r;
+  if (p.reverse) it = total - 1 - it;
   if (p.n_tab == 0) {
     const int q = it / p.tiles_x;
     r.n = q / p.tiles_y; r.x0 = (it % p.tiles_x) * TILE_W; r.y0 = (q % p.tiles_y) * ROWS; r.vh = p.H; r.vw = p.W;
@@ -150,25 +162,28 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
   const uint32_t sbase = (raw + 1023u) & ~1023u;
   uint8_t* sm = smem_raw + (sbase - raw);
 
+  const uint32_t SA = (uint32_t)p.sa;
   const uint32_t a_stage0 = sbase;
   const uint32_t w_stage0 = sbase + SA * C::A_STAGE;
-  const uint32_t bar0 = sbase + C::BAR_OFF;
-  // barrier map (8 B each): a_full[SA] a_empty[SA] w_full[SW] acc_full[2] acc_empty[2] | tmem slot
-  const uint32_t a_full = bar0, a_empty = bar0 + 8 * SA;
-  const uint32_t w_full = a_empty + 8 * SA;
+  const uint32_t bar_off = SA * C::A_STAGE + (uint32_t)p.NC * 3 * C::W_SLICE;
+  const uint32_t bar0 = sbase + bar_off;
+  // barrier map (8 B each): a_full[SA_MAX] a_empty[SA_MAX] w_full[SW] acc_full[2] acc_empty[2] | tmem slot
+  const uint32_t a_full = bar0, a_empty = bar0 + 8 * SA_MAX;
+  const uint32_t w_full = a_empty + 8 * SA_MAX;
   const uint32_t acc_full = w_full + 8 * C::SW, acc_empty = acc_full + 16;
   const uint32_t tmem_slot = acc_empty + 16;
-  volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(sm + C::BAR_OFF + (tmem_slot - bar0));
-  float* bias_s = reinterpret_cast<float*>(sm + C::BIAS_OFF);
+  static_assert(16 * SA_MAX + 8 * C::SW + 32 + 8 <= C::BAR_BYTES, "barrier block");
+  volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(sm + bar_off + (tmem_slot - bar0));
+  float* bias_s = reinterpret_cast<float*>(sm + bar_off + C::BAR_BYTES);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total = p.n_tab ? p.item0[p.n_tab] : p.tiles_x * p.tiles_y * p.n_img;
 
   if (threadIdx.x == 0) {
     // consumer-side barriers count APS arrivals: each of the two MMA threads commits its own MMAs
-    for (int i = 0; i < SA; ++i) { ptx::mbar_init(a_full + 8 * i, 1); ptx::mbar_init(a_empty + 8 * i, APS); }
+    for (int i = 0; i < SA_MAX; ++i) { ptx::mbar_init(a_full + 8 * i, 1); ptx::mbar_init(a_empty + 8 * i, APS); }
     for (int i = 0; i < C::SW; ++i) ptx::mbar_init(w_full + 8 * i, 1);
-    for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full + 8 * i, APS); ptx::mbar_init(acc_empty + 8 * i, 4); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full + 8 * i, APS); ptx::mbar_init(acc_empty + 8 * i, 8); }
     ptx::fence_mbar_init();
     ptx::prefetch_tensormap(&amap);
   }
@@ -194,7 +209,7 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
 #endif
       pdl_wait();                                       // activations of the previous layer
       for (int it = blockIdx.x; it < total; it += gridDim.x) {
-        const Item im = decode_item(p, it);
+        const Item im = decode_item(p, total, it);
         const int x0 = im.x0, y0 = im.y0, n = im.n;
         for (int c = 0; c < p.NC; ++c) {
           if (dbg) tq = clock64();
@@ -274,14 +289,16 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
     }
   } else {
     // ============================== epilogue ==================================
-    // 4 warps, TMEM lane quarter q = warp & 3 = tile row 4a + q of accumulator a; lane = tile column (pixel x0 - 1 + lane).
-    // Per accumulator a lane reads its three 32-column groups and finishes the horizontal taps with its neighbours:
+    // 8 warps: warps 2-5 drain accumulator 0, warps 8-11 accumulator 1 (since the MMAs got 2.4x shorter, four warps were
+    // what the 64-channel-input layers and the heads waited for).  TMEM lane quarter q = warp & 3 = tile row 4a + q of
+    // accumulator a; lane = tile column (pixel x0 - 1 + lane).
+    // A lane reads its three 32-column groups and finishes the horizontal taps with its neighbours:
     //   out(lane) = D[lane-1][0:32] + D[lane][32:64] + D[lane+1][64:96]          (lanes 1..30 are outputs)
     // then bias, LeakyReLU, residuals (fp32) -> 64 bytes of fp16.  Global accesses go through a 2 KB per-warp stage so
     // that one instruction covers 8 pixels x 64 B (lane l <-> pixel 8i + (l >> 2), 16-byte chunk l & 3).  Stage layout:
     // pixel px at px*64, chunk j at (j ^ ((px >> 1) & 3)) * 16.
-    const int q = warp & 3;
-    uint8_t* stage = sm + C::STAGE_OFF + (warp - 2) * 2048;
+    const int q = warp & 3, a = warp >= 8 ? 1 : 0;
+    uint8_t* stage = sm + bar_off + C::BAR_BYTES + 256 + (warp >= 8 ? warp - 4 : warp - 2) * 2048;
     const uint32_t tq = tmem + ((uint32_t)(q * 32) << 16);
     const int cpx = lane >> 2, cch = lane & 3;
     int own_off[4], co_off[4];
@@ -296,7 +313,7 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
     pdl_wait();                                         // residuals are read and the output buffer is written below
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++kk) {
       const uint32_t slot = kk & 1, pacc = (kk >> 1) & 1;
-      const Item im = decode_item(p, it);
+      const Item im = decode_item(p, total, it);
       const int xl = im.x0 - 1, n = im.n;               // x of tile column 0
       const int ybase = im.y0 + q;                      // accumulator row m = q*32 + lane of accumulator a -> y = ybase + 4a
       bool pxok[4], pxval[4];                           // an output inside the canvas (stored) / inside the image (else stored as zero)
@@ -312,12 +329,12 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
       const long long te1 = dbg ? clock64() : 0;
       ptx::tc_fence_after();
 #ifdef VEX_DEBUG_PROBES
-      const int nunits = (p.probe & 512) ? 0 : APS;
+      const int nunits = (p.probe & 512) ? 0 : 1;
 #else
-      constexpr int nunits = APS;
+      constexpr int nunits = 1;
 #endif
 #pragma unroll 1
-      for (int a = 0; a < nunits; ++a) {
+      for (int u = 0; u < nunits; ++u) {
         const int y = ybase + 4 * a;
         const bool yok = y < p.H, yval = y < im.vh;
         uint32_t v0[32], v1[32], v2[32];
@@ -344,8 +361,14 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
+#ifdef VEX_DEBUG_PROBES
+          const bool noshfl = p.probe & 4096;
+          const float left = noshfl ? __uint_as_float(v0[j]) : __shfl_up_sync(0xffffffffu, __uint_as_float(v0[j]), 1);
+          const float right = noshfl ? __uint_as_float(v2[j]) : __shfl_down_sync(0xffffffffu, __uint_as_float(v2[j]), 1);
+#else
           const float left = __shfl_up_sync(0xffffffffu, __uint_as_float(v0[j]), 1);      // D[lane-1][j]       (tap dx = 0)
           const float right = __shfl_down_sync(0xffffffffu, __uint_as_float(v2[j]), 1);   // D[lane+1][64 + j]  (tap dx = 2)
+#endif
           float t = (left + __uint_as_float(v1[j])) + right + bias_s[j];
           if (p.lrelu) t = t > 0.f ? t : 0.2f * t;        // nn.LeakyReLU(negative_slope=0.2)
           f[j] = t;
@@ -393,6 +416,9 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           uint4 o = *reinterpret_cast<const uint4*>(stage + co_off[i]);
+#ifdef VEX_DEBUG_PROBES
+          if (p.probe & 8192) continue;                   // no global stores
+#endif
           if (!(yok && pxok[i])) continue;
           if (!(yval && pxval[i])) o = make_uint4(0, 0, 0, 0);
           const int x = xl + 8 * i + cpx;

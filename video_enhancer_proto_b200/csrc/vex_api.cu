@@ -482,6 +482,8 @@ int vex_set_option(vex_ctx* ctx, const char* name, int value) {
   else if (!strcmp(name, "conv1_variant")) slot = &ctx->opt_conv1_variant;
   else if (!strcmp(name, "pdl")) slot = &ctx->opt_pdl;
   else if (!strcmp(name, "rrdb_batch")) slot = &ctx->opt_rrdb_batch;
+  else if (!strcmp(name, "rrdb_zigzag")) slot = &ctx->opt_rrdb_zigzag;
+  else if (!strcmp(name, "rrdb_stages")) slot = &ctx->opt_rrdb_stages;
   if (!slot) return vex::fail(ctx, VEX_ERR_INVALID, std::string("vex_set_option: unknown ") + name);
 #ifndef VEX_DEBUG_PROBES
   // timing probes that skip work and therefore produce wrong pixels exist only in -DVEX_DEBUG_PROBES builds

@@ -77,7 +77,9 @@ struct vex_ctx {
   int opt_conv_dbg = 0;           // bring-up: print per-role cycle counters of every conv_tc launch (synchronises)
   int opt_profile = 0;            // record per-layer events in cnn_forward (vex_cnn_profile_ms / vex_cnn_profile_stats)
   int opt_nvtx = 0;               // one NVTX range per layer launch
-  int opt_rrdb_batch = 1;         // Real-ESRGAN tile loop: tiles of a frame as one batch of canvases (1) or one after the other (0)
+  int opt_rrdb_stages = 0;        // A/B: cap on the activation stages of the RRDB conv kernel (0 = as many as fit, up to 4)
+  int opt_rrdb_zigzag = 1;        // RRDB conv launches alternate their sweep direction (L2 reuse between consecutive layers); 0 = A/B
+  int opt_rrdb_batch = 16;        // Real-ESRGAN tile loop: most tiles of a frame that run as one batch of canvases (1 = one after the other)
   int opt_pdl = 1;                // RRDB layer chain: programmatic dependent launch (a layer's prologue overlaps its predecessor's tail)
   int opt_conv1_variant = 0;      // 0 = fp16 offset-1024 operand builder (MODE_CONV1_H), 1 = bf16 builder with I2F conversions
   int opt_ws_budget_mb = 49152;   // CNN activation workspace cap; larger batches run in sub-batches

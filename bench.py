@@ -775,15 +775,15 @@ def gpu_rrdb(args, world, rank, local, warmup, peaks, torch, dist, synth):
             "config": {"workload": "Real-ESRGAN RRDBNet 23 blocks x4, 1080p->4320p, tile 512 pad 10 (SURVEY 8(f)4)",
                        "frames_per_step_per_gpu": fps_step, "tiles_per_frame": len(plan), "pixels_per_frame_incl_padding": px,
                        "weights": "random-init (torch default Conv2d init, seed 0)", "flop_per_frame": flop,
-                       "l2": "2.2 GB of activations per tile > 126 MB L2, no flush"},
+                       "l2": "20 GB of activations per frame (12 canvases) > 126 MB L2, no flush"},
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": world * n_e2e / float(dt.item()), "unit": "frames/s", "h2d_bytes_per_step": H * W * 3,
                     "d2h_bytes_per_step": H * W * 3 * 16, "api": "B200RealESRGAN._enhance_frame(ndarray BGR) -> ndarray BGR"},
-            "roofline": {"bound": "tensor", "kernel": "rconv3x3_kernel (345 of the 351 launches per tile)", "achieved": achieved,
+            "roofline": {"bound": "tensor", "kernel": "rconv3x3_kernel (418 of the 424 launches of a pass)", "achieved": achieved,
                          "peak": peaks["bf16_tflops"], "unit": "TFLOP/s", "frac": achieved / peaks["bf16_tflops"],
                          "traffic": None, "peak_source": peaks["source"] + " (burst cuBLAS bf16; fp16 has the same dense rate)",
                          "algorithmic_flop_per_step": flop * fps_step,
-                         "note": "whole pass incl. the 6 thin launches per tile; N = 32 / 64 MMAs are shared-memory bound (DESIGN.md 4)"}}
+                         "note": "whole pass incl. the 6 thin launches; the 12 tiles of a frame run as one batch of canvases; wide layers wait for HBM, narrow ones for the epilogue (DESIGN.md 4)"}}
     if world == 1 and not args.no_cpu_baseline:
         model = R.make_network(0, 4, 23)
         torch.set_num_threads(os.cpu_count() or 1)

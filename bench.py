@@ -759,10 +759,14 @@ def gpu_rrdb(args, world, rank, local, warmup, peaks, torch, dist, synth):
     px = sum((py1 - py0) * (px1 - px0) for (py0, py1, px0, px1, *_r) in plan)       # what the reference's loop computes on
     flop = R.flops_per_input_pixel(4, 23) * px
     achieved = flop * fps_step * steps / (total_ms / 1e3) / 1e12
-    hd._enhance_frame(frames[0])
+    # warm-up keeps two results alive at once, as the loop below does: the second pinned output block is then already in
+    # torch's host allocator cache and its first cudaHostAlloc (tens of ms for 100 MB) stays out of the timed region
+    w1 = hd._enhance_frame(frames[0])
+    w2 = hd._enhance_frame(frames[1 % fps_step])
+    del w1, w2
     barrier()
     t0 = time.perf_counter()
-    n_e2e = max(2, fps_step)
+    n_e2e = max(4, fps_step)
     for i in range(n_e2e):
         out = hd._enhance_frame(frames[i % fps_step])
     dt = torch.tensor([time.perf_counter() - t0], device="cuda")

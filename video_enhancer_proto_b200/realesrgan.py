@@ -251,9 +251,11 @@ class B200RealESRGAN:
         return self._lib.vex_set_option(self._ctx, name.encode(), int(value))
 
     # ------------------------------------------------------------------ RealESRGANHandler frame path
-    def _host_frame(self, frame: np.ndarray, in_bgr: bool, out_bgr: bool, tiled: Optional[bool] = None, slot: int = 0) -> np.ndarray:
+    def _host_frame(self, frame: np.ndarray, in_bgr: bool, out_bgr: bool, tiled: Optional[bool] = None, slot: Optional[int] = 0) -> np.ndarray:
         """One host frame through the GPU: pinned H2D, the (tiled) network, pinned D2H.  Returns a view of the pinned
-        output buffer of `slot` (valid until the next call with that slot)."""
+        output buffer of `slot` (valid until the next call with that slot); `slot=None` returns a FRESH array the caller
+        owns - a pinned block from torch's caching host allocator that the D2H copy lands in directly, instead of a 100 MB
+        host memcpy out of a reused buffer (the array keeps the block alive; freed blocks are reused, not re-pinned)."""
         self._ensure_model_loaded()
         if frame.dtype != np.uint8 or frame.ndim != 3 or frame.shape[2] != 3:
             raise ValueError("frames must be uint8 HWC with 3 channels")
@@ -261,7 +263,8 @@ class B200RealESRGAN:
         s = self.scale
         fin = h * w * 3
         pin_in = self._buf(self._pinned, "in", fin, True)
-        pin_out = self._buf(self._pinned, f"out{slot}", fin * s * s, True)
+        pin_out = (torch.empty(fin * s * s, dtype=torch.uint8, pin_memory=True) if slot is None
+                   else self._buf(self._pinned, f"out{slot}", fin * s * s, True))
         d_in = self._buf(self._dev, "in", fin, False)
         d_out = self._buf(self._dev, "out", fin * s * s, False)
         pin_in.numpy()[:fin] = np.ascontiguousarray(frame).ravel()
@@ -280,11 +283,11 @@ class B200RealESRGAN:
     def _enhance_frame(self, frame: np.ndarray) -> np.ndarray:
         """:286-306: BGR frame in, BGR frame out; tiled when a side exceeds ``tile_size`` (:292).  The two cv2.cvtColor
         calls of the reference are the in_bgr / out_bgr flags of the kernels."""
-        return self._host_frame(frame, True, True, None).copy()
+        return self._host_frame(frame, True, True, None, slot=None)
 
     def _process_single(self, img: np.ndarray) -> np.ndarray:
         """:308-322: RGB image in, RGB out, the whole image in one pass."""
-        return self._host_frame(img, False, False, False).copy()
+        return self._host_frame(img, False, False, False, slot=None)
 
     def _tile_process(self, img: np.ndarray) -> np.ndarray:
         """:324-372: RGB image in, RGB out, tile_size tiles with tile_pad context."""

@@ -135,8 +135,8 @@ struct Epi {
   int lrelu = 0, ups2 = 0;
 };
 
-// one launch = one block of 32 output channels (blk) of the layer
-int launch_rconv(vex_ctx* ctx, const RConv& L, int blk, const __half* in, int in_cs, const Epi& e, int n, int H, int W,
+// one launch per layer; a 64-channel layer carries its two 32-channel halves as interleaved work items (Params::nblk)
+int launch_rconv(vex_ctx* ctx, const RConv& L, const __half* in, int in_cs, const Epi& e, int n, int H, int W,
                  cudaStream_t s) {
   using C = rrdb::Cfg;
   RrdbPlan* P = ctx->rrdb;
@@ -149,10 +149,11 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, int blk, const __half* in, int in
     P->attr_mask |= abit;
   }
   rrdb::Params p;
-  p.wpack = L.wpack + (size_t)blk * L.nc * 3 * C::W_SLICE; p.bias = L.bias + blk * rrdb::CO;
-  p.out = e.out; p.out_cs = e.out_cs; p.out_c0 = e.out_c0 + blk * rrdb::CO;
-  p.r1 = e.r1 ? e.r1 + blk * rrdb::CO : nullptr; p.r1_cs = e.r1_cs; p.a1 = e.a1;
-  p.r2 = e.r2 ? e.r2 + blk * rrdb::CO : nullptr; p.r2_cs = e.r2_cs; p.a2 = e.a2;
+  p.wpack = L.wpack; p.bias = L.bias;
+  p.nblk = L.cout / rrdb::CO;
+  p.out = e.out; p.out_cs = e.out_cs; p.out_c0 = e.out_c0;
+  p.r1 = e.r1; p.r1_cs = e.r1_cs; p.a1 = e.a1;
+  p.r2 = e.r2; p.r2_cs = e.r2_cs; p.a2 = e.a2;
   p.lrelu = e.lrelu; p.ups2 = e.ups2;
   p.H = H; p.W = W; p.NC = L.nc;
   p.sa = C::stages(L.nc * 3);                           // what the layer's weights leave of the 227 KB
@@ -180,6 +181,7 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, int blk, const __half* in, int in
     }
     p.item0[n] = (int)total;
   }
+  total *= p.nblk;                                      // work items = (tile, half)
   if (total > 0x7fffffffLL) return fail(ctx, VEX_ERR_INVALID, "rrdb conv: too many tiles");
   if (ctx->opt_conv_dbg) {
     VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&p.dbg), (size_t)ctx->sm_count * 64));
@@ -189,7 +191,9 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, int blk, const __half* in, int in
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = ctx->opt_pdl ? 1 : 0;
-  cfg.gridDim = dim3((unsigned)std::min<long long>(total, ctx->sm_count));
+  unsigned grid_x = (unsigned)std::min<long long>(total, ctx->sm_count);
+  if (p.nblk == 2) grid_x &= ~1u;                       // even grid: a CTA's parity is the half it works on (total is even)
+  cfg.gridDim = dim3(grid_x);
   cfg.blockDim = dim3(rrdb::NTHREADS);
   cfg.dynamicSmemBytes = (size_t)C::smem(p.sa, L.nc * 3);
   cfg.stream = s;
@@ -214,9 +218,9 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, int blk, const __half* in, int in
       for (int i = 0; i < 8; ++i) a[i] += (double)h[(size_t)b * 8 + i] / grid;
     const double items = (double)total / grid;
     const double mma_clk = ((double)(L.nc - 1) * 4 + p.klast) * 3 * rrdb::APS;   // MMAs (N = 96) per item
-    fprintf(stderr, "[rconv_dbg cin=%d cout=%d blk=%d %dx%d] %.1f us, items/cta=%.2f, cycles/item: MMA total=%.0f (%.1f clk/MMA) wait_acc_empty=%.0f "
+    fprintf(stderr, "[rconv_dbg cin=%d cout=%d nblk=%d %dx%d] %.1f us, items/cta=%.2f, cycles/item: MMA total=%.0f (%.1f clk/MMA) wait_acc_empty=%.0f "
                     "wait_a_full=%.0f wait_w_full=%.0f | epilogue wait_acc_full=%.0f work=%.0f | producer wait_a_empty=%.0f\n",
-            L.cin, L.cout, blk, H, W, ms * 1e3, items, a[0] / items, a[0] / items / mma_clk, a[1] / items, a[2] / items, a[3] / items,
+            L.cin, L.cout, p.nblk, H, W, ms * 1e3, items, a[0] / items, a[0] / items / mma_clk, a[1] / items, a[2] / items, a[3] / items,
             a[4] / items, a[5] / items, a[6] / items);
   }
   return VEX_OK;
@@ -224,11 +228,7 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, int blk, const __half* in, int in
 
 int run_rconv(vex_ctx* ctx, const RConv& L, const __half* in, int in_cs, const Epi& e, int n, int H, int W,
               cudaStream_t s) {
-  for (int blk = 0; blk < L.cout / rrdb::CO; ++blk) {
-    const int rc = launch_rconv(ctx, L, blk, in, in_cs, e, n, H, W, s);
-    if (rc) return rc;
-  }
-  return VEX_OK;
+  return launch_rconv(ctx, L, in, in_cs, e, n, H, W, s);
 }
 
 // fp16 NHWC channel slice -> fp32 NCHW (parity taps).  One thread per (pixel, channel).

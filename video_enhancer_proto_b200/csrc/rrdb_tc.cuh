@@ -97,6 +97,10 @@ struct Params {
   int H, W, NC;           // NC = 64-channel chunks of the input that are read
   int klast;              // K = 16 steps of the LAST chunk: 2 when Cin % 64 == 32 (conv2 / conv4 of a dense block), else 4
   int tiles_x, tiles_y, n_img;
+  int nblk;               // 1, or 2: both 32-channel halves of a 64-channel layer in ONE launch.  Work item it = 2 * tile + half and the
+                          // grid is even, so even CTAs only ever see half 0 and odd CTAs half 1 (each keeps its own half's weights
+                          // resident) while neighbouring CTAs work on the same tile at the same time: the second read of its
+                          // activations hits L2 instead of HBM.  wpack / bias / out_c0 / r1 / r2 advance by one half per blk.
   int reverse;            // sweep the work items from the last to the first: consecutive layers alternate, so a layer starts on the
                           // ~100 MB its predecessor touched last, which are still in L2 (a dense buffer is 0.8 GB at 1080p)
   // Canvas batching (the tile loop of `_tile_process`, realesrgan_handler.py:324-372, in ONE launch per layer): the n_tab
@@ -135,6 +139,7 @@ struct Item { int n, x0, y0, vh, vw; };
 template <class P>
 __device__ __forceinline__ Item decode_item(const P& p, int total, int it) {
   Item r;
+  if (p.nblk == 2) { it >>= 1; total >>= 1; }           // the tile; the half is the CTA's parity
   if (p.reverse) it = total - 1 - it;
   if (p.n_tab == 0) {
     const int q = it / p.tiles_x;
@@ -177,7 +182,8 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
   float* bias_s = reinterpret_cast<float*>(sm + bar_off + C::BAR_BYTES);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int total = p.n_tab ? p.item0[p.n_tab] : p.tiles_x * p.tiles_y * p.n_img;
+  const int total = (p.n_tab ? p.item0[p.n_tab] : p.tiles_x * p.tiles_y * p.n_img) * p.nblk;
+  const int blk = p.nblk == 2 ? (int)(blockIdx.x & 1u) : 0;
 
   if (threadIdx.x == 0) {
     // consumer-side barriers count APS arrivals: each of the two MMA threads commits its own MMAs
@@ -187,7 +193,7 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
     ptx::fence_mbar_init();
     ptx::prefetch_tensormap(&amap);
   }
-  if (threadIdx.x < CO) bias_s[threadIdx.x] = p.bias[threadIdx.x];
+  if (threadIdx.x < CO) bias_s[threadIdx.x] = p.bias[blk * CO + threadIdx.x];
   if (warp == 1) {
     ptx::tmem_alloc(tmem_slot, C::TMEM_COLS);
     ptx::tmem_relinquish();
@@ -233,7 +239,7 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
       const int nslice = p.NC * 3;
       for (int i = 0; i < nslice; ++i) {
         ptx::mbar_expect_tx(w_full + 8 * i, C::W_SLICE);
-        ptx::bulk_load(w_stage0 + i * C::W_SLICE, p.wpack + (size_t)i * C::W_SLICE, C::W_SLICE, w_full + 8 * i);
+        ptx::bulk_load(w_stage0 + i * C::W_SLICE, p.wpack + (size_t)(blk * nslice + i) * C::W_SLICE, C::W_SLICE, w_full + 8 * i);
       }
     }
   } else if (warp == 1 || warp == 7) {
@@ -309,6 +315,9 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
       co_off[j] = px * 64 + ((cch ^ ((px >> 1) & 3)) << 4);
     }
     const int oh = p.ups2 ? 2 * p.H : p.H, ow = p.ups2 ? 2 * p.W : p.W;
+    const int oc0 = p.out_c0 + blk * CO;
+    const __half* r1p = p.r1 ? p.r1 + blk * CO : nullptr;
+    const __half* r2p = p.r2 ? p.r2 + blk * CO : nullptr;
     uint32_t kk = 0;
     pdl_wait();                                         // residuals are read and the output buffer is written below
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++kk) {
@@ -348,13 +357,13 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
         if (p.r1) {
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            s1[i] = (yval && pxok[i] && pxval[i]) ? __ldg(reinterpret_cast<const uint4*>(p.r1 + (pix0 + 8 * i) * p.r1_cs + cch * 8))
+            s1[i] = (yval && pxok[i] && pxval[i]) ? __ldg(reinterpret_cast<const uint4*>(r1p + (pix0 + 8 * i) * p.r1_cs + cch * 8))
                                                   : make_uint4(0, 0, 0, 0);
         }
         if (p.r2) {
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            s2[i] = (yval && pxok[i] && pxval[i]) ? __ldg(reinterpret_cast<const uint4*>(p.r2 + (pix0 + 8 * i) * p.r2_cs + cch * 8))
+            s2[i] = (yval && pxok[i] && pxval[i]) ? __ldg(reinterpret_cast<const uint4*>(r2p + (pix0 + 8 * i) * p.r2_cs + cch * 8))
                                                   : make_uint4(0, 0, 0, 0);
         }
         ptx::tmem_ld_wait();
@@ -423,12 +432,12 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
           if (!(yval && pxval[i])) o = make_uint4(0, 0, 0, 0);
           const int x = xl + 8 * i + cpx;
           if (!p.ups2) {
-            *reinterpret_cast<uint4*>(p.out + (((size_t)n * oh + y) * ow + x) * p.out_cs + p.out_c0 + cch * 8) = o;
+            *reinterpret_cast<uint4*>(p.out + (((size_t)n * oh + y) * ow + x) * p.out_cs + oc0 + cch * 8) = o;
           } else {
 #pragma unroll
             for (int d = 0; d < 4; ++d)
               *reinterpret_cast<uint4*>(p.out + (((size_t)n * oh + 2 * y + (d >> 1)) * ow + 2 * x + (d & 1)) * p.out_cs +
-                                        p.out_c0 + cch * 8) = o;
+                                        oc0 + cch * 8) = o;
           }
         }
         __syncwarp();

@@ -252,6 +252,12 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t use
   if (use_base_offset) hi |= ((saddr >> 7) & 7u) << 17;
   return (static_cast<uint64_t>(hi) << 32) | lo;
 }
+// Same for a K-major tile whose rows are 64 bytes (32 fp16), SWIZZLE_64B: 8 rows x 64 B = 512 B between 8-row groups.
+__device__ __forceinline__ uint64_t smem_desc_sw64(uint32_t saddr) {
+  const uint32_t lo = ((saddr >> 4) & 0x3FFFu) | (1u << 16);
+  const uint32_t hi = (512u >> 4) | (1u << 14) | (4u << 29);
+  return (static_cast<uint64_t>(hi) << 32) | lo;
+}
 // Advance a descriptor's start address by `bytes` (multiple of 16, staying inside the 256 KB window): the address
 // field is the low 14 bits of the low word, so this is one 32-bit add instead of re-encoding the descriptor.  The MMA
 // issue loop is a single thread on the uniform datapath; re-encoding both descriptors per MMA cost ~19 instructions

@@ -112,15 +112,15 @@ int pack_rconv(vex_ctx* ctx, RConv& L, const float* w, const float* b) {
 // 192-channel (384-byte) pixel would otherwise pull the neighbouring 128-byte chunk it never uses into L2 with every
 // request: measured with ncu on the batched 1080p pass, conv1 read 439 MB for 287 MB of input, conv2/3 732 for 574.
 int make_map(vex_ctx* ctx, CUtensorMap* map, const void* base, int n, int H, int W, int cs, int box_rows,
-             bool promo128 = false) {
+             bool promo128 = false, bool half = false) {
   RrdbPlan* P = ctx->rrdb;
   const cuuint64_t dims[4] = {(cuuint64_t)cs, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)n};
   const cuuint64_t strides[3] = {(cuuint64_t)cs * 2, (cuuint64_t)W * cs * 2, (cuuint64_t)H * W * cs * 2};
-  const cuuint32_t box[4] = {64, 32, (cuuint32_t)box_rows, 1};
+  const cuuint32_t box[4] = {half ? 32u : 64u, 32, (cuuint32_t)box_rows, 1};   // half: 32 channels, 64-byte rows
   const cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = reinterpret_cast<EncodeFn>(P->encode)(
       map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
-      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+      CU_TENSOR_MAP_INTERLEAVE_NONE, half ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
       promo128 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B : CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
@@ -143,6 +143,9 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, const __half* in, int in_cs, cons
   CUtensorMap amap;
   int rc = make_map(ctx, &amap, in, n, H, W, in_cs, rrdb::ROWS + 2, L.nc * 64 < in_cs && ctx->opt_rrdb_promo128);
   if (rc) return rc;
+  const bool half_last = L.cin % 64 == 32 && ctx->opt_rrdb_half;
+  CUtensorMap hmap = amap;
+  if (half_last && (rc = make_map(ctx, &hmap, in, n, H, W, in_cs, rrdb::ROWS + 2, true, true))) return rc;
   const unsigned abit = 1u;
   if (!(P->attr_mask & abit)) {
     VEX_CUDA(ctx, cudaFuncSetAttribute(rrdb::rconv3x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_MAX));
@@ -159,6 +162,7 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, const __half* in, int in_cs, cons
   p.sa = C::stages(L.nc * 3);                           // what the layer's weights leave of the 227 KB
   if (ctx->opt_rrdb_stages >= 2 && ctx->opt_rrdb_stages < p.sa) p.sa = ctx->opt_rrdb_stages;   // A/B against fewer
   p.klast = L.cin % 64 == 32 ? 2 : 4;
+  p.half_last = half_last ? 1 : 0;
   p.tiles_x = (W + rrdb::TILE_W - 1) / rrdb::TILE_W;
   p.tiles_y = (H + rrdb::ROWS - 1) / rrdb::ROWS;
   p.n_img = n;
@@ -200,7 +204,7 @@ int launch_rconv(vex_ctx* ctx, const RConv& L, const __half* in, int in_cs, cons
   cfg.attrs = attr; cfg.numAttrs = 1;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (p.dbg) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, s); }
-  VEX_CUDA(ctx, cudaLaunchKernelEx(&cfg, rrdb::rconv3x3_kernel, amap, p));
+  VEX_CUDA(ctx, cudaLaunchKernelEx(&cfg, rrdb::rconv3x3_kernel, amap, hmap, p));
   ctx->launches++;
   VEX_CUDA(ctx, cudaGetLastError());
   if (p.dbg) {

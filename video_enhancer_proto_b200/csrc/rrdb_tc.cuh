@@ -96,6 +96,9 @@ struct Params {
   int sa;                 // activation stages of this launch (Cfg::stages(NC * 3), or fewer: option rrdb_stages)
   int H, W, NC;           // NC = 64-channel chunks of the input that are read
   int klast;              // K = 16 steps of the LAST chunk: 2 when Cin % 64 == 32 (conv2 / conv4 of a dense block), else 4
+  int half_last;          // klast == 2 and the last chunk is loaded through `hmap`: 32 channels per pixel (64-byte rows, SWIZZLE_64B),
+                          // half the bytes of a full chunk - these layers wait for their activations, and the other 32 channels
+                          // of that chunk are the slice this very layer is writing
   int tiles_x, tiles_y, n_img;
   int nblk;               // 1, or 2: both 32-channel halves of a 64-channel layer in ONE launch.  Work item it = 2 * tile + half and the
                           // grid is even, so even CTAs only ever see half 0 and odd CTAs half 1 (each keeps its own half's weights
@@ -160,7 +163,8 @@ __host__ __device__ constexpr uint32_t idesc_f16_f32(int m, int n) {
 }
 
 __global__ void __launch_bounds__(NTHREADS, 1)
-rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ Params p) {
+rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant__ CUtensorMap hmap,
+                const __grid_constant__ Params p) {
   using C = Cfg;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -192,6 +196,7 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
     for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full + 8 * i, APS); ptx::mbar_init(acc_empty + 8 * i, 8); }
     ptx::fence_mbar_init();
     ptx::prefetch_tensormap(&amap);
+    if (p.half_last) ptx::prefetch_tensormap(&hmap);
   }
   if (threadIdx.x < CO) bias_s[threadIdx.x] = p.bias[blk * CO + threadIdx.x];
   if (warp == 1) {
@@ -225,8 +230,13 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
           if ((p.probe & 256) && nload >= SA) { ptx::mbar_arrive(a_full + 8 * sa); if (++sa == SA) { sa = 0; pa ^= 1; } continue; }
           ++nload;
 #endif
-          ptx::mbar_expect_tx(a_full + 8 * sa, C::A_STAGE);
-          ptx::tma_load_4d(a_stage0 + sa * C::A_STAGE, &amap, a_full + 8 * sa, c * KC, x0 - 1, y0 - 1, n);
+          if (p.half_last && c == p.NC - 1) {
+            ptx::mbar_expect_tx(a_full + 8 * sa, C::A_STAGE / 2);
+            ptx::tma_load_4d(a_stage0 + sa * C::A_STAGE, &hmap, a_full + 8 * sa, c * KC, x0 - 1, y0 - 1, n);
+          } else {
+            ptx::mbar_expect_tx(a_full + 8 * sa, C::A_STAGE);
+            ptx::tma_load_4d(a_stage0 + sa * C::A_STAGE, &amap, a_full + 8 * sa, c * KC, x0 - 1, y0 - 1, n);
+          }
           if (++sa == SA) { sa = 0; pa ^= 1; }
         }
       }
@@ -264,7 +274,9 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
           ptx::mbar_wait(a_full + 8 * sa, pa);
           if (dbg) t2 += clock64() - tq;
           // accumulator a = tile rows 4a .. 4a+3; vertical tap dy reads tile rows 4a+dy .. 4a+dy+3 (the box starts at y0 - 1)
-          const uint32_t abase = a_stage0 + sa * C::A_STAGE + (4 * a) * PITCH * 128;
+          const bool half = p.half_last && c == p.NC - 1;     // 64-byte rows
+          const uint32_t rowb = half ? 64u : 128u;
+          const uint32_t abase = a_stage0 + sa * C::A_STAGE + (4 * a) * PITCH * rowb;
           const int ksteps = c == p.NC - 1 ? p.klast : KC / 16;
 #pragma unroll
           for (int dy = 0; dy < 3; ++dy) {
@@ -275,7 +287,7 @@ rconv3x3_kernel(const __grid_constant__ CUtensorMap amap, const __grid_constant_
               if (dbg) t3 += clock64() - tq;
             }
             ptx::tc_fence_after();
-            const uint64_t ad0 = ptx::smem_desc_sw128(abase + dy * PITCH * 128, 0);
+            const uint64_t ad0 = half ? ptx::smem_desc_sw64(abase + dy * PITCH * 64) : ptx::smem_desc_sw128(abase + dy * PITCH * 128, 0);
             const uint64_t bd0 = ptx::smem_desc_sw128(w_stage0 + sl * C::W_SLICE, 0);
 #pragma unroll
             for (int k = 0; k < KC / 16; ++k) {

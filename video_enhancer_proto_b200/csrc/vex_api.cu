@@ -483,6 +483,7 @@ int vex_set_option(vex_ctx* ctx, const char* name, int value) {
   else if (!strcmp(name, "pdl")) slot = &ctx->opt_pdl;
   else if (!strcmp(name, "rrdb_batch")) slot = &ctx->opt_rrdb_batch;
   else if (!strcmp(name, "rrdb_zigzag")) slot = &ctx->opt_rrdb_zigzag;
+  else if (!strcmp(name, "rrdb_half")) slot = &ctx->opt_rrdb_half;
   else if (!strcmp(name, "rrdb_promo128")) slot = &ctx->opt_rrdb_promo128;
   else if (!strcmp(name, "rrdb_stages")) slot = &ctx->opt_rrdb_stages;
   if (!slot) return vex::fail(ctx, VEX_ERR_INVALID, std::string("vex_set_option: unknown ") + name);

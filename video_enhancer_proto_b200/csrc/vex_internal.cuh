@@ -78,6 +78,7 @@ struct vex_ctx {
   int opt_profile = 0;            // record per-layer events in cnn_forward (vex_cnn_profile_ms / vex_cnn_profile_stats)
   int opt_nvtx = 0;               // one NVTX range per layer launch
   int opt_rrdb_stages = 0;        // A/B: cap on the activation stages of the RRDB conv kernel (0 = as many as fit, up to 4)
+  int opt_rrdb_half = 1;          // RRDB conv: the half-filled last chunk of a 96 / 160-channel input is loaded as 32 channels; 0 = A/B
   int opt_rrdb_promo128 = 1;      // RRDB conv layers that read part of a pixel's channels use 128-byte L2 promotion; 0 = A/B
   int opt_rrdb_zigzag = 1;        // RRDB conv launches alternate their sweep direction (L2 reuse between consecutive layers); 0 = A/B
   int opt_rrdb_batch = 16;        // Real-ESRGAN tile loop: most tiles of a frame that run as one batch of canvases (1 = one after the other)

@@ -269,7 +269,8 @@ int vex_kernel_launches(const vex_ctx* ctx, unsigned long long* out);
  *              1 = one after the other as in realesrgan_handler.py:342-370; bit-identical for every value).
  *   variants kept as bit-identity cross-checks (tests/test_cnn_gpu.py): "conv_variant" (0 = default v3 cta_group::2,
  *              1 = single-CTA, 2 = multicast pairs), "conv1_variant" (0 = fp16 offset-1024 operand builder, 1 = bf16 builder), "thin_tc" (0 = fp32 CUDA-core thin layers), "fuse_tail" (0 = upconv1 /
- *              upconv2 as two kernels with `up` in HBM, 3 = fused with `up` kept in tensor memory), "force_generic_bicubic", "force_generic_resize", "bicubic_rows".
+ *              upconv2 as two kernels with `up` in HBM, 3 = fused with `up` kept in tensor memory, 4 = fused with the vertical tap of
+ *              upconv2 accumulated by the tensor core: same products, other fp32 summation order, within 1 LSB of the default), "force_generic_bicubic", "force_generic_resize", "bicubic_rows".
  *   bring-up probes that PRODUCE WRONG RESULTS (timing experiments only; refused unless the library was built with
  *              -DVEX_DEBUG_PROBES): "epi_variant", "thin_probe", "desc_base_offset"; "conv_dbg" prints per-role cycle
  *              counters and synchronises. */

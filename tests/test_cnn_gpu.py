@@ -523,6 +523,29 @@ def test_fused_tail_generations_bit_identical(enhancers, h, w):
         assert np.array_equal(a8, b8), (key, h, w)
 
 
+@pytest.mark.parametrize("h,w", [(1, 1), (2, 3), (3, 15), (4, 16), (37, 53), (130, 70), (45, 16), (360, 480)])
+def test_fused_tail_with_the_vertical_tap_in_the_tensor_core(enhancers, h, w):
+    """option fuse_tail = 4 (csrc/tail_tc3.cuh): the second GEMM accumulates the vertical tap (three row-shifted MMAs of
+    N = 16 per K step) and the epilogue adds the three horizontal taps with lane shuffles; no 27-plane gather.  The products
+    are the default tail's, the order of the fp32 additions is not, so the pre-quantisation output agrees to fp32 rounding
+    and the truncated uint8 to 1 LSB on a handful of bytes - on ragged tiles and image borders too."""
+    rng = np.random.default_rng(56)
+    frames = [synth.random_frame(h, w, rng), synth.edges_frame(h, w, rng), synth.random_frame(h, w, rng)]
+    for key in ("seed0", "stress"):
+        enh = enhancers[key]
+        a8 = enh.upscale_device(dev(frames), mode="cnn", out_bgr=True).cpu().numpy().astype(int)
+        a = enh.cnn_debug_f32(dev(frames), tap=0).cpu().numpy()
+        prev = enh.set_option("fuse_tail", 4)
+        try:
+            b8 = enh.upscale_device(dev(frames), mode="cnn", out_bgr=True).cpu().numpy().astype(int)
+            b = enh.cnn_debug_f32(dev(frames), tap=0).cpu().numpy()
+        finally:
+            enh.set_option("fuse_tail", prev)
+        assert float(np.abs(a - b).max()) <= 4e-6, (key, h, w, float(np.abs(a - b).max()))    # a few fp32 ulps of values <= 1
+        d = np.abs(a8 - b8)
+        assert d.max() <= 1 and float((d > 0).mean()) <= 1e-3, (key, h, w, int(d.max()), float((d > 0).mean()))
+
+
 def test_nvtx_option_and_unknown_option(enhancers):
     """option nvtx: one NVTX range per layer launch; without a profiler attached it must be a no-op
     that changes no pixel.  Unknown option names are errors, not silently ignored."""

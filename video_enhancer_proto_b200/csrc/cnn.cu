@@ -20,6 +20,7 @@
 #include "thin_tc.cuh"
 #include "tail_tc.cuh"
 #include "tail_tc2.cuh"
+#include "tail_tc3.cuh"
 #include "vex_internal.cuh"
 
 namespace vex {
@@ -42,6 +43,7 @@ struct CnnPlan {
   TcLayer extra[VEX_CNN_MAX_EXTRA];          // deepened plans: c3 -> c3 blocks after conv3
   // thin layers on the tensor cores (thin_tc.cuh): SWIZZLE_128B operand images, bf16
   uint8_t *t1w = nullptr, *tu1wb = nullptr, *t5w = nullptr, *tu2w = nullptr;   // t1w / tu1wb carry their bias in k = 27, 28
+  uint8_t* tu2w3 = nullptr;                  // upconv2 for tail_tc3.cuh: [dy] slices of 16 rows (dx*3 + co) x 64 k
   // workspace
   uint8_t* ws = nullptr;
   size_t ws_bytes = 0;
@@ -430,9 +432,12 @@ int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_
                   uint8_t* out_u8, float* out_nchw, int n, int H, int W, int out_bgr, cudaStream_t s) {
   // fuse_tail: 1 = default (relu(upconv1) handed to the second GEMM through shared memory, tail_tc.cuh); 3 = the variant
   // that keeps it in tensor memory (tail_tc2.cuh: bit-identical, 40 % less shared-memory traffic, two issuing threads; it
-  // measures 2007-2022 against 1960 cycles per item - a tie, the tail is bound by warp-instruction issue)
-  const bool v2 = ctx->opt_fuse_tail == 3;
+  // measures 2007-2022 against 1960 cycles per item - a tie); 4 = tail_tc3.cuh (vertical tap of upconv2 in the tensor core,
+  // horizontal tap by lane shuffles, a ring of three half-accumulators for GEMM #1: 1990-2010 cycles per item, a tie again)
+  const bool v2 = ctx->opt_fuse_tail == 3, v3 = ctx->opt_fuse_tail == 4;   // 4: tail_tc3.cuh (vertical tap in the tensor core)
   if (!(ctx->attr_mask & 0x400u)) {
+    VEX_CUDA(ctx, cudaFuncSetAttribute(thin::uptail3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       thin::UT3Cfg::SMEM));
     VEX_CUDA(ctx, cudaFuncSetAttribute(thin::uptail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        thin::UTCfg::SMEM));
     VEX_CUDA(ctx, cudaFuncSetAttribute(thin::uptail2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -466,7 +471,8 @@ int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_
         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(ctx, VEX_ERR_CUDA, "cuTensorMapEncodeTiled (x5) failed (" + std::to_string((int)r) + ")");
   }
-  if (v2) thin::uptail2_kernel<<<grid, thin::UT_THREADS, thin::UT2Cfg::SMEM, s>>>(xmap, p);
+  if (v3) thin::uptail3_kernel<<<grid, thin::UT3_THREADS, thin::UT3Cfg::SMEM, s>>>(xmap, p);
+  else if (v2) thin::uptail2_kernel<<<grid, thin::UT_THREADS, thin::UT2Cfg::SMEM, s>>>(xmap, p);
   else thin::uptail_kernel<<<grid, thin::UT_THREADS, thin::UTCfg::SMEM, s>>>(xmap, p);
   ctx->launches++;
   VEX_CUDA(ctx, cudaGetLastError());
@@ -708,6 +714,14 @@ int cnn_load_weights(vex_ctx* ctx, const vex_cnn_desc* arch, const float* const*
     return u2w[(((size_t)k * 3 + co) * 3 + (2 - ky)) * 3 + (2 - kx)];
   });
   if (rc) return rc;
+  if (up == 64) {   // tail_tc3.cuh: slice dy (the "chunk" of pack_rows_sw128), row dx*3 + co, k = up channel
+    rc = pack_rows_sw128(ctx, &P->tu2w3, 16, 3, [&](int r, int kq) -> float {
+      if (r >= 9) return 0.f;
+      const int dy = kq / 64, k = kq % 64, dx = r / 3, co = r % 3;
+      return u2w[(((size_t)k * 3 + co) * 3 + (2 - dy)) * 3 + (2 - dx)];
+    });
+    if (rc) return rc;
+  }
   return VEX_OK;
 }
 
@@ -836,7 +850,9 @@ static int forward_chunk(vex_ctx* ctx, const uint8_t* in, uint8_t* out_u8, float
   layer("vex.tail");
   if (thin_tc && ctx->opt_fuse_tail && d.up_ch == 64 && !(out_f32 && tap == 6)) {
     // upconv1 + relu + upconv2 + clamp + uint8 in one kernel: `up` never reaches HBM
-    if ((rc = launch_uptail(ctx, x5, P->tu1wb, P->tu2w, P->bu2, out_u8, out_f32, n, H, W, out_bgr, s))) return rc;
+    if ((rc = launch_uptail(ctx, x5, P->tu1wb, ctx->opt_fuse_tail == 4 ? P->tu2w3 : P->tu2w, P->bu2, out_u8, out_f32, n, H, W,
+                            out_bgr, s)))
+      return rc;
     mark();                                  // the fused time is reported in upconv1's slot, upconv2's reads 0
     mark();
     return VEX_OK;
@@ -1069,7 +1085,7 @@ void cnn_destroy(vex_ctx* ctx) {
   CnnPlan* P = ctx->cnn;
   if (!P) return;
   float* fs[] = {P->w1g, P->b1, P->w5g, P->b5, P->wu1, P->bu1, P->wu2, P->bu2};
-  uint8_t* us[] = {P->t1w, P->tu1wb, P->t5w, P->tu2w, P->t1wf, P->t1wh[0], P->t1wh[1]};
+  uint8_t* us[] = {P->t1w, P->tu1wb, P->t5w, P->tu2w, P->tu2w3, P->t1wf, P->t1wh[0], P->t1wh[1]};
   for (uint8_t* u : us)
     if (u) cudaFree(u);
   for (float* f : fs)

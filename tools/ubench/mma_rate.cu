@@ -52,6 +52,11 @@ void run(const char* name) {
   cudaFree(d);
 }
 int main() {
+  run<1, 32, 0>("cta_group::1 M128 N32");
+  run<1, 32, 33>("cta_group::1 M128 N32 A+33 rows");
+  run<1, 64, 0>("cta_group::1 M128 N64");
+  run<1, 64, 33>("cta_group::1 M128 N64 A+33 rows");
+  run<1, 96, 0>("cta_group::1 M128 N96");
   run<1, 128, 0>("cta_group::1 M128 N128");
   run<1, 256, 0>("cta_group::1 M128 N256");
   run<1, 128, 33>("cta_group::1 M128 N128 A+33 rows");

@@ -120,7 +120,7 @@ struct Params {
                           // 3 wait w_full; epilogue warp 2: 4 wait acc_full, 5 work; producer: 6 wait a_empty
 };
 
-// Programmatic dependent launch: the ~420 layer kernels of one pass form a chain on one stream.  A kernel launched with
+// Programmatic dependent launch: the ~350 layer kernels of one pass form a chain on one stream.  A kernel launched with
 // the programmatic-serialisation attribute may start while its predecessor's last CTAs are still running; its prologue
 // (barrier init, TMEM allocation, bias, tensor-map prefetch, weights) then overlaps the predecessor's tail, and `pdl_wait`
 // holds every access to activations until the predecessor has completed and flushed.  `pdl_launch_dependents` lets the

@@ -44,7 +44,16 @@ constexpr int PITCH = 32;     // pixels per smem tile row (30 valid outputs + 2 
 constexpr int TILE_W = 30;
 constexpr int KC = 64;        // channels per K chunk = one 128 B swizzle row
 constexpr int SA = 2;         // activation stages
-constexpr int NTHREADS = 320;    // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
+constexpr int NTHREADS = 352;    // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue, warp 10 second MMA issuer (BN = 128 only)
+constexpr int ISS2_WARP = 10;
+// Two issuing threads when an item has two accumulators (BN = 128: conv2, conv4), one accumulator each.  A single thread
+// spends ~55-65 clocks of its own instruction stream per tcgen05.mma (measured in rrdb_tc.cuh with the MMAs switched off) plus
+// two barrier waits per tap; an N = 128 MMA of a CTA pair takes the pipe 64 clocks, so one issuer was right at the limit
+// (tensor pipe 87.6 % active in conv2, 97 % in conv4) while the N = 256 kernel (128 clocks per MMA) reached 99.9 %.
+// Both issuers wait on the same "full" barriers; the barriers they commit to count one arrival per issuer.
+// This loop's code generation decides the speed of the BN = 128 layers: the same split with run-time accumulator bounds,
+// with the loop instantiated per accumulator in a generic lambda, or with the tap loop unrolled each measured conv4 at
+// 7.8-9 ms instead of 6.1 (tools/conv_iss_ab.py) - change it only with that tool at hand.
 
 template <int BN>
 struct Cfg {
@@ -105,10 +114,11 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
   const uint32_t rank = ptx::cluster_ctarank();
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < SA; ++i) { ptx::mbar_init(a_full + 8 * i, 1); ptx::mbar_init(a_empty + 8 * i, 1); }
-    for (int i = 0; i < C::SW; ++i) { ptx::mbar_init(w_full + 8 * i, 1); ptx::mbar_init(w_empty + 8 * i, 1); ptx::mbar_init(w_peer + 8 * i, 1); }
+    constexpr int NISS = C::APS == 2 ? 2 : 1;           // issuing threads (in the leader CTA; their commits are multicast to both)
+    for (int i = 0; i < SA; ++i) { ptx::mbar_init(a_full + 8 * i, 1); ptx::mbar_init(a_empty + 8 * i, NISS); }
+    for (int i = 0; i < C::SW; ++i) { ptx::mbar_init(w_full + 8 * i, 1); ptx::mbar_init(w_empty + 8 * i, NISS); ptx::mbar_init(w_peer + 8 * i, 1); }
     for (int i = 0; i < SA; ++i) ptx::mbar_init(a_peer + 8 * i, 1);
-    for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full + 8 * i, 1); ptx::mbar_init(acc_empty + 8 * i, 16); }   // 8 + 8 epilogue warps of the pair
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full + 8 * i, NISS); ptx::mbar_init(acc_empty + 8 * i, 16); }   // 8 + 8 epilogue warps of the pair
     ptx::fence_mbar_init();
     ptx::prefetch_tensormap(&amap);
   }
@@ -148,9 +158,11 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
         }
       }
     }
-  } else if (warp == 1) {
-    // ============================== MMA issuer ================================
-    const bool elected = ptx::elect_one();
+  } else if (warp == 1 || warp == ISS2_WARP) {
+    // ============================== MMA issuer(s) =============================
+    const bool second = warp == ISS2_WARP;              // takes accumulator 1 when the item has two
+    const int a_lo = (C::APS == 2 && second) ? 1 : 0, a_hi = C::APS == 2 ? a_lo + 1 : C::APS;
+    const bool elected = ptx::elect_one() && !(second && (C::APS != 2 || rank != 0));
     if (elected && rank != 0) {
       // ---- peer: relay "stage full" to the leader (same loop structure as the issuer below)
       uint32_t sa = 0, pa = 0, sw = 0, pw = 0;
@@ -171,7 +183,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap amap, const Params p) {
       constexpr uint32_t idesc = ptx::idesc_bf16_f32(256, BN);
       uint32_t sa = 0, pa = 0, sw = 0, pw = 0;
       long long t_acc = 0, t_a = 0, t_w = 0, t0 = 0, t1;
-      const bool dbg = p.dbg != nullptr;
+      const bool dbg = p.dbg != nullptr && !second;
       const long long t_begin = dbg ? clock64() : 0;
       for (int kk = 0; kk < iters; ++kk) {
         const uint32_t slot = kk & 1, pacc = (kk >> 1) & 1;
@@ -198,6 +210,7 @@ const uint64_t ad0 = ptx::smem_desc_sw128(abase + tap_off, p.desc_base_offset);
             const uint64_t bd0 = ptx::smem_desc_sw128(wbase, 0);
 #pragma unroll
             for (int a = 0; a < C::APS; ++a) {
+              if (a < a_lo || a >= a_hi) continue;
 #pragma unroll
               for (int k = 0; k < KC / 16; ++k) {
                 const uint64_t ad = ptx::desc_advance(ad0, a * (128 * 128) + k * 32);
@@ -218,7 +231,7 @@ const uint64_t ad0 = ptx::smem_desc_sw128(abase + tap_off, p.desc_base_offset);
         d[0] = clock64() - t_begin; d[1] = t_acc; d[2] = t_a; d[3] = t_w;
       }
     }
-  } else {
+  } else if (warp < ISS2_WARP) {
     // ============================== epilogue ==================================
     // 8 warps: TMEM lane quarter q = warp & 3 (hardware rule), column-group parity `par` = (warp-2) >> 2.
     // Units (accumulator a, 32-column group g) are software-pipelined: the tcgen05.ld (and the skip loads)

@@ -448,7 +448,7 @@ int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_
   p.x5 = reinterpret_cast<const float4*>(x5); p.w1pack = w1; p.w2pack = w2; p.bias2 = b2;
   p.out_u8 = out_u8; p.out_nchw = out_nchw; p.H = H; p.W = W;
   p.tiles_x = (2 * W + thin::G27_TW - 1) / thin::G27_TW;
-  p.tiles_y = (2 * H + thin::G27_ROWS - 1) / thin::G27_ROWS;
+  p.tiles_y = v3 ? (2 * H + thin::UT3_OROWS - 1) / thin::UT3_OROWS : (2 * H + thin::G27_ROWS - 1) / thin::G27_ROWS;
   p.n_img = n; p.out_bgr = out_bgr; p.probe = ctx->opt_thin_probe;
   p.dbg = nullptr;
   const long long total = (long long)p.tiles_x * p.tiles_y * n;
@@ -463,7 +463,7 @@ int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_
     CnnPlan* P = ctx->cnn;
     const cuuint64_t dims[4] = {4, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)n};
     const cuuint64_t strides[3] = {16, (cuuint64_t)W * 16, (cuuint64_t)H * W * 16};
-    const cuuint32_t box[4] = {4, (cuuint32_t)thin::UT_XW, (cuuint32_t)thin::UT_XH, 1};
+    const cuuint32_t box[4] = {4, (cuuint32_t)(v3 ? thin::UT3_XW : thin::UT_XW), (cuuint32_t)(v3 ? thin::UT3_XH : thin::UT_XH), 1};
     const cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = reinterpret_cast<EncodeFn>(P->encode)(
         &xmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(x5), dims, strides, box, estr,

@@ -24,28 +24,40 @@
 namespace vex {
 namespace thin {
 
-// 24 warps: 0-3 builders | 4-6, 8-10 mid-drain (phases 0-1 / 2-3; TMEM lanes 0-95) | 7 GEMM #1 | 11 TMA | 12, 13 GEMM #2
-// (accumulator 0 / 1) | 16-19, 20-23 epilogue groups (items k % 2).  A 32-warp layout with four mid-drain groups was
-// measured too: every role got SLOWER (2620 clocks per item against 1990) - the SM is saturated, more warps only add polling.
+// Item = 10 x 30 hi-res outputs (halo tile 12 x 32 = 384 rows of the second GEMM, three accumulators) from a 7 x 17 low-res
+// patch: 119 of the 128 rows of GEMM #1 are live (tail_tc.cuh: 5 x 17 = 85 rows for 6 x 30 outputs).  Every role pays its
+// barrier round trips and its dependent per-lane chain once per item, so 1.67x the outputs per item is the lever that is
+// left; tail_tc.cuh cannot take it because its 27 gather planes for 384 rows would not fit shared memory.
+// 28 warps: 0-3 builders | 4-7, 8-11 mid-drain (phases 0-1 / 2-3; warp & 3 = TMEM lane quarter) | 12 GEMM #1 | 13 TMA |
+// 14-16 GEMM #2 (one accumulator each) | 20-23, 24-27 epilogue groups (items k % 2).  A 32-warp layout with four mid-drain
+// groups was measured on the small item: every role got SLOWER (2620 clocks per item against 1990).
+constexpr int UT3_LR = 7, UT3_LC = 17;             // low-res pixels under the 12 x 32 hi-res halo tile
+constexpr int UT3_ROWS1 = UT3_LR * UT3_LC;         // 119 live rows of the first GEMM
+constexpr int UT3_OROWS = 10;                      // hi-res output rows per item
+constexpr int UT3_HROWS = UT3_OROWS + 2;           // halo tile rows
+constexpr int UT3_NACC2 = 3;                       // accumulators of GEMM #2 (4 tile rows each)
+constexpr int UT3_XW = UT3_LC + 2, UT3_XH = UT3_LR + 2;   // x5 window: 19 x 9 low-res pixels
+constexpr int UT3_X_BYTES = UT3_XW * UT3_XH * 16;
+constexpr int UT3_X_STAGE = (UT3_X_BYTES + 127) / 128 * 128;
 constexpr int UT3_EPI_GROUPS = 2;
-constexpr int UT3_MMA2_WARP_A = 12, UT3_MMA2_WARP_B = 13;
-constexpr int UT3_EPI_WARP0 = 16;      // warp & 3 = TMEM lane quarter
-constexpr int UT3_THREADS = 32 * (UT3_EPI_WARP0 + 4 * UT3_EPI_GROUPS);   // 768
+constexpr int UT3_MMA1_WARP = 12, UT3_TMA_WARP = 13, UT3_MMA2_WARP0 = 14;
+constexpr int UT3_EPI_WARP0 = 20;      // warp & 3 = TMEM lane quarter
+constexpr int UT3_THREADS = 32 * (UT3_EPI_WARP0 + 4 * UT3_EPI_GROUPS);   // 896
 constexpr int UT3_NACC1 = 3;           // ring of half-accumulators (128 columns each) of GEMM #1
 
 struct UT3Cfg {
   static constexpr int A1_STAGE = 128 * 128;
   static constexpr int A1_OFF = 0;                                  // 2 stages
   static constexpr int W1_OFF = A1_OFF + 2 * A1_STAGE;              // 256 rows x 128 B
-  static constexpr int A2_STAGE = 256 * 128;
+  static constexpr int A2_STAGE = UT3_HROWS * 32 * 128;
   static constexpr int A2_OFF = W1_OFF + 256 * 128;                 // 2 stages
   static constexpr int W2_BYTES = 3 * 16 * 128;                     // [dy] slices of 16 rows (dx*3 + co, 9 used) x 64 k
   static constexpr int W2_OFF = A2_OFF + 2 * A2_STAGE;
-  static constexpr int PAD_OFF = W2_OFF + 8192;                     // GEMM #2 of accumulator 1, dy = 2 reads 8 KB past its A2 stage
+  static constexpr int PAD_OFF = W2_OFF + 8192;                     // GEMM #2 of the last accumulator, dy = 2 reads 8 KB past its A2 stage
   static constexpr int OB_OFF = PAD_OFF + 8192;                     // (rows of outputs that do not exist): keep that finite, zeroed
-  static constexpr int OB_BYTES = G27_ROWS * G27_OB_PITCH + 16;
+  static constexpr int OB_BYTES = UT3_OROWS * G27_OB_PITCH + 16;
   static constexpr int X_OFF = (OB_OFF + UT3_EPI_GROUPS * OB_BYTES + 127) / 128 * 128;
-  static constexpr int BAR_OFF = X_OFF + UT_XS * UT_X_STAGE;
+  static constexpr int BAR_OFF = X_OFF + UT_XS * UT3_X_STAGE;
   static constexpr int SMEM = BAR_OFF + 512 + 1024;
 };
 
@@ -77,10 +89,10 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
       // producers arrive ONCE PER WARP (fence, __syncwarp, lane 0): 4 builder warps, 6 mid-drain warps.  tail_tc.cuh has every
       // thread arrive - ~450 shared-memory atomics per item on three barriers
       ptx::mbar_init(a1_full + 8 * i, 4); ptx::mbar_init(a1_empty + 8 * i, 1);
-      ptx::mbar_init(a2_full + 8 * i, 6); ptx::mbar_init(a2_empty + 8 * i, 2);       // both GEMM #2 threads release a stage
+      ptx::mbar_init(a2_full + 8 * i, 8); ptx::mbar_init(a2_empty + 8 * i, UT3_NACC2);   // every GEMM #2 thread releases a stage
     }
-    for (int i = 0; i < UT3_NACC1; ++i) { ptx::mbar_init(acc1_full + 8 * i, 1); ptx::mbar_init(acc1_empty + 8 * i, 3); }
-    for (int i = 0; i < UT3_EPI_GROUPS; ++i) { ptx::mbar_init(acc2_full + 8 * i, 2); ptx::mbar_init(acc2_empty + 8 * i, 4); }
+    for (int i = 0; i < UT3_NACC1; ++i) { ptx::mbar_init(acc1_full + 8 * i, 1); ptx::mbar_init(acc1_empty + 8 * i, 4); }
+    for (int i = 0; i < UT3_EPI_GROUPS; ++i) { ptx::mbar_init(acc2_full + 8 * i, UT3_NACC2); ptx::mbar_init(acc2_empty + 8 * i, 4); }
     ptx::mbar_init(w_bar, 1);
     for (int i = 0; i < UT_XS; ++i) { ptx::mbar_init(x_full + 8 * i, 1); ptx::mbar_init(x_empty + 8 * i, 4); }
     ptx::fence_mbar_init();
@@ -89,8 +101,8 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
   for (int i = threadIdx.x; i < 8192 / 16; i += UT3_THREADS) reinterpret_cast<uint4*>(sm + C::PAD_OFF)[i] = make_uint4(0u, 0u, 0u, 0u);
   for (int i = threadIdx.x; i < 8192 / 16; i += UT3_THREADS) reinterpret_cast<uint4*>(sm + C::W2_OFF)[i] = make_uint4(0u, 0u, 0u, 0u);
   ptx::fence_proxy_async_smem();
-  if (warp == UT_MMA_WARP) {
-    ptx::tmem_alloc(tmem_slot, 512);                 // [0,384): first GEMM, three half-accumulators; 384 + grp*32 + g*16: second GEMM
+  if (warp == UT3_MMA1_WARP) {
+    ptx::tmem_alloc(tmem_slot, 512);                 // [0,384): first GEMM, three half-accumulators; 384 + grp*64 + g*16: second GEMM
     ptx::tmem_relinquish();
   }
   ptx::tc_fence_before();
@@ -101,15 +113,15 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
   if (warp < 4) {
     // ================================ builders: low-res pixel r of the 5 x 17 patch -> one operand row
     const int r = threadIdx.x;
-    const int lr = r / UT_LC, lc = r - lr * UT_LC;
+    const int lr = r / UT3_LC, lc = r - lr * UT3_LC;
     uint32_t k = 0;
     const bool dbg = p.dbg != nullptr && threadIdx.x == 0;
     long long tw = 0, tx = 0, tb0 = dbg ? clock64() : 0;
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
       const int txi = it % p.tiles_x, t = it / p.tiles_x;
       const int tyi = t % p.tiles_y;
-      const int y = 3 * tyi - 1 + lr, x = 15 * txi - 1 + lc;
-      const bool live = r < UT_ROWS1 && y >= 0 && y < p.H && x >= 0 && x < p.W && !(p.probe & 4);
+      const int y = (UT3_OROWS / 2) * tyi - 1 + lr, x = 15 * txi - 1 + lc;
+      const bool live = r < UT3_ROWS1 && y >= 0 && y < p.H && x >= 0 && x < p.W && !(p.probe & 4);
       const uint32_t xs = k % UT_XS, xp = (k / UT_XS) & 1;
       uint32_t w[16];
 #pragma unroll
@@ -118,11 +130,11 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
       ptx::mbar_wait(x_full + 8 * xs, xp);             // the window of this item has landed (TMA, 4 items ahead)
       if (dbg) tx += clock64() - tx0;
       if (live) {
-        const float4* win = reinterpret_cast<const float4*>(sm + C::X_OFF + xs * UT_X_STAGE) + lr * UT_XW + lc;
+        const float4* win = reinterpret_cast<const float4*>(sm + C::X_OFF + xs * UT3_X_STAGE) + lr * UT3_XW + lc;
         float v[27];
 #pragma unroll
         for (int q9 = 0; q9 < 9; ++q9) {
-          const float4 f = win[(q9 / 3) * UT_XW + q9 % 3];
+          const float4 f = win[(q9 / 3) * UT3_XW + q9 % 3];
           v[q9 * 3 + 0] = f.x; v[q9 * 3 + 1] = f.y; v[q9 * 3 + 2] = f.z;
         }
 #pragma unroll
@@ -146,7 +158,7 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
     }
     if (dbg) p.dbg[blockIdx.x * 16 + 13] = tx;
     if (dbg) { p.dbg[blockIdx.x * 16 + 5] = tw; p.dbg[blockIdx.x * 16 + 6] = clock64() - tb0; }
-  } else if (warp == UT_TMA_WARP) {
+  } else if (warp == UT3_TMA_WARP) {
     // ================================ x5 windows: one box load per item, UT_XS items ahead of the builders
     if (ptx::elect_one()) {
       uint32_t k = 0;
@@ -155,11 +167,11 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
         const int tyi = t % p.tiles_y, n = t / p.tiles_y;
         const uint32_t xs = k % UT_XS, xp = (k / UT_XS) & 1;
         ptx::mbar_wait(x_empty + 8 * xs, xp ^ 1);
-        ptx::mbar_expect_tx(x_full + 8 * xs, UT_X_BYTES);
-        ptx::tma_load_4d(sbase + C::X_OFF + xs * UT_X_STAGE, &xmap, x_full + 8 * xs, 0, 15 * txi - 2, 3 * tyi - 2, n);
+        ptx::mbar_expect_tx(x_full + 8 * xs, UT3_X_BYTES);
+        ptx::tma_load_4d(sbase + C::X_OFF + xs * UT3_X_STAGE, &xmap, x_full + 8 * xs, 0, 15 * txi - 2, (UT3_OROWS / 2) * tyi - 2, n);
       }
     }
-  } else if (warp == UT_MMA_WARP) {
+  } else if (warp == UT3_MMA1_WARP) {
     // ================================ GEMM #1 (and the weight loads)
     if (ptx::elect_one()) {
       ptx::mbar_expect_tx(w_bar, 256 * 128 + C::W2_BYTES);
@@ -199,9 +211,9 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
         d[0] = clock64() - tm0; d[1] = t1; d[2] = t2;
       }
     }
-  } else if (warp == UT3_MMA2_WARP_A || warp == UT3_MMA2_WARP_B) {
+  } else if (warp >= UT3_MMA2_WARP0 && warp < UT3_MMA2_WARP0 + UT3_NACC2) {
     // ================================ GEMM #2, accumulator g: output rows 4g .. 4g+3 of the tile (rows 6, 7 do not exist)
-    const int g = warp == UT3_MMA2_WARP_A ? 0 : 1;
+    const int g = warp - UT3_MMA2_WARP0;
     if (ptx::elect_one()) {
       ptx::mbar_wait(w_bar, 0);
       constexpr uint32_t idesc2 = ptx::idesc_bf16_f32(128, 16);
@@ -219,7 +231,7 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
         ptx::mbar_wait(a2_full + 8 * s, ph);
         if (dbg) t4 += clock64() - tq;
         ptx::tc_fence_after();
-        const uint32_t dcol = tmem + 384 + eg * 32 + g * 16;
+        const uint32_t dcol = tmem + 384 + eg * 64 + g * 16;
 #pragma unroll
         for (int dy = 0; dy < 3; ++dy)               // output row r reads halo rows r, r+1, r+2
 #pragma unroll
@@ -233,13 +245,13 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
       }
       if (dbg) { long long* d = p.dbg + blockIdx.x * 16; d[3] = t3; d[4] = t4; }
     }
-  } else if (warp < 11) {   // (warp 7 = GEMM #1 and warp 11 = TMA were taken above)
-    // ================================ mid-drain: relu(upconv1) of low-res pixel r -> rows of A2.  Group h (warps 4-6 /
-    // 8-10) takes phases 2h and 2h+1 = one half-accumulator of 128 columns.
-    const int h = warp >> 3;
+  } else if (warp < 12) {
+    // ================================ mid-drain: relu(upconv1) of low-res pixel r -> rows of A2.  Group h (warps 4-7 /
+    // 8-11) takes phases 2h and 2h+1 = one half-accumulator of 128 columns.
+    const int h = (warp >> 2) - 1;
     const int q = warp & 3;
     const int r = q * 32 + lane;
-    const int lr = r / UT_LC, lc = r - lr * UT_LC;
+    const int lr = r / UT3_LC, lc = r - lr * UT3_LC;
     uint32_t k = 0;
     const bool dbg = p.dbg != nullptr && warp == 4 && lane == 0;
     long long t7 = 0, t8 = 0, tq = 0, tld = 0;
@@ -260,13 +272,13 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
       for (int pp = 0; pp < 2; ++pp) {
         // hi-res pixel of this phase in halo-tile coordinates: hr = 2*lr + py - 1, hc = 2*lc + px - 1 (py = h, px = pp)
         const int hr = 2 * lr + h - 1, hc = 2 * lc + pp - 1;
-        const bool in_tile = r < UT_ROWS1 && hr >= 0 && hr < 8 && hc >= 0 && hc < 32;
-        const int hy = 6 * tyi - 1 + hr, hx = 30 * txi - 1 + hc;
+        const bool in_tile = r < UT3_ROWS1 && hr >= 0 && hr < UT3_HROWS && hc >= 0 && hc < 32;
+        const int hy = UT3_OROWS * tyi - 1 + hr, hx = 30 * txi - 1 + hc;
         const bool in_img = hy >= 0 && hy < H2 && hx >= 0 && hx < W2;
         // A2 row order: within a hi-res row the even columns come first, then the odd ones.  One PixelShuffle phase has
         // one column parity, so a warp's 16-byte stores then cover all 8 swizzle positions (4 wavefronts instead of 8).
         const int m = hr * 32 + (hc >> 1) + 16 * (hc & 1);
-        uint8_t* row = a2 + (m >> 7) * 16384 + (m & 127) * 128;
+        uint8_t* row = a2 + m * 128;
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint32_t v[32];
@@ -318,14 +330,15 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
     for (int it = blockIdx.x + grp * gridDim.x; it < total; it += UT3_EPI_GROUPS * gridDim.x) {
       const int txi = it % p.tiles_x, t = it / p.tiles_x;
       const int tyi = t % p.tiles_y, n = t / p.tiles_y;
-      const int x0 = txi * G27_TW, y0 = tyi * G27_ROWS;
+      const int x0 = txi * G27_TW, y0 = tyi * UT3_OROWS;
       const long long tq = dbg ? clock64() : 0;
       ptx::mbar_wait(acc2_full + 8 * grp, pb);
       if (dbg) { t10 += clock64() - tq; ++n_items; }
       ptx::tc_fence_after();
-      uint32_t va[16], vb[16];
-      ptx::tmem_ld_32x16(tmem + ((uint32_t)(q * 32) << 16) + 384 + grp * 32, va);        // accumulator 0: tile row q
-      ptx::tmem_ld_32x16(tmem + ((uint32_t)(q * 32) << 16) + 384 + grp * 32 + 16, vb);   // accumulator 1: tile row 4 + q
+      uint32_t va[16], vb[16], vc[16];
+      ptx::tmem_ld_32x16(tmem + ((uint32_t)(q * 32) << 16) + 384 + grp * 64, va);        // accumulator 0: tile row q
+      ptx::tmem_ld_32x16(tmem + ((uint32_t)(q * 32) << 16) + 384 + grp * 64 + 16, vb);   // accumulator 1: tile row 4 + q
+      ptx::tmem_ld_32x16(tmem + ((uint32_t)(q * 32) << 16) + 384 + grp * 64 + 32, vc);   // accumulator 2: tile row 8 + q (rows 10, 11 do not exist)
       ptx::tmem_ld_wait();
       ptx::tc_fence_before();
       __syncwarp();
@@ -333,8 +346,8 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
       pb ^= 1;
       const int nvx = min(G27_TW, W2 - x0);
 #pragma unroll
-      for (int g = 0; g < 2; ++g) {
-        const uint32_t* v = g ? vb : va;
+      for (int g = 0; g < UT3_NACC2; ++g) {
+        const uint32_t* v = g == 0 ? va : (g == 1 ? vb : vc);
         float s[3];
 #pragma unroll
         for (int co = 0; co < 3; ++co) {
@@ -344,7 +357,7 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
         }
         const int ty = 4 * g + q;
         const int y = y0 + ty, x = x0 + tx;
-        if (ty < G27_ROWS && tx >= 0 && tx < G27_TW && y < H2 && x < W2 && !(p.probe & 1)) {
+        if (ty < UT3_OROWS && tx >= 0 && tx < G27_TW && y < H2 && x < W2 && !(p.probe & 1)) {
           const float c0 = fminf(fmaxf(s[0] + b0, 0.f), 1.f), c1 = fminf(fmaxf(s[1] + b1, 0.f), 1.f),
                       c2 = fminf(fmaxf(s[2] + b2, 0.f), 1.f);
           if (p.out_nchw) {
@@ -365,7 +378,7 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
       }
       if (p.out_u8) {
         named_bar_sync(1 + grp, 128);
-        for (int wi = et; wi < G27_ROWS * 24; wi += 128) {
+        for (int wi = et; wi < UT3_OROWS * 24; wi += 128) {
           const int ty = wi / 24, jw = wi - ty * 24;
           const int y = y0 + ty;
           if (y >= H2) continue;
@@ -389,7 +402,7 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
   }
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == UT_MMA_WARP) {
+  if (warp == UT3_MMA1_WARP) {
     __syncwarp();
     ptx::tmem_dealloc(tmem, 512);
   }

@@ -268,9 +268,10 @@ int vex_kernel_launches(const vex_ctx* ctx, unsigned long long* out);
  *              Real-ESRGAN layer chain), "rrdb_batch" (how many tiles of a Real-ESRGAN frame run as one batch of canvases;
  *              1 = one after the other as in realesrgan_handler.py:342-370; bit-identical for every value).
  *   variants kept as bit-identity cross-checks (tests/test_cnn_gpu.py): "conv_variant" (0 = default v3 cta_group::2,
- *              1 = single-CTA, 2 = multicast pairs), "conv1_variant" (0 = fp16 offset-1024 operand builder, 1 = bf16 builder), "thin_tc" (0 = fp32 CUDA-core thin layers), "fuse_tail" (0 = upconv1 /
- *              upconv2 as two kernels with `up` in HBM, 3 = fused with `up` kept in tensor memory, 4 = fused with the vertical tap of
- *              upconv2 accumulated by the tensor core: same products, other fp32 summation order, within 1 LSB of the default), "force_generic_bicubic", "force_generic_resize", "bicubic_rows".
+ *              1 = single-CTA, 2 = multicast pairs), "conv1_variant" (0 = fp16 offset-1024 operand builder, 1 = bf16 builder), "thin_tc" (0 = fp32 CUDA-core thin layers), "fuse_tail" (default 4 = fused tail with upconv2's vertical
+ *              tap accumulated by the tensor core; 1 = the first fused tail (27 planes + 9-tap gather; same products, other fp32
+ *              summation order, within 1 LSB of 4), 3 = 1 with `up` kept in tensor memory (bit-identical to 1), 0 = upconv1 / upconv2 as two
+ *              kernels with `up` in HBM), "force_generic_bicubic", "force_generic_resize", "bicubic_rows".
  *   bring-up probes that PRODUCE WRONG RESULTS (timing experiments only; refused unless the library was built with
  *              -DVEX_DEBUG_PROBES): "epi_variant", "thin_probe", "desc_base_offset"; "conv_dbg" prints per-role cycle
  *              counters and synchronises. */

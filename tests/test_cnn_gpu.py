@@ -503,18 +503,19 @@ def test_conv1_operand_builders_agree(enhancers, models, h, w):
 
 @pytest.mark.parametrize("h,w", [(1, 1), (2, 3), (3, 15), (4, 16), (37, 53), (130, 70), (45, 16), (360, 480)])
 def test_fused_tail_generations_bit_identical(enhancers, h, w):
-    """option fuse_tail: 1 = default (relu(upconv1) written to shared memory in PixelShuffle order as the A operand of the
-    second GEMM), 3 = the variant that keeps it in TENSOR memory (the PixelShuffle becomes four phase planes indexed by the
+    """option fuse_tail: 1 = the first fused tail (relu(upconv1) written to shared memory in PixelShuffle order as the A operand of the
+    second GEMM, 27 planes + 9-tap gather), 3 = the variant that keeps it in TENSOR memory (the PixelShuffle becomes four phase planes indexed by the
     low-res pixel, the second GEMM reads its A operand from TMEM).  Same products, same K order per accumulator, same tap order in the gather: the uint8
     frames and the pre-quantisation fp32 output must be bit-identical, on ragged tiles and image borders too."""
     rng = np.random.default_rng(55)
     frames = [synth.random_frame(h, w, rng), synth.edges_frame(h, w, rng), synth.random_frame(h, w, rng)]
     for key in ("seed0", "stress"):
         enh = enhancers[key]
-        a8 = enh.upscale_device(dev(frames), mode="cnn", out_bgr=True).cpu().numpy()
-        a = enh.cnn_debug_f32(dev(frames), tap=0).cpu().numpy()
-        prev = enh.set_option("fuse_tail", 3)
+        prev = enh.set_option("fuse_tail", 1)
         try:
+            a8 = enh.upscale_device(dev(frames), mode="cnn", out_bgr=True).cpu().numpy()
+            a = enh.cnn_debug_f32(dev(frames), tap=0).cpu().numpy()
+            enh.set_option("fuse_tail", 3)
             b8 = enh.upscale_device(dev(frames), mode="cnn", out_bgr=True).cpu().numpy()
             b = enh.cnn_debug_f32(dev(frames), tap=0).cpu().numpy()
         finally:
@@ -525,18 +526,21 @@ def test_fused_tail_generations_bit_identical(enhancers, h, w):
 
 @pytest.mark.parametrize("h,w", [(1, 1), (2, 3), (3, 15), (4, 16), (37, 53), (130, 70), (45, 16), (360, 480)])
 def test_fused_tail_with_the_vertical_tap_in_the_tensor_core(enhancers, h, w):
-    """option fuse_tail = 4 (csrc/tail_tc3.cuh): the second GEMM accumulates the vertical tap (three row-shifted MMAs of
-    N = 16 per K step) and the epilogue adds the three horizontal taps with lane shuffles; no 27-plane gather.  The products
-    are the default tail's, the order of the fp32 additions is not, so the pre-quantisation output agrees to fp32 rounding
-    and the truncated uint8 to 1 LSB on a handful of bytes - on ragged tiles and image borders too."""
+    """option fuse_tail: 4 = the default (csrc/tail_tc3.cuh: 10 x 30-output items, the second GEMM accumulates the vertical tap
+    with three row-shifted MMAs of N = 16 per K step, the epilogue adds the three horizontal taps with lane shuffles; no
+    27-plane gather) against 1 = the first fused tail.  The products are the same, the order of the fp32 additions is not,
+    so the pre-quantisation output agrees to fp32 rounding and the truncated uint8 to 1 LSB on a handful of bytes - on
+    ragged tiles, image borders and frames smaller than one item too."""
     rng = np.random.default_rng(56)
     frames = [synth.random_frame(h, w, rng), synth.edges_frame(h, w, rng), synth.random_frame(h, w, rng)]
     for key in ("seed0", "stress"):
         enh = enhancers[key]
-        a8 = enh.upscale_device(dev(frames), mode="cnn", out_bgr=True).cpu().numpy().astype(int)
-        a = enh.cnn_debug_f32(dev(frames), tap=0).cpu().numpy()
-        prev = enh.set_option("fuse_tail", 4)
+        prev = enh.set_option("fuse_tail", 1)
+        assert prev == 4                                                   # the default
         try:
+            a8 = enh.upscale_device(dev(frames), mode="cnn", out_bgr=True).cpu().numpy().astype(int)
+            a = enh.cnn_debug_f32(dev(frames), tap=0).cpu().numpy()
+            enh.set_option("fuse_tail", 4)
             b8 = enh.upscale_device(dev(frames), mode="cnn", out_bgr=True).cpu().numpy().astype(int)
             b = enh.cnn_debug_f32(dev(frames), tap=0).cpu().numpy()
         finally:

@@ -430,10 +430,10 @@ int launch_g27(vex_ctx* ctx, unsigned abit, const __nv_bfloat16* in, int C, cons
 // x5 [n][H][W] -> uint8 [n][2H][2W][3]: upconv1 + relu + upconv2 + clamp + quantise in one kernel (tail_tc.cuh)
 int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_t* w2, const float* b2,
                   uint8_t* out_u8, float* out_nchw, int n, int H, int W, int out_bgr, cudaStream_t s) {
-  // fuse_tail: 1 = default (relu(upconv1) handed to the second GEMM through shared memory, tail_tc.cuh); 3 = the variant
+  // fuse_tail: 4 = default (tail_tc3.cuh, below); 1 = the first fused tail (relu(upconv1) handed to the second GEMM through shared memory, tail_tc.cuh); 3 = the variant
   // that keeps it in tensor memory (tail_tc2.cuh: bit-identical, 40 % less shared-memory traffic, two issuing threads; it
   // measures 2007-2022 against 1960 cycles per item - a tie); 4 = tail_tc3.cuh (vertical tap of upconv2 in the tensor core,
-  // horizontal tap by lane shuffles, a ring of three half-accumulators for GEMM #1: 1990-2010 cycles per item, a tie again)
+  // horizontal tap by lane shuffles, 10 x 30 outputs per item from a 7 x 17 low-res patch: 2.7-2.9 ms against 3.4-3.9)
   const bool v2 = ctx->opt_fuse_tail == 3, v3 = ctx->opt_fuse_tail == 4;   // 4: tail_tc3.cuh (vertical tap in the tensor core)
   if (!(ctx->attr_mask & 0x400u)) {
     VEX_CUDA(ctx, cudaFuncSetAttribute(thin::uptail3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

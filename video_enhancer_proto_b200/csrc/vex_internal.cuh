@@ -71,7 +71,7 @@ struct vex_ctx {
   int max_pairs = 0;                 // co-resident 2-CTA clusters of conv_tc2 (queried once)
   int opt_bicubic_rows = 0;          // rows per strip override (0 = auto)
   int opt_conv3_bn = 256;         // Cout block of conv3 on the tensor cores (128 or 256)
-  int opt_fuse_tail = 1;          // upconv1 + upconv2 in one kernel (tail_tc.cuh); 0 = two kernels with `up` in HBM
+  int opt_fuse_tail = 4;          // upconv1 + upconv2 in one kernel: 4 = tail_tc3.cuh (default), 1 = tail_tc.cuh, 3 = tail_tc2.cuh; 0 = two kernels with `up` in HBM
   int opt_thin_tc = 1;            // thin layers on tcgen05 (thin_tc.cuh); 0 = fp32 CUDA-core kernels (cnn_small.cuh)
   int opt_epi_variant = 0;        // bring-up timing probes for the conv_tc epilogue (produce wrong results)
   int opt_conv_dbg = 0;           // bring-up: print per-role cycle counters of every conv_tc launch (synchronises)

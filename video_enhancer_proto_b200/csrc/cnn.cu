@@ -453,6 +453,8 @@ int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_
   p.dbg = nullptr;
   const long long total = (long long)p.tiles_x * p.tiles_y * n;
   if (total > 0x7fffffffLL) return fail(ctx, VEX_ERR_INVALID, "uptail: too many tiles");
+  p.rcp_tx = p.rcp_ty = 0.f;
+  if (total < (1LL << 22)) { p.rcp_tx = 1.0f / (float)p.tiles_x; p.rcp_ty = 1.0f / (float)p.tiles_y; }
   const unsigned grid = (unsigned)std::min<long long>(total, ctx->sm_count);
   if (ctx->opt_conv_dbg) {                   // bring-up: per-role cycle counters, printed after the launch
     VEX_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&p.dbg), (size_t)grid * 128));

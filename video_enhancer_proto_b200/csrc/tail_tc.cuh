@@ -62,6 +62,7 @@ struct UTParams {
   int H, W;                // LOW-res size
   int tiles_x, tiles_y, n_img;
   int out_bgr;
+  float rcp_tx, rcp_ty;    // 1 / tiles_x, 1 / tiles_y when the item count is below 2^22 (else 0): tail_tc3.cuh divides by multiplying
   int probe;               // bring-up timing probes (WRONG RESULTS): 4 = no gather loads, 2 = mid-drain without stores, 1 = epilogue without gather
   long long* dbg;          // optional [gridDim.x][16] cycle counters per role (option conv_dbg): MMA thread 0 total, 1 wait a1_full,
                            // 2 wait acc1_empty, 3 wait acc2_empty, 4 wait a2_full; builder 5 wait a1_empty, 6 total; mid-drain (warp 4)

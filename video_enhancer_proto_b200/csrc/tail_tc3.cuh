@@ -61,6 +61,27 @@ struct UT3Cfg {
   static constexpr int SMEM = BAR_OFF + 512 + 1024;
 };
 
+// it -> (txi, tyi, n).  Every warp of every role needs this once per item, and two 32-bit integer divisions are ~60
+// instructions each time - a quarter of all warp-instructions the kernel issues per item, on schedulers that are 63 %
+// busy.  For item counts below 2^22 the quotient is a float multiply plus one correction step (exact: the estimate is off by
+// at most one).
+__device__ __forceinline__ void ut3_tile(const UTParams& p, int it, int& txi, int& tyi, int& n) {
+  if (p.rcp_tx != 0.f) {
+    int t = __float2int_rz(__int2float_rn(it) * p.rcp_tx);
+    int r = it - t * p.tiles_x;
+    if (r < 0) { --t; r += p.tiles_x; } else if (r >= p.tiles_x) { ++t; r -= p.tiles_x; }
+    txi = r;
+    int q = __float2int_rz(__int2float_rn(t) * p.rcp_ty);
+    int r2 = t - q * p.tiles_y;
+    if (r2 < 0) { --q; r2 += p.tiles_y; } else if (r2 >= p.tiles_y) { ++q; r2 -= p.tiles_y; }
+    tyi = r2; n = q;
+  } else {
+    txi = it % p.tiles_x;
+    const int t = it / p.tiles_x;
+    tyi = t % p.tiles_y; n = t / p.tiles_y;
+  }
+}
+
 __global__ void __launch_bounds__(UT3_THREADS, 1)
 uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
   using C = UT3Cfg;
@@ -118,8 +139,8 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
     const bool dbg = p.dbg != nullptr && threadIdx.x == 0;
     long long tw = 0, tx = 0, tb0 = dbg ? clock64() : 0;
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
-      const int txi = it % p.tiles_x, t = it / p.tiles_x;
-      const int tyi = t % p.tiles_y;
+      int txi, tyi, n_unused;
+      ut3_tile(p, it, txi, tyi, n_unused);
       const int y = (UT3_OROWS / 2) * tyi - 1 + lr, x = 15 * txi - 1 + lc;
       const bool live = r < UT3_ROWS1 && y >= 0 && y < p.H && x >= 0 && x < p.W && !(p.probe & 4);
       const uint32_t xs = k % UT_XS, xp = (k / UT_XS) & 1;
@@ -163,8 +184,8 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
     if (ptx::elect_one()) {
       uint32_t k = 0;
       for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
-        const int txi = it % p.tiles_x, t = it / p.tiles_x;
-        const int tyi = t % p.tiles_y, n = t / p.tiles_y;
+        int txi, tyi, n;
+        ut3_tile(p, it, txi, tyi, n);
         const uint32_t xs = k % UT_XS, xp = (k / UT_XS) & 1;
         ptx::mbar_wait(x_empty + 8 * xs, xp ^ 1);
         ptx::mbar_expect_tx(x_full + 8 * xs, UT3_X_BYTES);
@@ -257,8 +278,8 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
     long long t7 = 0, t8 = 0, tq = 0, tld = 0;
     const long long td0 = dbg ? clock64() : 0;
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
-      const int txi = it % p.tiles_x, t = it / p.tiles_x;
-      const int tyi = t % p.tiles_y;
+      int txi, tyi, n_unused;
+      ut3_tile(p, it, txi, tyi, n_unused);
       const uint32_t s = k & 1;
       if (dbg) tq = clock64();
       ptx::mbar_wait(a2_empty + 8 * s, ((k >> 1) & 1) ^ 1);
@@ -328,8 +349,8 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
     long long t10 = 0, n_items = 0;
     const long long te0 = dbg ? clock64() : 0;
     for (int it = blockIdx.x + grp * gridDim.x; it < total; it += UT3_EPI_GROUPS * gridDim.x) {
-      const int txi = it % p.tiles_x, t = it / p.tiles_x;
-      const int tyi = t % p.tiles_y, n = t / p.tiles_y;
+      int txi, tyi, n;
+      ut3_tile(p, it, txi, tyi, n);
       const int x0 = txi * G27_TW, y0 = tyi * UT3_OROWS;
       const long long tq = dbg ? clock64() : 0;
       ptx::mbar_wait(acc2_full + 8 * grp, pb);

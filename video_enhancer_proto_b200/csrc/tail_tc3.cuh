@@ -82,6 +82,9 @@ __device__ __forceinline__ void ut3_tile(const UTParams& p, int it, int& txi, in
   }
 }
 
+// DBG = the per-role cycle counters of option conv_dbg.  They are a template parameter, not a run-time flag: predicated-off
+// instructions still take issue slots, and issue slots are what this kernel is short of.
+template <bool DBG>
 __global__ void __launch_bounds__(UT3_THREADS, 1)
 uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
   using C = UT3Cfg;
@@ -136,7 +139,7 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
     const int r = threadIdx.x;
     const int lr = r / UT3_LC, lc = r - lr * UT3_LC;
     uint32_t k = 0;
-    const bool dbg = p.dbg != nullptr && threadIdx.x == 0;
+    const bool dbg = DBG && p.dbg != nullptr && threadIdx.x == 0;
     long long tw = 0, tx = 0, tb0 = dbg ? clock64() : 0;
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
       int txi, tyi, n_unused;
@@ -201,7 +204,7 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
       ptx::mbar_wait(w_bar, 0);
       constexpr uint32_t idesc1 = ptx::idesc_bf16_f32(128, 128);
       const uint64_t a1d0 = ptx::smem_desc_sw128(sbase + C::A1_OFF, 0), w1d = ptx::smem_desc_sw128(sbase + C::W1_OFF, 0);
-      const bool dbg = p.dbg != nullptr;
+      const bool dbg = DBG && p.dbg != nullptr;
       long long t1 = 0, t2 = 0, tq;
       const long long tm0 = dbg ? clock64() : 0;
       uint32_t k = 0;
@@ -240,7 +243,7 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
       constexpr uint32_t idesc2 = ptx::idesc_bf16_f32(128, 16);
       const uint64_t a2d0 = ptx::smem_desc_sw128(sbase + C::A2_OFF + (4 * g) * 32 * 128, 0);
       const uint64_t w2d = ptx::smem_desc_sw128(sbase + C::W2_OFF, 0);
-      const bool dbg = p.dbg != nullptr && g == 0;
+      const bool dbg = DBG && p.dbg != nullptr && g == 0;
       long long t3 = 0, t4 = 0, tq;
       uint32_t k = 0;
       for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
@@ -274,7 +277,7 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
     const int r = q * 32 + lane;
     const int lr = r / UT3_LC, lc = r - lr * UT3_LC;
     uint32_t k = 0;
-    const bool dbg = p.dbg != nullptr && warp == 4 && lane == 0;
+    const bool dbg = DBG && p.dbg != nullptr && warp == 4 && lane == 0;
     long long t7 = 0, t8 = 0, tq = 0, tld = 0;
     const long long td0 = dbg ? clock64() : 0;
     for (int it = blockIdx.x; it < total; it += gridDim.x, ++k) {
@@ -345,7 +348,7 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
     const int src_r = even ? 16 + j : (j + 1) & 15;     // lane holding column hc + 1 (column 31 has none)
     const int tx = hc - 1;
     uint32_t pb = 0;
-    const bool dbg = p.dbg != nullptr && warp == UT3_EPI_WARP0 && lane == 0;
+    const bool dbg = DBG && p.dbg != nullptr && warp == UT3_EPI_WARP0 && lane == 0;
     long long t10 = 0, n_items = 0;
     const long long te0 = dbg ? clock64() : 0;
     for (int it = blockIdx.x + grp * gridDim.x; it < total; it += UT3_EPI_GROUPS * gridDim.x) {

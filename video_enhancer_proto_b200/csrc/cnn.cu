@@ -436,9 +436,9 @@ int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_
   // horizontal tap by lane shuffles, 10 x 30 outputs per item from a 7 x 17 low-res patch: 2.7-2.9 ms against 3.4-3.9)
   const bool v2 = ctx->opt_fuse_tail == 3, v3 = ctx->opt_fuse_tail == 4;   // 4: tail_tc3.cuh (vertical tap in the tensor core)
   if (!(ctx->attr_mask & 0x400u)) {
-    VEX_CUDA(ctx, cudaFuncSetAttribute(thin::uptail3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    VEX_CUDA(ctx, cudaFuncSetAttribute(thin::uptail3_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        thin::UT3Cfg::SMEM));
-    VEX_CUDA(ctx, cudaFuncSetAttribute(thin::uptail3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    VEX_CUDA(ctx, cudaFuncSetAttribute(thin::uptail3_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        thin::UT3Cfg::SMEM));
     VEX_CUDA(ctx, cudaFuncSetAttribute(thin::uptail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        thin::UTCfg::SMEM));
@@ -475,8 +475,9 @@ int launch_uptail(vex_ctx* ctx, const float* x5, const uint8_t* w1, const uint8_
         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(ctx, VEX_ERR_CUDA, "cuTensorMapEncodeTiled (x5) failed (" + std::to_string((int)r) + ")");
   }
-  if (v3 && p.dbg) thin::uptail3_kernel<true><<<grid, thin::UT3_THREADS, thin::UT3Cfg::SMEM, s>>>(xmap, p);
-  else if (v3) thin::uptail3_kernel<false><<<grid, thin::UT3_THREADS, thin::UT3Cfg::SMEM, s>>>(xmap, p);
+  // the production instantiation carries neither the cycle counters nor the fp32 output of the parity hook
+  if (v3 && (p.dbg || out_nchw)) thin::uptail3_kernel<true, true><<<grid, thin::UT3_THREADS, thin::UT3Cfg::SMEM, s>>>(xmap, p);
+  else if (v3) thin::uptail3_kernel<false, false><<<grid, thin::UT3_THREADS, thin::UT3Cfg::SMEM, s>>>(xmap, p);
   else if (v2) thin::uptail2_kernel<<<grid, thin::UT_THREADS, thin::UT2Cfg::SMEM, s>>>(xmap, p);
   else thin::uptail_kernel<<<grid, thin::UT_THREADS, thin::UTCfg::SMEM, s>>>(xmap, p);
   ctx->launches++;

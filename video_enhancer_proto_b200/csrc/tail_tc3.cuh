@@ -19,6 +19,8 @@
 // Everything up to the A2 operand (x5 windows by TMA, builders, GEMM #1, mid-drain) is tail_tc.cuh's.
 #pragma once
 
+#include <type_traits>
+
 #include "tail_tc.cuh"
 
 namespace vex {
@@ -84,7 +86,7 @@ __device__ __forceinline__ void ut3_tile(const UTParams& p, int it, int& txi, in
 
 // DBG = the per-role cycle counters of option conv_dbg.  They are a template parameter, not a run-time flag: predicated-off
 // instructions still take issue slots, and issue slots are what this kernel is short of.
-template <bool DBG>
+template <bool DBG, bool NCHW>   // NCHW: the fp32 pre-quantisation output of the parity hook (p.out_nchw) is written too
 __global__ void __launch_bounds__(UT3_THREADS, 1)
 uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
   using C = UT3Cfg;
@@ -292,13 +294,18 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
       if (dbg) t8 += clock64() - tq;
       ptx::tc_fence_after();
       uint8_t* a2 = sm + C::A2_OFF + s * C::A2_STAGE;
+      // An item whose halo tile lies inside the image (all but the border items) needs no per-pixel image test and no
+      // zero rows: the same loop is instantiated without them (fewer instructions on the role that paces the kernel).
+      const bool interior = UT3_OROWS * tyi >= 1 && UT3_OROWS * tyi + UT3_HROWS - 1 <= H2 && 30 * txi >= 1 && 30 * txi + 31 <= W2;
+      auto drain = [&](auto interior_c) {
+      constexpr bool INTERIOR = decltype(interior_c)::value;
 #pragma unroll
       for (int pp = 0; pp < 2; ++pp) {
         // hi-res pixel of this phase in halo-tile coordinates: hr = 2*lr + py - 1, hc = 2*lc + px - 1 (py = h, px = pp)
         const int hr = 2 * lr + h - 1, hc = 2 * lc + pp - 1;
         const bool in_tile = r < UT3_ROWS1 && hr >= 0 && hr < UT3_HROWS && hc >= 0 && hc < 32;
         const int hy = UT3_OROWS * tyi - 1 + hr, hx = 30 * txi - 1 + hc;
-        const bool in_img = hy >= 0 && hy < H2 && hx >= 0 && hx < W2;
+        const bool in_img = INTERIOR || (hy >= 0 && hy < H2 && hx >= 0 && hx < W2);
         // A2 row order: within a hi-res row the even columns come first, then the odd ones.  One PixelShuffle phase has
         // one column parity, so a warp's 16-byte stores then cover all 8 swizzle positions (4 wavefronts instead of 8).
         const int m = hr * 32 + (hc >> 1) + 16 * (hc & 1);
@@ -310,7 +317,7 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
           ptx::tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + jb * 128 + pp * 64 + half * 32, v);
           ptx::tmem_ld_wait();
           if (dbg) tld += clock64() - tl0;
-          if (in_tile && !(p.probe & 2)) {
+          if (in_tile) {
 #pragma unroll
             for (int j4 = 0; j4 < 4; ++j4) {
               uint4 o = make_uint4(0u, 0u, 0u, 0u);
@@ -324,6 +331,8 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
           }
         }
       }
+      };
+      if (interior) drain(std::true_type{}); else drain(std::false_type{});
       ptx::tc_fence_before();
       ptx::fence_proxy_async_smem();
       __syncwarp();
@@ -369,6 +378,10 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
       if (lane == 0) ptx::mbar_arrive(acc2_empty + 8 * grp);
       pb ^= 1;
       const int nvx = min(G27_TW, W2 - x0);
+      // low address bits of the first byte of output row y0 + q; a row further down adds 3 * W2 (only bits 0-1 matter)
+      const uint32_t row_step_lo = (uint32_t)(3 * W2);
+      const uint32_t row0_lo = (uint32_t)reinterpret_cast<uintptr_t>(p.out_u8) +
+                               (uint32_t)(((uint32_t)n * (uint32_t)H2 + (uint32_t)(y0 + q)) * row_step_lo) + (uint32_t)(3 * x0);
 #pragma unroll
       for (int g = 0; g < UT3_NACC2; ++g) {
         const uint32_t* v = g == 0 ? va : (g == 1 ? vb : vc);
@@ -384,7 +397,7 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
         if (ty < UT3_OROWS && tx >= 0 && tx < G27_TW && y < H2 && x < W2 && !(p.probe & 1)) {
           const float c0 = fminf(fmaxf(s[0] + b0, 0.f), 1.f), c1 = fminf(fmaxf(s[1] + b1, 0.f), 1.f),
                       c2 = fminf(fmaxf(s[2] + b2, 0.f), 1.f);
-          if (p.out_nchw) {
+          if (NCHW && p.out_nchw) {
             const size_t plane = (size_t)H2 * W2;
             float* o = p.out_nchw + (size_t)n * 3 * plane + (size_t)y * W2 + x;
             o[0] = c0; o[plane] = c1; o[2 * plane] = c2;
@@ -393,8 +406,7 @@ uptail3_kernel(const __grid_constant__ CUtensorMap xmap, const UTParams p) {
             // np.clip(x*255, 0, 255).astype(np.uint8): fp32 product, truncation (app.py:549)
             const uint8_t q0 = (uint8_t)__float2uint_rz(c0 * 255.0f), q1 = (uint8_t)__float2uint_rz(c1 * 255.0f),
                           q2 = (uint8_t)__float2uint_rz(c2 * 255.0f);
-            const size_t rowb = (((size_t)n * H2 + y) * W2 + x0) * 3;
-            const int ph = (int)(reinterpret_cast<uintptr_t>(p.out_u8 + rowb) & 3);
+            const int ph = (int)((row0_lo + (uint32_t)(4 * g) * row_step_lo) & 3u);   // (out_u8 + row start of y) & 3
             uint8_t* sp = ob + ty * G27_OB_PITCH + ph + tx * 3;
             sp[0] = p.out_bgr ? q2 : q0; sp[1] = q1; sp[2] = p.out_bgr ? q0 : q2;
           }
